@@ -1,0 +1,25 @@
+// Test-infrastructure shim (NOT product code): prototype-only C++ view of the
+// volk_gnsssdr dispatchers, so that the reference's
+// src/algorithms/tracking/libs/cpu_multicorrelator*.cc compile unmodified.
+// The symbols are defined (as C) in oracle/ref_kernels.c.
+#ifndef ORACLE_SHIM_VOLK_GNSSSDR_CXX_H
+#define ORACLE_SHIM_VOLK_GNSSSDR_CXX_H
+#include <complex>
+#include <cstddef>
+#include <cstdint>
+typedef std::complex<float> lv_32fc_t;
+typedef std::complex<int16_t> lv_16sc_t;
+template <typename T>
+inline std::complex<T> lv_cmake(const T& r, const T& i) { return std::complex<T>(r, i); }
+extern "C" {
+void* volk_gnsssdr_malloc(size_t size, size_t alignment);
+void volk_gnsssdr_free(void* p);
+size_t volk_gnsssdr_get_alignment(void);
+void volk_gnsssdr_32f_xn_resampler_32f_xn(float** result, const float* local_code, float rem_code_phase_chips, float code_phase_step_chips, float* shifts_chips, unsigned int code_length_chips, int num_out_vectors, unsigned int num_points);
+void volk_gnsssdr_32f_xn_high_dynamics_resampler_32f_xn(float** result, const float* local_code, float rem_code_phase_chips, float code_phase_step_chips, float code_phase_rate_step_chips, float* shifts_chips, unsigned int code_length_chips, int num_out_vectors, unsigned int num_points);
+void volk_gnsssdr_32fc_32f_rotator_dot_prod_32fc_xn(lv_32fc_t* result, const lv_32fc_t* in_common, const lv_32fc_t phase_inc, lv_32fc_t* phase, const float** in_a, int num_a_vectors, unsigned int num_points);
+void volk_gnsssdr_32fc_32f_high_dynamic_rotator_dot_prod_32fc_xn(lv_32fc_t* result, const lv_32fc_t* in_common, const lv_32fc_t phase_inc, const lv_32fc_t phase_inc_rate, lv_32fc_t* phase, const float** in_a, int num_a_vectors, unsigned int num_points);
+void volk_gnsssdr_32fc_xn_resampler_32fc_xn(lv_32fc_t** result, const lv_32fc_t* local_code, float rem_code_phase_chips, float code_phase_step_chips, float* shifts_chips, unsigned int code_length_chips, int num_out_vectors, unsigned int num_points);
+void volk_gnsssdr_32fc_x2_rotator_dot_prod_32fc_xn(lv_32fc_t* result, const lv_32fc_t* in_common, const lv_32fc_t phase_inc, lv_32fc_t* phase, const lv_32fc_t** in_a, int num_a_vectors, unsigned int num_points);
+}
+#endif
