@@ -1,0 +1,238 @@
+"""ctypes doors onto the TEST-ONLY oracles.
+
+* ``oracle/liboracle.so``       — our plain-C restatement (always buildable; `make -C oracle liboracle.so`)
+* ``oracle/_ref/libgnssref.so`` — the reference's own code compiled where it lies (built in the dev container only;
+  the prebuilt .so travels to the GPU box, /root/reference does not)
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs import this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+
+f32p = C.POINTER(C.c_float)
+f64p = C.POINTER(C.c_double)
+i32p = C.POINTER(C.c_int32)
+i64p = C.POINTER(C.c_int64)
+
+
+def _p(a, t=f32p):
+    return a.ctypes.data_as(t)
+
+
+def build_oracle():
+    so = os.path.join(ORACLE_DIR, "liboracle.so")
+    srcs = [os.path.join(ORACLE_DIR, f) for f in os.listdir(ORACLE_DIR) if f.endswith((".c", ".h"))]
+    if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "liboracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+class AcqConf(C.Structure):
+    _fields_ = [
+        ("fft_size", C.c_int32), ("consumed", C.c_int32), ("num_doppler_bins", C.c_int32), ("bit_transition", C.c_int32),
+        ("use_cfar", C.c_int32), ("samples_per_chip", C.c_int32), ("doppler_max", C.c_int32), ("doppler_step", C.c_int32),
+        ("doppler_center", C.c_int32), ("max_dwells", C.c_int32), ("samples_per_code", C.c_float), ("fs_in", C.c_double),
+        ("fft_f64", C.c_int32), ("sincos_arch", C.c_int32),
+    ]
+
+
+class AcqResult(C.Structure):
+    _fields_ = [
+        ("indext", C.c_uint32), ("doppler_index", C.c_int32), ("doppler_hz", C.c_int32), ("peak", C.c_float),
+        ("input_power", C.c_float), ("test_statistics", C.c_float), ("acq_delay_samples", C.c_float), ("acq_doppler_hz", C.c_float),
+    ]
+
+
+_ORC = None
+_REF = None
+
+
+def orc():
+    global _ORC
+    if _ORC is None:
+        _ORC = C.CDLL(build_oracle())
+        _ORC.orc_acq_threshold.restype = C.c_float
+        _ORC.orc_acq_threshold.argtypes = [C.POINTER(AcqConf), C.c_float]
+    return _ORC
+
+
+def ref_available():
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libgnssref.so"))
+
+
+def ref():
+    """The reference's own compiled code (None when oracle/_ref was never built)."""
+    global _REF
+    if _REF is None:
+        if not ref_available():
+            return None
+        _REF = C.CDLL(os.path.join(ORACLE_DIR, "_ref", "libgnssref.so"))
+        _REF.ref_mc_real_codes_bench.restype = C.c_double
+        for name in ("ref_pll_cloop_two_quadrant_atan", "ref_pll_four_quadrant_atan", "ref_fll_four_quadrant_atan", "ref_fll_diff_atan",
+                     "ref_dll_nc_e_minus_l_normalized", "ref_dll_nc_vemlp_normalized", "ref_sinboc_slope_abs", "ref_sinboc_yintercept_abs"):
+            getattr(_REF, name).restype = C.c_double
+        for name in ("ref_cn0_m2m4_estimator", "ref_cn0_svn_estimator", "ref_carrier_lock_detector"):
+            getattr(_REF, name).restype = C.c_float
+    return _REF
+
+
+# ------------------------------------------------------------------ tracking
+def mc_real_codes(sig, code, shifts, rem_carr, phase_step, rem_code, code_step, n=None, high_dyn=False, phase_rate=0.0, code_rate=0.0, impl="orc", arch=0):
+    """One Cpu_Multicorrelator_Real_Codes call. impl: 'orc' (restatement) | 'ref' (reference .so; arch 0 generic / 1 AVX)."""
+    sig = np.ascontiguousarray(sig, dtype=np.complex64)
+    code = np.ascontiguousarray(code, dtype=np.float32)
+    shifts = np.ascontiguousarray(shifts, dtype=np.float32)
+    n = len(sig) if n is None else n
+    out = np.zeros(len(shifts), dtype=np.complex64)
+    f = C.c_float
+    if impl == "orc":
+        rc = orc().orc_mc_real_codes(int(high_dyn), _p(sig), n, _p(code), len(code), _p(shifts), len(shifts), f(rem_carr), f(phase_step),
+                                     f(phase_rate), f(rem_code), f(code_step), f(code_rate), _p(out))
+    else:
+        rc = ref().ref_mc_real_codes(arch, int(high_dyn), _p(sig), n, _p(code), len(code), _p(shifts), len(shifts), f(rem_carr), f(phase_step),
+                                     f(phase_rate), f(rem_code), f(code_step), f(code_rate), _p(out))
+    assert rc == 0
+    return out
+
+
+def mc_complex_codes(sig, code, shifts, rem_carr, phase_step, rem_code, code_step, impl="orc", arch=0):
+    sig = np.ascontiguousarray(sig, dtype=np.complex64)
+    code = np.ascontiguousarray(code, dtype=np.complex64)
+    shifts = np.ascontiguousarray(shifts, dtype=np.float32)
+    out = np.zeros(len(shifts), dtype=np.complex64)
+    f = C.c_float
+    if impl == "orc":
+        rc = orc().orc_mc_complex_codes(_p(sig), len(sig), _p(code), len(code), _p(shifts), len(shifts), f(rem_carr), f(phase_step), f(rem_code), f(code_step), _p(out))
+    else:
+        rc = ref().ref_mc_complex_codes(arch, _p(sig), len(sig), _p(code), len(code), _p(shifts), len(shifts), f(rem_carr), f(phase_step), f(rem_code), f(code_step), _p(out))
+    assert rc == 0
+    return out
+
+
+def mc_real_codes_f64(sig, code, shifts, rem_carr, phase_step, rem_code, code_step, mimic_inc=False):
+    sig = np.ascontiguousarray(sig, dtype=np.complex64)
+    code = np.ascontiguousarray(code, dtype=np.float32)
+    shifts = np.ascontiguousarray(shifts, dtype=np.float32)
+    out = np.zeros(len(shifts), dtype=np.complex128)
+    f = C.c_float
+    rc = orc().orc_mc_real_codes_f64(_p(sig), len(sig), _p(code), len(code), _p(shifts), len(shifts), f(rem_carr), f(phase_step), f(rem_code),
+                                     f(code_step), int(mimic_inc), _p(out, f64p))
+    assert rc == 0
+    return out
+
+
+def mc_batch(ring, offsets, lens, codes, shifts, rem_carr, phase_step, rem_code, code_step, nthreads=0):
+    """Open-loop batch: channel c correlates ring[offsets[c] : offsets[c]+lens[c]] (scalar fp32 restatement, OpenMP over channels)."""
+    ring = np.ascontiguousarray(ring, dtype=np.complex64)
+    nch, L = codes.shape
+    ntaps = shifts.shape[1]
+    offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+    lens = np.ascontiguousarray(lens, dtype=np.int32)
+    codes = np.ascontiguousarray(codes, dtype=np.float32)
+    shifts = np.ascontiguousarray(shifts, dtype=np.float32)
+    a = [np.ascontiguousarray(x, dtype=np.float32) for x in (rem_carr, phase_step, rem_code, code_step)]
+    out = np.zeros((nch, ntaps), dtype=np.complex64)
+    rc = orc().orc_mc_batch(_p(ring), C.c_int64(len(ring)), nch, ntaps, _p(offsets, i64p), _p(lens, i32p), _p(codes), L, _p(shifts),
+                            _p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), _p(out), nthreads)
+    assert rc == 0
+    return out
+
+
+def resampler_index(rem, step, shifts, L, n):
+    shifts = np.ascontiguousarray(shifts, dtype=np.float32)
+    idx = np.zeros((len(shifts), n), dtype=np.int32)
+    orc().orc_resampler_index(_p(idx, i32p), C.c_float(rem), C.c_float(step), _p(shifts), L, len(shifts), n)
+    return idx
+
+
+# ------------------------------------------------------------------ codes
+def gps_l1_ca_code(prn, chip_shift=0, impl="orc"):
+    out = np.zeros(1023, dtype=np.float32)
+    if impl == "orc":
+        orc().orc_gps_l1_ca_code_gen_float(_p(out), prn, chip_shift)
+    else:
+        ref().ref_gps_l1_ca_code_gen_float(_p(out), prn, chip_shift)
+    return out
+
+
+def gps_l1_ca_code_sampled(prn, fs, n, chip_shift=0, impl="orc"):
+    out = np.zeros(n, dtype=np.complex64)
+    if impl == "orc":
+        orc().orc_gps_l1_ca_code_gen_complex_sampled(_p(out), n, prn, int(fs), chip_shift)
+    else:
+        ref().ref_gps_l1_ca_code_gen_complex_sampled(_p(out), n, prn, int(fs), chip_shift)
+    return out
+
+
+# ------------------------------------------------------------------ FFT / acquisition
+def fft_c32(x, inverse=False):
+    x = np.ascontiguousarray(x, dtype=np.complex64)
+    out = np.zeros_like(x)
+    rc = orc().orc_fft_c32(_p(x), _p(out), len(x), int(inverse))
+    assert rc == 0
+    return out
+
+
+def fft_c64(x, inverse=False):
+    x = np.ascontiguousarray(x, dtype=np.complex128)
+    out = np.zeros_like(x)
+    rc = orc().orc_fft_c64(_p(x, f64p), _p(out, f64p), len(x), int(inverse))
+    assert rc == 0
+    return out
+
+
+def acq_conf(fs, consumed, fft_size, doppler_max, doppler_step, samples_per_code, samples_per_chip, bit_transition=False, use_cfar=True,
+             doppler_center=0, max_dwells=1, fft_f64=False):
+    import math
+    c = AcqConf()
+    c.fft_size, c.consumed = fft_size, consumed
+    c.num_doppler_bins = int(math.ceil(2.0 * doppler_max / doppler_step))
+    c.bit_transition, c.use_cfar, c.samples_per_chip = int(bit_transition), int(use_cfar), samples_per_chip
+    c.doppler_max, c.doppler_step, c.doppler_center, c.max_dwells = doppler_max, doppler_step, doppler_center, max_dwells
+    c.samples_per_code, c.fs_in, c.fft_f64, c.sincos_arch = samples_per_code, float(fs), int(fft_f64), 0
+    return c
+
+
+def acq_neff(conf):
+    return orc().orc_acq_neff(C.byref(conf))
+
+
+def acq_set_local_code(conf, code):
+    code = np.ascontiguousarray(code, dtype=np.complex64)
+    out = np.zeros(conf.fft_size, dtype=np.complex64)
+    rc = orc().orc_acq_set_local_code(C.byref(conf), _p(code), _p(out))
+    assert rc == 0
+    return out
+
+
+def acq_dwell(conf, sig, fft_codes, grid=None, dwell_index=0, nthreads=0):
+    sig = np.ascontiguousarray(sig, dtype=np.complex64)
+    assert len(sig) >= conf.consumed
+    if grid is None:
+        grid = np.zeros((conf.num_doppler_bins, acq_neff(conf)), dtype=np.float32)
+    rc = orc().orc_acq_dwell(C.byref(conf), _p(sig), _p(fft_codes), _p(grid), dwell_index, nthreads)
+    assert rc == 0
+    return grid
+
+
+def acq_statistic(conf, grid, num_dwells=1):
+    r = AcqResult()
+    rc = orc().orc_acq_statistic(C.byref(conf), _p(grid), num_dwells, C.byref(r))
+    assert rc == 0
+    return r
+
+
+def acq_threshold(conf, pfa):
+    return float(orc().orc_acq_threshold(C.byref(conf), C.c_float(pfa)))
+
+
+def acq_wipeoff(n, freq, fs):
+    out = np.zeros(n, dtype=np.complex64)
+    orc().orc_acq_wipeoff(_p(out), n, C.c_float(freq), C.c_double(fs))
+    return out
