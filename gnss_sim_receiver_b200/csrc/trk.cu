@@ -1,0 +1,235 @@
+// Tracking multicorrelator engine: C ABI (include/gnss_b200.h) over trk_kernel.cuh.
+#include "trk_kernel.cuh"
+#include <algorithm>
+#include <cmath>
+#include <complex>
+#include <cstring>
+#include <new>
+#include <vector>
+
+using namespace gb200;
+
+struct gb200_trk
+{
+    gb200_trk_config cfg{};
+    cudaStream_t stream{};
+    cudaEvent_t ev0{}, ev1{};
+    int elem_bytes{8};
+    // IQ ring: capacity + max_block samples; the first max_block samples are mirrored behind the end so that every
+    // window of up to max_block samples is contiguous
+    char* d_ring{nullptr};
+    uint64_t head{0};  // absolute index one past the newest sample
+    // code tables, one slot of max_code_len float2 per channel (real tables use the first half)
+    float* d_codes{nullptr};
+    std::vector<int> code_len;
+    std::vector<char> code_cplx;
+    // command staging
+    TrkDevCmd* h_cmds{nullptr};  // pinned
+    TrkDevCmd* d_cmds{nullptr};
+    float* d_out{nullptr};
+    float* h_out{nullptr};  // pinned
+    float* d_partials{nullptr};
+    unsigned* d_counters{nullptr};
+    size_t partial_ctas{0};
+    // last enqueued launch (for collect / replay)
+    int last_n{0}, last_T{0}, last_chunks{0}, last_cplx{0};
+    size_t last_smem{0};
+    int sm_count{148};
+    int max_smem{0};
+};
+
+namespace
+{
+constexpr double TWO_PI = 6.283185307179586476925286766559;
+
+// fraction of a turn in [0,1) -> 64-bit fixed point
+inline unsigned long long turns_to_fix(double turns)
+{
+    double f = turns - std::floor(turns);
+    if (f >= 1.0) f = 0.0;
+    return (unsigned long long)std::ldexp(f, 64 - 11) << 11;  // 53 significant bits, shifted to the top
+}
+
+template <int T, int IQ, bool CPLX>
+cudaError_t launch_one(gb200_trk* h, int n_cmds, int n_chunks, size_t smem)
+{
+    if (smem > 48 * 1024)
+        {
+            cudaError_t e = cudaFuncSetAttribute(trk_correlate_kernel<T, IQ, CPLX>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem);
+            if (e != cudaSuccess) return e;
+        }
+    dim3 grid(n_chunks, n_cmds);
+    trk_correlate_kernel<T, IQ, CPLX><<<grid, TRK_THREADS, smem, h->stream>>>(h->d_cmds, n_chunks, h->d_partials, h->d_counters, h->d_out);
+    count_launch();
+    return cudaGetLastError();
+}
+
+template <int IQ, bool CPLX>
+cudaError_t launch_T(gb200_trk* h, int T, int n_cmds, int n_chunks, size_t smem)
+{
+    switch (T)
+        {
+        case 1: return launch_one<1, IQ, CPLX>(h, n_cmds, n_chunks, smem);
+        case 2: return launch_one<2, IQ, CPLX>(h, n_cmds, n_chunks, smem);
+        case 3: return launch_one<3, IQ, CPLX>(h, n_cmds, n_chunks, smem);
+        case 5: return launch_one<5, IQ, CPLX>(h, n_cmds, n_chunks, smem);
+        case 8: return launch_one<8, IQ, CPLX>(h, n_cmds, n_chunks, smem);
+        case 11: return launch_one<11, IQ, CPLX>(h, n_cmds, n_chunks, smem);
+        default: return launch_one<16, IQ, CPLX>(h, n_cmds, n_chunks, smem);
+        }
+}
+
+int padded_taps(int t)
+{
+    static const int sizes[] = {1, 2, 3, 5, 8, 11, 16};
+    for (int s : sizes)
+        if (t <= s) return s;
+    return 16;
+}
+
+cudaError_t launch(gb200_trk* h)
+{
+    const int T = h->last_T, n = h->last_n, ch = h->last_chunks;
+    const size_t sm = h->last_smem;
+    if (h->last_cplx)
+        {
+            switch (h->cfg.iq_dtype)
+                {
+                case GB200_IQ_CF32: return launch_T<GB200_IQ_CF32, true>(h, T, n, ch, sm);
+                case GB200_IQ_CS16: return launch_T<GB200_IQ_CS16, true>(h, T, n, ch, sm);
+                default: return launch_T<GB200_IQ_CS8, true>(h, T, n, ch, sm);
+                }
+        }
+    switch (h->cfg.iq_dtype)
+        {
+        case GB200_IQ_CF32: return launch_T<GB200_IQ_CF32, false>(h, T, n, ch, sm);
+        case GB200_IQ_CS16: return launch_T<GB200_IQ_CS16, false>(h, T, n, ch, sm);
+        default: return launch_T<GB200_IQ_CS8, false>(h, T, n, ch, sm);
+        }
+}
+}  // namespace
+
+extern "C" {
+
+int gb200_trk_create(const gb200_trk_config* cfg, gb200_trk** out)
+{
+    if (!cfg || !out) return set_error(GB200_EINVAL, "null argument");
+    *out = nullptr;
+    if (cfg->max_channels <= 0 || cfg->max_code_len <= 0 || cfg->max_block <= 0 || cfg->max_cmds <= 0)
+        return set_error(GB200_EINVAL, "max_channels, max_code_len, max_block and max_cmds must be positive");
+    if (cfg->iq_dtype < GB200_IQ_CF32 || cfg->iq_dtype > GB200_IQ_CS8) return set_error(GB200_EINVAL, "unknown iq_dtype %d", cfg->iq_dtype);
+    if (cfg->ring_samples < 2LL * cfg->max_block) return set_error(GB200_EINVAL, "ring_samples must be >= 2*max_block");
+    if (cfg->max_block > (1 << 22)) return set_error(GB200_EINVAL, "max_block above 2^22 samples is not supported");
+    int rc = select_device(cfg->device);
+    if (rc) return rc;
+    gb200_trk* h = new (std::nothrow) gb200_trk;
+    if (!h) return set_error(GB200_ENOMEM, "out of host memory");
+    h->cfg = *cfg;
+    h->elem_bytes = cfg->iq_dtype == GB200_IQ_CF32 ? 8 : cfg->iq_dtype == GB200_IQ_CS16 ? 4 : 2;
+    cudaDeviceProp p;
+    GB_CUDA(cudaGetDeviceProperties(&p, cfg->device));
+    h->sm_count = p.multiProcessorCount;
+    h->max_smem = (int)p.sharedMemPerBlockOptin - 2048;
+    GB_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    GB_CUDA(cudaEventCreate(&h->ev0));
+    GB_CUDA(cudaEventCreate(&h->ev1));
+    GB_CUDA(cudaMalloc(&h->d_ring, (size_t)(cfg->ring_samples + cfg->max_block) * h->elem_bytes));
+    GB_CUDA(cudaMemsetAsync(h->d_ring, 0, (size_t)(cfg->ring_samples + cfg->max_block) * h->elem_bytes, h->stream));
+    GB_CUDA(cudaMalloc(&h->d_codes, (size_t)cfg->max_channels * cfg->max_code_len * sizeof(float2)));
+    h->code_len.assign(cfg->max_channels, 0);
+    h->code_cplx.assign(cfg->max_channels, 0);
+    GB_CUDA(cudaMallocHost(&h->h_cmds, (size_t)cfg->max_cmds * sizeof(TrkDevCmd)));
+    GB_CUDA(cudaMalloc(&h->d_cmds, (size_t)cfg->max_cmds * sizeof(TrkDevCmd)));
+    GB_CUDA(cudaMalloc(&h->d_out, (size_t)cfg->max_cmds * 2 * TRK_OUT_STRIDE * sizeof(float)));
+    GB_CUDA(cudaMallocHost(&h->h_out, (size_t)cfg->max_cmds * 2 * TRK_OUT_STRIDE * sizeof(float)));
+    const size_t min_chunks = (size_t)(cfg->max_block + 16383) / 16384 + 1;
+    h->partial_ctas = std::max<size_t>(16 * (size_t)h->sm_count, (size_t)cfg->max_cmds * min_chunks);
+    GB_CUDA(cudaMalloc(&h->d_partials, h->partial_ctas * 2 * TRK_OUT_STRIDE * sizeof(float)));
+    GB_CUDA(cudaMalloc(&h->d_counters, (size_t)cfg->max_cmds * sizeof(unsigned)));
+    GB_CUDA(cudaMemsetAsync(h->d_counters, 0, (size_t)cfg->max_cmds * sizeof(unsigned), h->stream));
+    GB_CUDA(cudaStreamSynchronize(h->stream));
+    *out = h;
+    return GB200_OK;
+}
+
+int gb200_trk_destroy(gb200_trk* h)
+{
+    if (!h) return GB200_OK;
+    cudaSetDevice(h->cfg.device);
+    cudaStreamSynchronize(h->stream);
+    cudaFree(h->d_ring);
+    cudaFree(h->d_codes);
+    cudaFreeHost(h->h_cmds);
+    cudaFree(h->d_cmds);
+    cudaFree(h->d_out);
+    cudaFreeHost(h->h_out);
+    cudaFree(h->d_partials);
+    cudaFree(h->d_counters);
+    cudaEventDestroy(h->ev0);
+    cudaEventDestroy(h->ev1);
+    cudaStreamDestroy(h->stream);
+    delete h;
+    return GB200_OK;
+}
+
+static int set_code_impl(gb200_trk* h, int ch, const void* code, int code_len, bool cplx)
+{
+    if (!h || !code) return set_error(GB200_EINVAL, "null argument");
+    if (ch < 0 || ch >= h->cfg.max_channels) return set_error(GB200_EINVAL, "channel %d out of range", ch);
+    if (code_len <= 0 || code_len > h->cfg.max_code_len) return set_error(GB200_EINVAL, "code_len %d outside 1..%d", code_len, h->cfg.max_code_len);
+    GB_CUDA(cudaSetDevice(h->cfg.device));
+    float* dst = h->d_codes + (size_t)ch * h->cfg.max_code_len * 2;
+    GB_CUDA(cudaMemcpyAsync(dst, code, (size_t)code_len * (cplx ? sizeof(float2) : sizeof(float)), cudaMemcpyHostToDevice, h->stream));
+    GB_CUDA(cudaStreamSynchronize(h->stream));  // the caller's buffer may be reused on return
+    h->code_len[ch] = code_len;
+    h->code_cplx[ch] = cplx;
+    return GB200_OK;
+}
+
+int gb200_trk_set_code(gb200_trk* h, int ch, const float* code, int code_len) { return set_code_impl(h, ch, code, code_len, false); }
+int gb200_trk_set_code_complex(gb200_trk* h, int ch, const gb200_cf32* code, int code_len) { return set_code_impl(h, ch, code, code_len, true); }
+
+static int push_impl(gb200_trk* h, const void* src, int64_t n, uint64_t* first_index, cudaMemcpyKind kind)
+{
+    if (!h || (!src && n > 0)) return set_error(GB200_EINVAL, "null argument");
+    if (n < 0 || n > h->cfg.ring_samples) return set_error(GB200_EINVAL, "push of %lld samples exceeds the ring (%lld)", (long long)n, (long long)h->cfg.ring_samples);
+    GB_CUDA(cudaSetDevice(h->cfg.device));
+    const int64_t cap = h->cfg.ring_samples, mb = h->cfg.max_block;
+    const int eb = h->elem_bytes;
+    if (first_index) *first_index = h->head;
+    int64_t done = 0;
+    while (done < n)
+        {
+            const int64_t pos = (int64_t)((h->head + (uint64_t)done) % (uint64_t)cap);
+            const int64_t run = std::min<int64_t>(n - done, cap - pos);
+            const char* s = static_cast<const char*>(src) + done * eb;
+            GB_CUDA(cudaMemcpyAsync(h->d_ring + pos * eb, s, (size_t)run * eb, kind, h->stream));
+            if (pos < mb)  // mirror the part that falls in [0, max_block) behind the end of the ring
+                {
+                    const int64_t m = std::min<int64_t>(run, mb - pos);
+                    GB_CUDA(cudaMemcpyAsync(h->d_ring + (cap + pos) * eb, s, (size_t)m * eb, kind, h->stream));
+                }
+            done += run;
+        }
+    h->head += (uint64_t)n;
+    return GB200_OK;
+}
+
+int gb200_trk_push_iq(gb200_trk* h, const void* iq_host, int64_t n_samples, uint64_t* first_index)
+{
+    int rc = push_impl(h, iq_host, n_samples, first_index, cudaMemcpyHostToDevice);
+    if (rc) return rc;
+    GB_CUDA(cudaStreamSynchronize(h->stream));  // pageable or pinned: the host buffer is free on return
+    return GB200_OK;
+}
+
+int gb200_trk_push_iq_device(gb200_trk* h, const void* iq_dev, int64_t n_samples, uint64_t* first_index)
+{
+    return push_impl(h, iq_dev, n_samples, first_index, cudaMemcpyDeviceToDevice);
+}
+
+uint64_t gb200_trk_head(const gb200_trk* h) { return h ? h->head : 0; }
+
+}  // extern "C"
+
+#include "trk_submit.inc"

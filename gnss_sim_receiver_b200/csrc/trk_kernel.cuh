@@ -1,0 +1,217 @@
+// Tracking multicorrelator kernel (K1) for sm_100a.
+//
+// One launch evaluates, for every command (= one channel's code period), what the reference does with
+//   volk_gnsssdr_32f_xn_resampler_32f_xn            (kernels/volk_gnsssdr/volk_gnsssdr_32f_xn_resampler_32f_xn.h:63-80)
+//   volk_gnsssdr_32fc_32f_rotator_dot_prod_32fc_xn  (kernels/volk_gnsssdr/volk_gnsssdr_32fc_32f_rotator_dot_prod_32fc_xn.h:66-98)
+// called from Cpu_Multicorrelator_Real_Codes::Carrier_wipeoff_multicorrelator_resampler
+// (src/algorithms/tracking/libs/cpu_multicorrelator_real_codes.cc:103-126), without materialising the T resampled
+// replicas: the chip index of every (tap, sample) is computed on the fly with the reference's exact fp32 law and
+// looked up in a shared-memory window of the code table.
+//
+// grid = (n_chunks, n_cmds); CTA (x, y) correlates samples [x*chunk_len, (x+1)*chunk_len) of command y for all taps.
+// Partial sums of the chunks are combined in fixed order by the last CTA of the command to finish (deterministic).
+#pragma once
+#include "common.cuh"
+
+namespace gb200
+{
+constexpr int TRK_THREADS = 128;
+constexpr int TRK_RESEED = 16;  // exact phasor re-seed period (in per-thread samples)
+constexpr int TRK_OUT_STRIDE = GB200_MAX_TAPS;
+
+// host-preprocessed command, one per Carrier_wipeoff_multicorrelator_resampler call
+struct TrkDevCmd
+{
+    unsigned long long u0;  // carrier multiplier exp(+j*2*pi*(u0 + n*du)/2^64): 64-bit fixed-point turns
+    unsigned long long du;
+    const void* iq;         // first sample of the window in the device ring
+    const void* code;       // channel's code table (float or float2), L entries
+    int n;                  // samples
+    int ntaps;
+    int L;
+    int flags;
+    float rem_code;
+    float code_step;
+    float code_rate;
+    float shift_min, shift_max;
+    float shifts[GB200_MAX_TAPS];
+    int pad_;
+};
+
+// reference chip index BEFORE the modulo: floor(step*(float)n + shift - rem), every operation rounded to fp32
+// separately (no FMA contraction), volk_gnsssdr_32f_xn_resampler_32f_xn.h:73.
+__device__ __forceinline__ int trk_raw_index(float step, float nf, float shift, float rem)
+{
+    return (int)floorf(__fsub_rn(__fadd_rn(__fmul_rn(step, nf), shift), rem));
+}
+
+__device__ __forceinline__ int math_mod(int a, int L)
+{
+    int r = a % L;
+    return r < 0 ? r + L : r;
+}
+
+template <int IQ>
+__device__ __forceinline__ float2 trk_load_iq(const void* base, int s)
+{
+    if (IQ == GB200_IQ_CF32) return __ldg(reinterpret_cast<const float2*>(base) + s);
+    if (IQ == GB200_IQ_CS16)
+        {
+            const short2 v = __ldg(reinterpret_cast<const short2*>(base) + s);
+            return make_float2((float)v.x, (float)v.y);
+        }
+    const char2 v = __ldg(reinterpret_cast<const char2*>(base) + s);
+    return make_float2((float)v.x, (float)v.y);
+}
+
+// phasor of the 64-bit fixed-point phase (turns): top 32 bits -> signed half-turn fraction -> sincospif
+__device__ __forceinline__ float2 trk_phasor(unsigned long long u)
+{
+    const int a = (int)(u >> 32);
+    float s, c;
+    sincospif((float)a * 4.656612873077393e-10f, &s, &c);  // a * 2^-31 half-turns
+    return make_float2(c, s);
+}
+
+// T = taps evaluated (commands with fewer taps are padded by the host with shift copies), CPLX = complex code table
+template <int T, int IQ, bool CPLX>
+__global__ void __launch_bounds__(TRK_THREADS) trk_correlate_kernel(const TrkDevCmd* __restrict__ cmds, int n_chunks,
+    float* __restrict__ partials, unsigned* __restrict__ counters, float* __restrict__ out)
+{
+    extern __shared__ __align__(16) float s_tab[];
+    __shared__ float s_red[TRK_THREADS / 32][2 * T];
+    __shared__ int s_last;
+
+    const TrkDevCmd& c = cmds[blockIdx.y];
+    const int tid = threadIdx.x;
+    const int n = c.n;
+    const int chunk_len = (((n + n_chunks - 1) / n_chunks) + TRK_THREADS - 1) & ~(TRK_THREADS - 1);
+    const int n0 = blockIdx.x * chunk_len;
+    const int n1 = min(n, n0 + chunk_len);
+
+    float acc_re[T], acc_im[T];
+#pragma unroll
+    for (int t = 0; t < T; t++) acc_re[t] = acc_im[t] = 0.0f;
+
+    if (n0 < n1)
+        {
+            const float step = c.code_step, rem = c.rem_code;
+            const int L = c.L;
+            // the index is monotone in n and in the shift: the chunk touches raw indices [idx_lo, idx_hi]
+            const int idx_lo = trk_raw_index(step, (float)n0, c.shift_min, rem);
+            const int idx_hi = trk_raw_index(step, (float)(n1 - 1), c.shift_max, rem);
+            const int span = idx_hi - idx_lo + 1;
+            {
+                int k = math_mod(idx_lo + tid, L);
+                const int adv = TRK_THREADS % L;
+                for (int j = tid; j < span; j += TRK_THREADS)
+                    {
+                        if (CPLX)
+                            reinterpret_cast<float2*>(s_tab)[j] = __ldg(reinterpret_cast<const float2*>(c.code) + k);
+                        else
+                            s_tab[j] = __ldg(reinterpret_cast<const float*>(c.code) + k);
+                        k += adv;
+                        if (k >= L) k -= L;
+                    }
+            }
+            __syncthreads();
+
+            float sh[T];
+#pragma unroll
+            for (int t = 0; t < T; t++) sh[t] = c.shifts[t];
+            // floor(x) for |x| < 2^22 as the low mantissa bits of RD(x + 1.5*2^23)
+            const float MAGIC = 12582912.0f;
+            const int bias = 0x4B400000 + idx_lo;
+            const float2 stp = trk_phasor(c.du * (unsigned long long)TRK_THREADS);
+            float nf = (float)(n0 + tid);
+            for (int base = n0 + tid; base < n1; base += TRK_THREADS * TRK_RESEED)
+                {
+                    float2 ph = trk_phasor(c.u0 + c.du * (unsigned long long)base);
+#pragma unroll 4
+                    for (int k = 0; k < TRK_RESEED; k++)
+                        {
+                            const int s = base + k * TRK_THREADS;
+                            if (s >= n1) break;
+                            const float2 x = trk_load_iq<IQ>(c.iq, s);
+                            const float wr = x.x * ph.x - x.y * ph.y;
+                            const float wi = x.x * ph.y + x.y * ph.x;
+                            const float pr = ph.x * stp.x - ph.y * stp.y;
+                            const float pi = ph.x * stp.y + ph.y * stp.x;
+                            ph.x = pr;
+                            ph.y = pi;
+                            const float a = __fmul_rn(step, nf);
+                            nf += (float)TRK_THREADS;
+#pragma unroll
+                            for (int t = 0; t < T; t++)
+                                {
+                                    const float xi = __fsub_rn(__fadd_rn(a, sh[t]), rem);
+                                    const int j = __float_as_int(__fadd_rd(xi, MAGIC)) - bias;
+                                    if (CPLX)
+                                        {
+                                            const float2 cc = reinterpret_cast<const float2*>(s_tab)[j];
+                                            acc_re[t] += wr * cc.x - wi * cc.y;
+                                            acc_im[t] += wr * cc.y + wi * cc.x;
+                                        }
+                                    else
+                                        {
+                                            const float cc = s_tab[j];
+                                            acc_re[t] += wr * cc;
+                                            acc_im[t] += wi * cc;
+                                        }
+                                }
+                        }
+                }
+        }
+
+    // block reduce: warp shuffle, then across the 4 warps through shared memory
+#pragma unroll
+    for (int t = 0; t < T; t++)
+        {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                {
+                    acc_re[t] += __shfl_xor_sync(0xffffffffu, acc_re[t], o);
+                    acc_im[t] += __shfl_xor_sync(0xffffffffu, acc_im[t], o);
+                }
+        }
+    if ((tid & 31) == 0)
+        {
+#pragma unroll
+            for (int t = 0; t < T; t++)
+                {
+                    s_red[tid >> 5][2 * t] = acc_re[t];
+                    s_red[tid >> 5][2 * t + 1] = acc_im[t];
+                }
+        }
+    __syncthreads();
+    float v = 0.0f;
+    if (tid < 2 * T)
+        {
+#pragma unroll
+            for (int w = 0; w < TRK_THREADS / 32; w++) v += s_red[w][tid];
+        }
+    float* o = out + (size_t)blockIdx.y * (2 * TRK_OUT_STRIDE);
+    if (n_chunks == 1)
+        {
+            if (tid < 2 * T) o[tid] = v;
+            return;
+        }
+    float* p = partials + ((size_t)blockIdx.y * n_chunks) * (2 * TRK_OUT_STRIDE);
+    if (tid < 2 * T) p[(size_t)blockIdx.x * (2 * TRK_OUT_STRIDE) + tid] = v;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = (atomicAdd(&counters[blockIdx.y], 1u) == (unsigned)(n_chunks - 1));
+    __syncthreads();
+    if (s_last)
+        {
+            __threadfence();
+            if (tid < 2 * T)
+                {
+                    float sum = 0.0f;
+                    for (int k = 0; k < n_chunks; k++) sum += __ldcg(p + (size_t)k * (2 * TRK_OUT_STRIDE) + tid);
+                    o[tid] = sum;
+                }
+            if (tid == 0) counters[blockIdx.y] = 0;
+        }
+}
+}  // namespace gb200

@@ -1,0 +1,201 @@
+/*
+ * gnss_b200.h — C ABI of the B200-native (sm_100a) GNSS hot paths.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.
+ * Every entry point names the reference interface it replaces (paths relative
+ * to the root of ShingoNishimoto/gnss_sim_receiver).  Host code (the C++
+ * adapters under gnss_sim_receiver_b200/host/, or GNSS-SDR itself through the
+ * patch in INTEGRATION.md) calls only these functions.
+ *
+ * Conventions
+ *   - every function returns 0 (GB200_OK) or a negative GB200_E* code;
+ *     gb200_last_error() gives the message of the last failure on this thread;
+ *   - there is NO CPU fallback: without a CUDA device every *_create fails
+ *     with GB200_ENODEVICE;
+ *   - complex samples are interleaved (re, im);
+ *   - all host pointers may be pageable; pinned memory only makes copies faster.
+ */
+#ifndef GNSS_B200_H
+#define GNSS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GB200_OK 0
+#define GB200_EINVAL (-1)    /* bad argument */
+#define GB200_ENODEVICE (-2) /* no usable CUDA device / wrong architecture */
+#define GB200_ECUDA (-3)     /* CUDA runtime error (message in gb200_last_error) */
+#define GB200_ENOMEM (-4)
+#define GB200_ESTATE (-5)    /* call out of order (e.g. correlate before set_code) */
+#define GB200_ERANGE (-6)    /* sample window not (or no longer) in the IQ ring */
+
+#define GB200_MAX_TAPS 16
+
+/* IQ sample types accepted on the device ring / acquisition input.
+ * Replaces the item types of the reference's blocks: gr_complex, cshort
+ * (lv_16sc_t, converted by volk_gnsssdr_16ic_convert_32fc at
+ * pcps_acquisition.cc:610) and cbyte (lv_8sc_t). */
+#define GB200_IQ_CF32 0 /* 2 x float   */
+#define GB200_IQ_CS16 1 /* 2 x int16_t */
+#define GB200_IQ_CS8 2  /* 2 x int8_t  */
+
+typedef struct
+{
+    float re, im;
+} gb200_cf32;
+
+const char* gb200_last_error(void);
+/* number of CUDA kernels this library has launched in this process (all handles) */
+uint64_t gb200_launch_count(void);
+/* number of visible CUDA devices (0 when there is none; never fails) */
+int gb200_device_count(void);
+const char* gb200_version(void);
+
+/* ======================================================================
+ * Tracking multicorrelator engine
+ *
+ * Replaces, for ALL channels resident on one GPU at once,
+ *   Cpu_Multicorrelator_Real_Codes   src/algorithms/tracking/libs/cpu_multicorrelator_real_codes.{h:37-61,cc:36-160}
+ *   Cpu_Multicorrelator              src/algorithms/tracking/libs/cpu_multicorrelator.{h,cc:73-100}
+ *   cuda_multicorrelator (legacy)    src/algorithms/tracking/libs/cuda_multicorrelator.{h:111-161,cu:32-346}
+ * i.e. volk_gnsssdr_32f_xn_resampler_32f_xn + volk_gnsssdr_32fc_32f_rotator_dot_prod_32fc_xn
+ * (and the 32fc_x2 complex-code sibling).  One engine owns a device-resident IQ
+ * ring shared by every channel; one gb200_trk_correlate call evaluates one
+ * Carrier_wipeoff_multicorrelator_resampler per command, all in one launch.
+ * ====================================================================== */
+typedef struct gb200_trk gb200_trk;
+
+typedef struct
+{
+    int32_t device;       /* CUDA ordinal */
+    int32_t max_channels; /* channels addressable by gb200_trk_set_code / cmd.ch */
+    int32_t max_code_len; /* longest code table (entries), e.g. 1023, 8184, 10230 */
+    int32_t iq_dtype;     /* GB200_IQ_* of the ring */
+    int64_t ring_samples; /* ring capacity in complex samples (>= 2 * max_block) */
+    int32_t max_block;    /* longest correlation window (samples); init()'s max_signal_length_samples */
+    int32_t max_cmds;     /* most commands in one correlate call */
+} gb200_trk_config;
+
+/* One Carrier_wipeoff_multicorrelator_resampler call
+ * (cpu_multicorrelator_real_codes.cc:103-126): same argument meaning, all float. */
+typedef struct
+{
+    int32_t ch;             /* channel whose code table is used */
+    int32_t n_samples;      /* signal_length_samples */
+    int32_t n_taps;         /* d_n_correlators, 1..GB200_MAX_TAPS */
+    int32_t flags;          /* GB200_TRK_HIGH_DYN: use the high-dynamics resampler/rotator pair */
+    uint64_t sample_offset; /* absolute index (since engine creation) of the window's first sample: d_sig_in */
+    float rem_carrier_phase_rad;
+    float phase_step_rad;
+    float phase_rate_step_rad; /* used only with GB200_TRK_HIGH_DYN */
+    float rem_code_phase_chips;
+    float code_phase_step_chips;
+    float code_phase_rate_step_chips; /* used only with GB200_TRK_HIGH_DYN */
+    float shifts_chips[GB200_MAX_TAPS]; /* d_shifts_chips, copied on every call (the caller may change them) */
+} gb200_trk_cmd;
+
+#define GB200_TRK_HIGH_DYN 1
+
+/* init() — cpu_multicorrelator_real_codes.cc:36-50 */
+int gb200_trk_create(const gb200_trk_config* cfg, gb200_trk** out);
+/* free() — cpu_multicorrelator_real_codes.cc:140-153 */
+int gb200_trk_destroy(gb200_trk* h);
+/* set_local_code_and_taps() code part — cpu_multicorrelator_real_codes.cc:53-63.
+ * The table is copied to the device (the reference borrows the pointer). */
+int gb200_trk_set_code(gb200_trk* h, int ch, const float* code, int code_len);
+/* Cpu_Multicorrelator::set_local_code_and_taps — cpu_multicorrelator.cc:48-58 (complex code table) */
+int gb200_trk_set_code_complex(gb200_trk* h, int ch, const gb200_cf32* code, int code_len);
+/* set_input_output_vectors() input part — cpu_multicorrelator_real_codes.cc:66-72.  Appends n_samples
+ * of cfg.iq_dtype to the ring (ONE host->device copy per GPU, shared by all channels);
+ * *first_index (may be NULL) receives the absolute index of the first appended sample. */
+int gb200_trk_push_iq(gb200_trk* h, const void* iq_host, int64_t n_samples, uint64_t* first_index);
+/* same, from a device pointer on cfg.device (device->device copy on the engine's stream) */
+int gb200_trk_push_iq_device(gb200_trk* h, const void* iq_dev, int64_t n_samples, uint64_t* first_index);
+/* absolute index one past the newest sample */
+uint64_t gb200_trk_head(const gb200_trk* h);
+
+/* Carrier_wipeoff_multicorrelator_resampler() for n_cmds commands:
+ * out[i * GB200_MAX_TAPS + t] = correlator output of command i, tap t (d_corr_out).
+ * Blocking: copies the commands in, launches, copies the results back. */
+int gb200_trk_correlate(gb200_trk* h, const gb200_trk_cmd* cmds, int n_cmds, gb200_cf32* out);
+/* Split form: enqueue (async copy-in + launch on the engine's stream) ... collect (copy-out + sync). */
+int gb200_trk_enqueue(gb200_trk* h, const gb200_trk_cmd* cmds, int n_cmds);
+int gb200_trk_collect(gb200_trk* h, gb200_cf32* out);
+/* Re-launch the most recently enqueued command set `iters` times with inputs and commands
+ * resident on the device; *ms_per_iter = CUDA-event time / iters on the engine's stream. */
+int gb200_trk_replay(gb200_trk* h, int iters, float* ms_per_iter);
+
+/* ======================================================================
+ * PCPS acquisition engine
+ *
+ * Replaces pcps_acquisition (src/algorithms/acquisition/gnuradio_blocks/pcps_acquisition.{h:92-290,cc:175-899})
+ * for all PRNs x Doppler bins of one signal at once:
+ *   set_local_code :175-208, update_grid_doppler_wipeoffs :232-245,295-302, acquisition_core :600-697,
+ *   max_to_input_power_statistic :496-528, first_vs_second_peak_statistic :531-597, calculate_threshold :884-899.
+ * The FFTs (FFTW through gr::fft in the reference) are hand-written mixed-radix kernels; no cuFFT.
+ * ====================================================================== */
+typedef struct gb200_acq gb200_acq;
+
+typedef struct
+{
+    int32_t device;
+    int32_t iq_dtype;         /* GB200_IQ_*: acq_parameters.it_size / item_type (acq_conf.cc:24-31) */
+    int32_t fft_size;         /* d_fft_size           pcps_acquisition.cc:84-93  (factors 2,3,5,7 only) */
+    int32_t consumed_samples; /* d_consumed_samples   pcps_acquisition.cc:84-91  (input zero-padded to fft_size, :612-619) */
+    int32_t bit_transition;   /* acq_parameters.bit_transition_flag */
+    int32_t use_cfar;         /* d_use_CFAR_algorithm_flag (pfa > 0), pcps_acquisition.cc:81 */
+    int32_t samples_per_chip; /* acq_conf.cc:110 */
+    int32_t max_dwells;       /* acq_parameters.max_dwells */
+    int32_t max_prns;         /* code spectra slots */
+    float samples_per_code;   /* acq_conf.cc:116-117 (float) */
+    double fs_in;             /* acq_parameters.fs_in */
+} gb200_acq_config;
+
+/* what acquisition_core leaves in Gnss_Synchro / the block members (pcps_acquisition.cc:505-527, 691-696) */
+typedef struct
+{
+    uint32_t indext;         /* code-phase index of the maximum, first index wins ties */
+    int32_t doppler_index;   /* Doppler bin of the maximum, first bin wins ties */
+    int32_t doppler_hz;      /* -doppler_max + doppler_center + doppler_step * doppler_index */
+    float peak;              /* grid maximum (d_mag) */
+    float input_power;       /* CFAR: sum(grid[opposite bin]) / N_eff / 2 / dwells;  2-peak: second peak */
+    float test_statistics;   /* d_test_statistics */
+    float acq_delay_samples; /* fmod((float)indext, samples_per_code) */
+    float acq_doppler_hz;
+} gb200_acq_result;
+
+int gb200_acq_create(const gb200_acq_config* cfg, gb200_acq** out);
+int gb200_acq_destroy(gb200_acq* h);
+/* set_local_code() for one slot — pcps_acquisition.cc:175-208: `code` holds the sampled local replica
+ * (consumed_samples complex values, or fft_size/2 with bit_transition); the device zero-pads, transforms
+ * and conjugates it. */
+int gb200_acq_set_local_code(gb200_acq* h, int slot, const gb200_cf32* code, int n_code);
+/* set_doppler_max/step/center + update_grid_doppler_wipeoffs — pcps_acquisition.cc:248-302 */
+int gb200_acq_set_doppler_grid(gb200_acq* h, int doppler_max, int doppler_step, int doppler_center);
+int gb200_acq_num_doppler_bins(const gb200_acq* h);
+int gb200_acq_neff(const gb200_acq* h);
+/* One dwell of acquisition_core for every slot in `slots` (NULL = 0..n_slots-1): `iq_host` holds
+ * consumed_samples samples of cfg.iq_dtype.  dwell_index 0 overwrites the magnitude grid, > 0 accumulates
+ * (pcps_acquisition.cc:657-665); `out[i]` is the statistic after this dwell for slots[i]. */
+int gb200_acq_run(gb200_acq* h, const void* iq_host, int dwell_index, const int32_t* slots, int n_slots, gb200_acq_result* out);
+/* same with the input already on the device */
+int gb200_acq_run_device(gb200_acq* h, const void* iq_dev, int dwell_index, const int32_t* slots, int n_slots, gb200_acq_result* out);
+/* Re-run the last gb200_acq_run_device sweep `iters` times, everything resident; event-timed. */
+int gb200_acq_replay(gb200_acq* h, int iters, float* ms_per_iter);
+/* calculate_threshold — pcps_acquisition.cc:884-899 */
+float gb200_acq_threshold(const gb200_acq* h, float pfa);
+/* d_magnitude_grid of one slot after the last run: bins x N_eff floats (dump support, pcps_acquisition.cc:393-493).
+ * Only available when the engine keeps a grid (max_dwells > 1 or keep_grid set through gb200_acq_keep_grid). */
+int gb200_acq_keep_grid(gb200_acq* h, int keep);
+int gb200_acq_read_grid(gb200_acq* h, int slot, float* grid_host);
+/* forward transform of one fft_size block through the engine's FFT (test hook: natural-order output) */
+int gb200_acq_fft(gb200_acq* h, const gb200_cf32* in_host, gb200_cf32* out_host, int inverse);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNSS_B200_H */
