@@ -1,0 +1,97 @@
+"""ctypes binding of the C ABI in include/gnss_b200.h (libgnss_b200.so, built in-tree by csrc/Makefile).
+
+Plumbing only: the structures mirror the header field by field.  There is no CPU fallback; a missing library
+raises ImportError with the build command, a missing GPU makes every *_create call fail with GB200_ENODEVICE.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgnss_b200.so")
+
+GB200_MAX_TAPS = 16
+IQ_CF32, IQ_CS16, IQ_CS8 = 0, 1, 2
+TRK_HIGH_DYN = 1
+
+
+class TrkConfig(C.Structure):
+    _fields_ = [("device", C.c_int32), ("max_channels", C.c_int32), ("max_code_len", C.c_int32), ("iq_dtype", C.c_int32),
+                ("ring_samples", C.c_int64), ("max_block", C.c_int32), ("max_cmds", C.c_int32)]
+
+
+class TrkCmd(C.Structure):
+    _fields_ = [("ch", C.c_int32), ("n_samples", C.c_int32), ("n_taps", C.c_int32), ("flags", C.c_int32),
+                ("sample_offset", C.c_uint64),
+                ("rem_carrier_phase_rad", C.c_float), ("phase_step_rad", C.c_float), ("phase_rate_step_rad", C.c_float),
+                ("rem_code_phase_chips", C.c_float), ("code_phase_step_chips", C.c_float), ("code_phase_rate_step_chips", C.c_float),
+                ("shifts_chips", C.c_float * GB200_MAX_TAPS)]
+
+
+class AcqConfig(C.Structure):
+    _fields_ = [("device", C.c_int32), ("iq_dtype", C.c_int32), ("fft_size", C.c_int32), ("consumed_samples", C.c_int32),
+                ("bit_transition", C.c_int32), ("use_cfar", C.c_int32), ("samples_per_chip", C.c_int32), ("max_dwells", C.c_int32),
+                ("max_prns", C.c_int32), ("samples_per_code", C.c_float), ("fs_in", C.c_double)]
+
+
+class AcqResult(C.Structure):
+    _fields_ = [("indext", C.c_uint32), ("doppler_index", C.c_int32), ("doppler_hz", C.c_int32), ("peak", C.c_float),
+                ("input_power", C.c_float), ("test_statistics", C.c_float), ("acq_delay_samples", C.c_float), ("acq_doppler_hz", C.c_float)]
+
+
+# every symbol include/gnss_b200.h declares: name -> (restype, argtypes)
+_vp = C.c_void_p
+SYMBOLS = {
+    "gb200_last_error": (C.c_char_p, []),
+    "gb200_launch_count": (C.c_uint64, []),
+    "gb200_device_count": (C.c_int, []),
+    "gb200_version": (C.c_char_p, []),
+    "gb200_trk_create": (C.c_int, [C.POINTER(TrkConfig), C.POINTER(_vp)]),
+    "gb200_trk_destroy": (C.c_int, [_vp]),
+    "gb200_trk_set_code": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "gb200_trk_set_code_complex": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "gb200_trk_push_iq": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_uint64)]),
+    "gb200_trk_push_iq_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_uint64)]),
+    "gb200_trk_head": (C.c_uint64, [_vp]),
+    "gb200_trk_correlate": (C.c_int, [_vp, _vp, C.c_int, _vp]),
+    "gb200_trk_enqueue": (C.c_int, [_vp, _vp, C.c_int]),
+    "gb200_trk_collect": (C.c_int, [_vp, _vp]),
+    "gb200_trk_replay": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
+    "gb200_acq_create": (C.c_int, [C.POINTER(AcqConfig), C.POINTER(_vp)]),
+    "gb200_acq_destroy": (C.c_int, [_vp]),
+    "gb200_acq_set_local_code": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
+    "gb200_acq_set_doppler_grid": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
+    "gb200_acq_num_doppler_bins": (C.c_int, [_vp]),
+    "gb200_acq_neff": (C.c_int, [_vp]),
+    "gb200_acq_run": (C.c_int, [_vp, _vp, C.c_int, _vp, C.c_int, _vp]),
+    "gb200_acq_run_device": (C.c_int, [_vp, _vp, C.c_int, _vp, C.c_int, _vp]),
+    "gb200_acq_replay": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
+    "gb200_acq_threshold": (C.c_float, [_vp, C.c_float]),
+    "gb200_acq_keep_grid": (C.c_int, [_vp, C.c_int]),
+    "gb200_acq_read_grid": (C.c_int, [_vp, C.c_int, _vp]),
+    "gb200_acq_fft": (C.c_int, [_vp, _vp, _vp, C.c_int]),
+}
+
+_LIB = None
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: build it with `make -C gnss_sim_receiver_b200/csrc` (python -c 'import __graft_entry__ as g; g.build()')")
+        _LIB = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            f = getattr(_LIB, name)  # AttributeError here = header/library mismatch, which must be loud
+            f.restype, f.argtypes = res, args
+    return _LIB
+
+
+class GB200Error(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"gb200 error {code}: {msg}")
+        self.code = code
+
+
+def check(rc):
+    if rc != 0:
+        raise GB200Error(rc, lib().gb200_last_error().decode(errors="replace"))

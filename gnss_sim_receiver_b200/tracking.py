@@ -1,0 +1,111 @@
+"""Python door onto the tracking multicorrelator engine (C ABI gb200_trk_*), used by tests/ and bench.py.
+
+The product host layer is the C++ under gnss_sim_receiver_b200/host/; this module only marshals numpy arrays
+into the C structures.  Argument names follow Cpu_Multicorrelator_Real_Codes
+(src/algorithms/tracking/libs/cpu_multicorrelator_real_codes.h:37-61 of the reference).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from ._capi import GB200_MAX_TAPS, IQ_CF32, IQ_CS16, IQ_CS8, TrkCmd, TrkConfig, check
+
+_IQ_NP = {IQ_CF32: (np.complex64, 8), IQ_CS16: (np.int16, 4), IQ_CS8: (np.int8, 2)}
+
+
+class TrackingEngine:
+    """All channels of one GPU: shared device IQ ring + per-channel code tables."""
+
+    def __init__(self, device=0, max_channels=64, max_code_len=10230, iq_dtype=IQ_CF32, ring_samples=1 << 20, max_block=1 << 17, max_cmds=None):
+        self._lib = _capi.lib()
+        self.cfg = TrkConfig(device, max_channels, max_code_len, iq_dtype, ring_samples, max_block, max_cmds or max_channels)
+        self._h = C.c_void_p()
+        check(self._lib.gb200_trk_create(C.byref(self.cfg), C.byref(self._h)))
+        self.iq_dtype = iq_dtype
+        self._cmds = None
+        self._n = 0
+
+    def close(self):
+        if self._h:
+            self._lib.gb200_trk_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # set_local_code_and_taps (code part)
+    def set_code(self, ch, code):
+        code = np.ascontiguousarray(code)
+        if np.iscomplexobj(code):
+            code = code.astype(np.complex64)
+            check(self._lib.gb200_trk_set_code_complex(self._h, ch, code.ctypes.data, len(code)))
+        else:
+            code = code.astype(np.float32)
+            check(self._lib.gb200_trk_set_code(self._h, ch, code.ctypes.data, len(code)))
+
+    # set_input_output_vectors (input part): append samples to the ring, returns the absolute index of the first one
+    def push_iq(self, iq):
+        np_t, eb = _IQ_NP[self.iq_dtype]
+        iq = np.ascontiguousarray(iq)
+        if self.iq_dtype == IQ_CF32:
+            iq = iq.astype(np.complex64, copy=False)
+            n = iq.size
+        else:
+            assert iq.dtype == np_t, f"ring holds interleaved {np_t.__name__} I,Q"
+            n = iq.size // 2
+        first = C.c_uint64()
+        check(self._lib.gb200_trk_push_iq(self._h, iq.ctypes.data, n, C.byref(first)))
+        return first.value
+
+    def push_iq_device(self, dev_ptr, n_samples):
+        first = C.c_uint64()
+        check(self._lib.gb200_trk_push_iq_device(self._h, C.c_void_p(dev_ptr), n_samples, C.byref(first)))
+        return first.value
+
+    @property
+    def head(self):
+        return self._lib.gb200_trk_head(self._h)
+
+    @staticmethod
+    def make_cmds(ch, sample_offset, n_samples, shifts, rem_carr, phase_step, rem_code, code_step, phase_rate=None, code_rate=None, flags=0):
+        """Arrays (one entry per command) -> ctypes array of gb200_trk_cmd.  shifts: (n_cmds, n_taps)."""
+        shifts = np.atleast_2d(np.asarray(shifts, dtype=np.float32))
+        n = len(ch)
+        arr = (TrkCmd * n)()
+        for i in range(n):
+            c = arr[i]
+            c.ch, c.n_samples, c.n_taps, c.flags = int(ch[i]), int(n_samples[i]), shifts.shape[1], int(flags)
+            c.sample_offset = int(sample_offset[i])
+            c.rem_carrier_phase_rad, c.phase_step_rad = float(rem_carr[i]), float(phase_step[i])
+            c.phase_rate_step_rad = 0.0 if phase_rate is None else float(phase_rate[i])
+            c.rem_code_phase_chips, c.code_phase_step_chips = float(rem_code[i]), float(code_step[i])
+            c.code_phase_rate_step_chips = 0.0 if code_rate is None else float(code_rate[i])
+            row = shifts[i if shifts.shape[0] > 1 else 0]
+            for t in range(shifts.shape[1]):
+                c.shifts_chips[t] = float(row[t])
+        return arr
+
+    # Carrier_wipeoff_multicorrelator_resampler for a batch of commands: (n_cmds, n_taps) complex64
+    def correlate(self, cmds):
+        n = len(cmds)
+        out = np.zeros((n, GB200_MAX_TAPS), dtype=np.complex64)
+        check(self._lib.gb200_trk_correlate(self._h, cmds, n, out.ctypes.data))
+        return out[:, : max(c.n_taps for c in cmds)]
+
+    def enqueue(self, cmds):
+        self._n = len(cmds)
+        check(self._lib.gb200_trk_enqueue(self._h, cmds, self._n))
+
+    def collect(self):
+        out = np.zeros((self._n, GB200_MAX_TAPS), dtype=np.complex64)
+        check(self._lib.gb200_trk_collect(self._h, out.ctypes.data))
+        return out
+
+    def replay(self, iters):
+        ms = C.c_float()
+        check(self._lib.gb200_trk_replay(self._h, iters, C.byref(ms)))
+        return ms.value

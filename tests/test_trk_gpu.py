@@ -1,0 +1,147 @@
+"""GPU parity of the tracking multicorrelator (C ABI gb200_trk_*) against the oracle.
+
+Oracle = oracle/liboracle.so (scalar restatement of Cpu_Multicorrelator_Real_Codes, bit-pinned against the
+reference's own code in tests/test_oracle_pin.py) and, when the prebuilt oracle/_ref/libgnssref.so travelled,
+the reference's generic protokernels themselves.
+Tolerance (north_star): 1e-4 relative, measured as max_t|out - ref| / max_t|ref| per command (float32).
+"""
+import numpy as np
+import pytest
+
+import _oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def rel_err(a, b):
+    return float(np.max(np.abs(a - b)) / np.max(np.abs(b)))
+
+
+def _taps(nt, spacing=0.5):
+    return ((np.arange(nt) - (nt - 1) / 2.0) * spacing).astype(np.float32)
+
+
+def _engine(**kw):
+    from gnss_sim_receiver_b200.tracking import TrackingEngine
+    return TrackingEngine(**kw)
+
+
+@pytest.mark.parametrize("n,L,ntaps,code_step", [
+    (4000, 1023, 3, 1.023e6 / 4e6), (8111, 1023, 3, 0.3), (16000, 8184, 5, 2 * 1.023e6 / 4e6), (16000, 8184, 11, 2 * 1.023e6 / 4e6),
+    (20000, 10230, 11, 10.23e6 / 20e6), (25000, 1023, 11, 1.023e6 / 25e6), (100000, 1023, 11, 1.023e6 / 100e6), (2048, 2046, 3, 0.3),
+    (777, 1023, 1, 0.26), (129, 31, 2, 0.9),
+])
+def test_single_channel_vs_oracle(n, L, ntaps, code_step):
+    rng = np.random.default_rng(n + ntaps)
+    sig = (rng.uniform(-0.5, 0.5, n) + 1j * rng.uniform(-0.5, 0.5, n)).astype(np.complex64)
+    code = rng.choice([-1.0, 1.0], L).astype(np.float32)
+    shifts = _taps(ntaps)
+    eng = _engine(max_channels=4, max_code_len=L, ring_samples=4 * 131072, max_block=131072)
+    eng.set_code(1, code)
+    eng.push_iq(np.zeros(37, np.complex64))
+    first = eng.push_iq(sig)
+    assert first == 37
+    for rem_carr, phase_step, rem_code in [(0.25, 0.1, 0.4), (-1.3, -0.02137, -0.7), (2.9, 0.0, 0.0)]:
+        cmds = eng.make_cmds([1], [first], [n], shifts[None, :], [rem_carr], [phase_step], [rem_code], [code_step])
+        got = eng.correlate(cmds)[0]
+        ref32 = O.mc_real_codes(sig, code, shifts, rem_carr, phase_step, rem_code, code_step)
+        ref64 = O.mc_real_codes_f64(sig, code, shifts, rem_carr, phase_step, rem_code, code_step, mimic_inc=True)
+        assert rel_err(got, ref64) < TOL, (got, ref64)
+        assert rel_err(got, ref32) < TOL, (got, ref32)
+    eng.close()
+
+
+def test_signal_like_input_many_channels():
+    """C3-shaped: 25 MS/s GPS L1, 11 taps, 64 channels at different window offsets of one ring."""
+    rng = np.random.default_rng(7)
+    fs, n, L, nt, nch = 25e6, 25000, 1023, 11, 64
+    ring = (rng.standard_normal(3 * n) + 1j * rng.standard_normal(3 * n)).astype(np.complex64)
+    codes = np.stack([O.gps_l1_ca_code(p) for p in range(1, 33)] * 2)
+    eng = _engine(max_channels=nch, max_code_len=L, ring_samples=8 * n, max_block=2 * n)
+    for c in range(nch):
+        eng.set_code(c, codes[c])
+    eng.push_iq(ring)
+    offs = rng.integers(0, 2 * n, nch)
+    lens = n + rng.integers(-1, 2, nch)
+    dopp = rng.uniform(-5e3, 5e3, nch)
+    step = (2 * np.pi * dopp / fs).astype(np.float32)
+    remc = rng.uniform(0, 2 * np.pi, nch).astype(np.float32)
+    cstep = ((1.023e6 * (1 + dopp / 1575.42e6)) / fs).astype(np.float32)
+    remcode = rng.uniform(-0.5, 0.5, nch).astype(np.float32)
+    shifts = np.tile(_taps(nt, 0.1), (nch, 1))
+    cmds = eng.make_cmds(np.arange(nch), offs, lens, shifts, remc, step, remcode, cstep)
+    got = eng.correlate(cmds)
+    ref = O.mc_batch(ring, offs, lens, codes, shifts, remc, step, remcode, cstep)
+    for c in range(nch):
+        r64 = O.mc_real_codes_f64(ring[offs[c]:offs[c] + lens[c]], codes[c], shifts[c], remc[c], step[c], remcode[c], cstep[c], mimic_inc=True)
+        assert rel_err(got[c], r64) < TOL, c
+        assert rel_err(got[c], ref[c]) < TOL, c
+    # replay is deterministic: same bits
+    eng.enqueue(cmds)
+    again = eng.collect()[:, :nt]
+    assert np.array_equal(again.view(np.uint32), got.view(np.uint32))
+    eng.close()
+
+
+@pytest.mark.parametrize("iq_dtype,np_t,scale", [(1, np.int16, 400.0), (2, np.int8, 25.0)])
+def test_integer_iq_ingest(iq_dtype, np_t, scale):
+    rng = np.random.default_rng(11)
+    n, L, nt = 16000, 8184, 5
+    info = np.iinfo(np_t)
+    raw = np.clip(np.rint(rng.standard_normal((n, 2)) * scale), -info.max, info.max).astype(np_t)
+    sig = (raw[:, 0].astype(np.float32) + 1j * raw[:, 1].astype(np.float32)).astype(np.complex64)
+    code = rng.choice([-1.0, 1.0], L).astype(np.float32)
+    shifts = _taps(nt, 0.3)
+    eng = _engine(max_channels=1, max_code_len=L, iq_dtype=iq_dtype, ring_samples=4 * n, max_block=n)
+    eng.set_code(0, code)
+    first = eng.push_iq(raw.reshape(-1))
+    cmds = eng.make_cmds([0], [first], [n], shifts[None, :], [1.0], [0.05], [0.2], [0.5115])
+    got = eng.correlate(cmds)[0]
+    ref = O.mc_real_codes_f64(sig, code, shifts, 1.0, 0.05, 0.2, 0.5115, mimic_inc=True)
+    assert rel_err(got, ref) < TOL
+    eng.close()
+
+
+def test_complex_code_sibling():
+    """Cpu_Multicorrelator (cpu_multicorrelator.cc:73-100): complex code table."""
+    rng = np.random.default_rng(5)
+    n, L, nt = 4096, 1023, 3
+    sig = (rng.uniform(0, 1, n) + 1j * rng.uniform(0, 1, n)).astype(np.complex64)
+    code = (rng.choice([-1.0, 1.0], L) + 1j * rng.choice([-1.0, 1.0], L)).astype(np.complex64)
+    shifts = _taps(nt)
+    eng = _engine(max_channels=1, max_code_len=L, ring_samples=4 * n, max_block=n)
+    eng.set_code(0, code)
+    first = eng.push_iq(sig)
+    cmds = eng.make_cmds([0], [first], [n], shifts[None, :], [0.0], [0.1], [0.4], [0.3])
+    got = eng.correlate(cmds)[0]
+    ref = O.mc_complex_codes(sig, code, shifts, 0.0, 0.1, 0.4, 0.3)
+    assert rel_err(got, ref) < TOL
+    eng.close()
+
+
+def test_ring_wraparound_and_errors():
+    from gnss_sim_receiver_b200._capi import GB200Error
+    rng = np.random.default_rng(3)
+    n, L = 4000, 1023
+    eng = _engine(max_channels=2, max_code_len=L, ring_samples=3 * n + 17, max_block=n + 8)
+    code = rng.choice([-1.0, 1.0], L).astype(np.float32)
+    eng.set_code(0, code)
+    stream = (rng.standard_normal(10 * n) + 1j * rng.standard_normal(10 * n)).astype(np.complex64)
+    shifts = _taps(3)
+    pos = 0
+    for k in range(10):  # wraps the ring three times; every window is checked while it is still resident
+        eng.push_iq(stream[pos:pos + n])
+        pos += n
+        off = max(0, pos - n - 5 * (k % 3))
+        cmds = eng.make_cmds([0], [off], [n], shifts[None, :], [0.3], [0.01], [0.1], [0.25575])
+        got = eng.correlate(cmds)[0]
+        ref = O.mc_real_codes_f64(stream[off:off + n], code, shifts, 0.3, 0.01, 0.1, 0.25575, mimic_inc=True)
+        assert rel_err(got, ref) < TOL, k
+    with pytest.raises(GB200Error):  # overwritten window
+        eng.correlate(eng.make_cmds([0], [0], [n], shifts[None, :], [0.0], [0.0], [0.0], [0.25]))
+    with pytest.raises(GB200Error):  # beyond head
+        eng.correlate(eng.make_cmds([0], [pos - 10], [n], shifts[None, :], [0.0], [0.0], [0.0], [0.25]))
+    with pytest.raises(GB200Error):  # channel without code
+        eng.correlate(eng.make_cmds([1], [pos - n], [n], shifts[None, :], [0.0], [0.0], [0.0], [0.25]))
+    eng.close()
