@@ -1,19 +1,169 @@
-// PCPS acquisition engine — placeholder entry points until the FFT kernels land (next commit).
-#include "common.cuh"
+// PCPS acquisition engine: C ABI (include/gnss_b200.h) over acq_kernel.cuh.
+#include "acq_kernel.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <new>
+#include <vector>
+
 using namespace gb200;
-#define NOTYET return set_error(GB200_ESTATE, "%s: acquisition engine not built yet", __func__)
-extern "C" {
-int gb200_acq_create(const gb200_acq_config*, gb200_acq**) { NOTYET; }
-int gb200_acq_destroy(gb200_acq*) { return GB200_OK; }
-int gb200_acq_set_local_code(gb200_acq*, int, const gb200_cf32*, int) { NOTYET; }
-int gb200_acq_set_doppler_grid(gb200_acq*, int, int, int) { NOTYET; }
-int gb200_acq_num_doppler_bins(const gb200_acq*) { return 0; }
-int gb200_acq_neff(const gb200_acq*) { return 0; }
-int gb200_acq_run(gb200_acq*, const void*, int, const int32_t*, int, gb200_acq_result*) { NOTYET; }
-int gb200_acq_run_device(gb200_acq*, const void*, int, const int32_t*, int, gb200_acq_result*) { NOTYET; }
-int gb200_acq_replay(gb200_acq*, int, float*) { NOTYET; }
-float gb200_acq_threshold(const gb200_acq*, float) { return 0.0f; }
-int gb200_acq_keep_grid(gb200_acq*, int) { NOTYET; }
-int gb200_acq_read_grid(gb200_acq*, int, float*) { NOTYET; }
-int gb200_acq_fft(gb200_acq*, const gb200_cf32*, gb200_cf32*, int) { NOTYET; }
+
+struct gb200_acq
+{
+    gb200_acq_config cfg{};
+    cudaStream_t stream{};
+    cudaEvent_t ev0{}, ev1{};
+    FftPlan plan{};
+    int elem_bytes{8};
+    int threads{1024};
+    size_t smem{0};
+    int n_bins{0}, neff{0}, out_offset{0}, n_parts{1};
+    int doppler_max{0}, doppler_step{0}, doppler_center{0};
+    int keep_grid{0}, user_keep{0};
+    std::vector<int> pos_of_k;  // natural index -> digit-reversed position
+    float2 *d_twA{nullptr}, *d_twB{nullptr};
+    void* d_iq{nullptr};
+    float2* d_X{nullptr};        // [n_bins][N] forward spectra of the wiped input
+    float2* d_C{nullptr};        // [max_prns][N] conjugated code spectra
+    float2* d_stage{nullptr};    // [max(n_bins,1)][N] global-stage staging for forward transforms
+    float2* d_scratch{nullptr};  // [cells][N] inverse global-stage staging
+    size_t scratch_cells{0};
+    float* d_grid{nullptr};      // [max_prns][n_bins][neff]
+    AcqCell* d_cells{nullptr};
+    int* d_slots{nullptr};
+    unsigned long long* d_dphi{nullptr};
+    float* d_phase{nullptr};     // [n_bins][consumed] fp32 accumulated wipe-off phases (reference law); unused in exact mode
+    float* d_inc{nullptr};
+    int exact_wipeoff{0};
+    gb200_acq_result* d_results{nullptr};
+    gb200_acq_result* h_results{nullptr};
+    std::vector<char> code_set;
+    std::vector<int> dwells_done;  // per slot: dwells accumulated in the grid
+    // last run (replay)
+    std::vector<int> last_slots;
+    int last_dwell{0};
+    bool have_run{false};
+};
+
+namespace
+{
+constexpr double TWO_PI = 6.283185307179586476925286766559;
+
+bool factor_235(int n, std::vector<int>& radix)
+{
+    radix.clear();
+    while (n % 4 == 0) { radix.push_back(4); n /= 4; }
+    while (n % 2 == 0) { radix.push_back(2); n /= 2; }
+    while (n % 3 == 0) { radix.push_back(3); n /= 3; }
+    while (n % 5 == 0) { radix.push_back(5); n /= 5; }
+    while (n % 7 == 0) { radix.push_back(7); n /= 7; }
+    return n == 1 && (int)radix.size() <= FFT_MAX_STAGES;
 }
+
+int make_plan(gb200_acq* h, int max_smem)
+{
+    const int N = h->cfg.fft_size;
+    FftPlan& pl = h->plan;
+    pl.n = N;
+    pl.n_hi = (N + FFT_TW_LO - 1) / FFT_TW_LO;
+    const size_t tab_bytes = (size_t)(pl.n_hi + FFT_TW_LO) * sizeof(float2);
+    int g = 0;
+    for (int r = 1; r <= 8; r++)
+        if (N % r == 0 && (size_t)(N / r) * sizeof(float2) + tab_bytes <= (size_t)max_smem)
+            {
+                g = r;
+                break;
+            }
+    if (!g) return set_error(GB200_EINVAL, "fft_size %d: no split into <= 8 shared-memory blocks", N);
+    pl.g_radix = g;
+    pl.m = N / g;
+    std::vector<int> radix;
+    if (!factor_235(pl.m, radix)) return set_error(GB200_EINVAL, "fft_size %d has a prime factor other than 2, 3, 5, 7", N);
+    pl.n_stages = (int)radix.size();
+    int n_s = pl.m;
+    for (int s = 0; s < pl.n_stages; s++)
+        {
+            pl.radix[s] = radix[s];
+            const unsigned ms = (unsigned)(n_s / radix[s]);
+            pl.inv_ms[s] = ms == 1 ? 0u : (unsigned)((0x100000000ull + ms - 1) / ms);
+            n_s /= radix[s];
+        }
+    h->smem = (size_t)pl.m * sizeof(float2) + tab_bytes;
+    h->threads = std::min(1024, std::max(128, ((pl.m / 8) + 63) / 64 * 64));
+    // natural index -> position after the DIF stages (global stage first)
+    h->pos_of_k.resize(N);
+    for (int k = 0; k < N; k++)
+        {
+            int p = 0, size = N, kk = k;
+            auto digit = [&](int r) {
+                const int m = size / r;
+                p += (kk % r) * m;
+                kk /= r;
+                size = m;
+            };
+            if (g > 1) digit(g);
+            for (int s = 0; s < pl.n_stages; s++) digit(pl.radix[s]);
+            h->pos_of_k[k] = p;
+        }
+    return GB200_OK;
+}
+
+unsigned long long turns_fix(double turns)
+{
+    double f = turns - std::floor(turns);
+    if (f >= 1.0) f = 0.0;
+    return (unsigned long long)std::ldexp(f, 53) << 11;
+}
+
+template <typename K>
+cudaError_t opt_in_smem(K kernel, size_t smem)
+{
+    if (smem > 48 * 1024) return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    return cudaSuccess;
+}
+
+// forward transform of `batch` blocks: raw IQ + wipe-off (src_iq) or cf32 buffers; result in dst (digit-reversed order)
+template <int IQ>
+cudaError_t forward_iq(gb200_acq* h, int batch, float2* dst)
+{
+    const FftPlan& pl = h->plan;
+    cudaError_t e;
+    if (pl.g_radix == 1)
+        {
+            if ((e = opt_in_smem(acq_fwd_kernel<IQ, true>, h->smem)) != cudaSuccess) return e;
+            acq_fwd_kernel<IQ, true><<<dim3(1, batch), h->threads, h->smem, h->stream>>>(pl, h->d_iq, h->cfg.consumed_samples, h->d_dphi, h->exact_wipeoff ? nullptr : h->d_phase, h->d_twA, h->d_twB, dst, 0);
+            count_launch();
+            return cudaGetLastError();
+        }
+    acq_gstage_fwd_kernel<IQ, true><<<dim3((pl.m + 255) / 256, batch), 256, 0, h->stream>>>(pl, h->d_iq, h->cfg.consumed_samples, h->d_dphi, h->exact_wipeoff ? nullptr : h->d_phase, h->d_twA, h->d_twB, h->d_stage);
+    count_launch();
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if ((e = opt_in_smem(acq_fwd_kernel<0, false>, h->smem)) != cudaSuccess) return e;
+    acq_fwd_kernel<0, false><<<dim3(pl.g_radix, batch), h->threads, h->smem, h->stream>>>(pl, h->d_stage, 0, nullptr, nullptr, h->d_twA, h->d_twB, dst, 0);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// forward transform of ONE cf32 block held in d_stage[0..N) (code replica / test hook); result in dst
+cudaError_t forward_cf32(gb200_acq* h, float2* dst, int conj_out)
+{
+    const FftPlan& pl = h->plan;
+    cudaError_t e;
+    const float2* src = h->d_stage;
+    if (pl.g_radix > 1)
+        {
+            // the global stage is not in place: stage into the second half of d_stage (it holds >= 2 blocks, see create)
+            float2* tmp = h->d_stage + pl.n;
+            acq_gstage_fwd_kernel<0, false><<<dim3((pl.m + 255) / 256, 1), 256, 0, h->stream>>>(pl, h->d_stage, 0, nullptr, nullptr, h->d_twA, h->d_twB, tmp);
+            count_launch();
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            src = tmp;
+        }
+    if ((e = opt_in_smem(acq_fwd_kernel<0, false>, h->smem)) != cudaSuccess) return e;
+    acq_fwd_kernel<0, false><<<dim3(pl.g_radix, 1), h->threads, h->smem, h->stream>>>(pl, src, 0, nullptr, nullptr, h->d_twA, h->d_twB, dst, conj_out);
+    count_launch();
+    return cudaGetLastError();
+}
+}  // namespace
+
+#include "acq_api.inc"

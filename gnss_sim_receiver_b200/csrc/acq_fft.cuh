@@ -1,0 +1,230 @@
+// Hand-written batched mixed-radix FFT building blocks for the PCPS acquisition kernels (no cuFFT).
+//
+// Replaces FFTW reached through gr::fft::fft_complex_fwd/rev (src/algorithms/libs/gnss_sdr_fft.h:27-61; call sites
+// pcps_acquisition.cc:113-114,206,647,653): unnormalised complex DFT of d_fft_size points, sizes such as 4000, 16000,
+// 20000, 25000, 32000, 100000 (factors 2, 3, 5, 7).
+//
+// Scheme: in-place decimation-in-frequency forward transform whose output is left in mixed-radix digit-reversed order,
+// element-wise product with a code spectrum stored in the SAME order, then the transposed decimation-in-time inverse
+// that consumes that order and delivers natural order.  No reordering pass, no ping-pong buffer: a 25000-point block
+// (200 KB) lives in one SM's shared memory.  Transforms longer than one SM's shared memory take their first DIF stage
+// (last DIT stage) through global memory and continue as g_radix independent shared-memory blocks.
+#pragma once
+#include "common.cuh"
+
+namespace gb200
+{
+constexpr int FFT_MAX_STAGES = 20;
+constexpr int FFT_TW_SHIFT = 8;  // W_N^e = A[e >> 8] * B[e & 255]
+constexpr int FFT_TW_LO = 1 << FFT_TW_SHIFT;
+
+struct FftPlan
+{
+    int n;         // transform length N
+    int m;         // shared-memory block length (N / g_radix)
+    int g_radix;   // 1, or the radix of the stage done through global memory
+    int n_stages;  // shared-memory stages
+    int n_hi;      // entries of twiddle table A
+    int radix[FFT_MAX_STAGES];      // DIF order
+    unsigned inv_ms[FFT_MAX_STAGES];  // ceil(2^32 / ms) (0 when ms == 1) for the per-stage butterfly -> (block, j2) split
+};
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+__device__ __forceinline__ float2 cmulc(float2 a, float2 b) { return make_float2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y); }  // a * conj(b)
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+// multiply by -i (forward) / +i (inverse)
+template <bool INV>
+__device__ __forceinline__ float2 rot90(float2 a)
+{
+    return INV ? make_float2(-a.y, a.x) : make_float2(a.y, -a.x);
+}
+
+// W_N^e = exp(-2*pi*i*e/N), 0 <= e < N, from the two-level table staged in shared memory
+__device__ __forceinline__ float2 fft_twiddle(const float2* sA, const float2* sB, int e)
+{
+    return cmul(sA[e >> FFT_TW_SHIFT], sB[e & (FFT_TW_LO - 1)]);
+}
+
+template <int R, bool INV>
+struct Dft;
+
+template <bool INV>
+struct Dft<2, INV>
+{
+    static __device__ __forceinline__ void run(float2* v)
+    {
+        const float2 a = v[0], b = v[1];
+        v[0] = cadd(a, b);
+        v[1] = csub(a, b);
+    }
+};
+
+template <bool INV>
+struct Dft<3, INV>
+{
+    static __device__ __forceinline__ void run(float2* v)
+    {
+        const float2 t = cadd(v[1], v[2]);
+        const float2 d = csub(v[1], v[2]);
+        const float2 a = make_float2(v[0].x - 0.5f * t.x, v[0].y - 0.5f * t.y);
+        const float2 b = rot90<INV>(make_float2(0.86602540378443865f * d.x, 0.86602540378443865f * d.y));
+        v[0] = cadd(v[0], t);
+        v[1] = cadd(a, b);
+        v[2] = csub(a, b);
+    }
+};
+
+template <bool INV>
+struct Dft<4, INV>
+{
+    static __device__ __forceinline__ void run(float2* v)
+    {
+        const float2 t0 = cadd(v[0], v[2]), t1 = csub(v[0], v[2]);
+        const float2 t2 = cadd(v[1], v[3]), t3 = rot90<INV>(csub(v[1], v[3]));
+        v[0] = cadd(t0, t2);
+        v[2] = csub(t0, t2);
+        v[1] = cadd(t1, t3);
+        v[3] = csub(t1, t3);
+    }
+};
+
+template <bool INV>
+struct Dft<5, INV>
+{
+    static __device__ __forceinline__ void run(float2* v)
+    {
+        const float c1 = 0.30901699437494742f, c2 = -0.80901699437494742f;
+        const float s1 = 0.95105651629515357f, s2 = 0.58778525229247313f;
+        const float2 t1 = cadd(v[1], v[4]), t2 = cadd(v[2], v[3]);
+        const float2 t3 = csub(v[1], v[4]), t4 = csub(v[2], v[3]);
+        const float2 a1 = make_float2(v[0].x + c1 * t1.x + c2 * t2.x, v[0].y + c1 * t1.y + c2 * t2.y);
+        const float2 a2 = make_float2(v[0].x + c2 * t1.x + c1 * t2.x, v[0].y + c2 * t1.y + c1 * t2.y);
+        const float2 b1 = rot90<INV>(make_float2(s1 * t3.x + s2 * t4.x, s1 * t3.y + s2 * t4.y));
+        const float2 b2 = rot90<INV>(make_float2(s2 * t3.x - s1 * t4.x, s2 * t3.y - s1 * t4.y));
+        v[0] = make_float2(v[0].x + t1.x + t2.x, v[0].y + t1.y + t2.y);
+        v[1] = cadd(a1, b1);
+        v[4] = csub(a1, b1);
+        v[2] = cadd(a2, b2);
+        v[3] = csub(a2, b2);
+    }
+};
+
+// generic O(R^2) butterfly with coefficients from the twiddle tables: W_R^q = W_N^{q * N / R}
+template <int R, bool INV>
+__device__ __forceinline__ void dft_generic(float2* v, const float2* sA, const float2* sB, int n)
+{
+    float2 y[R];
+    const int unit = n / R;
+#pragma unroll
+    for (int k = 0; k < R; k++)
+        {
+            float2 acc = v[0];
+#pragma unroll
+            for (int j = 1; j < R; j++)
+                {
+                    const float2 w = fft_twiddle(sA, sB, ((j * k) % R) * unit);
+                    acc = cadd(acc, INV ? cmulc(v[j], w) : cmul(v[j], w));
+                }
+            y[k] = acc;
+        }
+#pragma unroll
+    for (int k = 0; k < R; k++) v[k] = y[k];
+}
+
+template <bool INV>
+struct Dft<7, INV>
+{
+    static __device__ __forceinline__ void run(float2* v, const float2* sA, const float2* sB, int n) { dft_generic<7, INV>(v, sA, sB, n); }
+};
+
+// One in-place stage over a shared-memory block x[0..m_blk): sub-blocks of n_s points, radix R.
+// Forward (DIF): butterfly, then twiddle W_{n_s}^{j2*k}.  Inverse (DIT): conj twiddle, then inverse butterfly.
+template <int R, bool INV>
+__device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, unsigned inv_ms, int n, const float2* sA, const float2* sB)
+{
+    const int ms = n_s / R;
+    const int nb = m_blk / R;
+    const int tw_mul = n / n_s;
+    for (int id = threadIdx.x; id < nb; id += blockDim.x)
+        {
+            const int blk = ms == 1 ? id : (int)__umulhi((unsigned)id, inv_ms);  // id / ms (exact for id * ms < 2^32)
+            const int j2 = id - blk * ms;
+            float2* p = x + blk * n_s + j2;
+            float2 v[R];
+#pragma unroll
+            for (int k = 0; k < R; k++) v[k] = p[k * ms];
+            if (INV && ms > 1)
+                {
+                    const float2 w1 = fft_twiddle(sA, sB, j2 * tw_mul);
+                    float2 w = w1;
+#pragma unroll
+                    for (int k = 1; k < R; k++)
+                        {
+                            v[k] = cmulc(v[k], w);
+                            if (k + 1 < R) w = cmul(w, w1);
+                        }
+                }
+            if constexpr (R == 7)
+                Dft<7, INV>::run(v, sA, sB, n);
+            else
+                Dft<R, INV>::run(v);
+            if (!INV && ms > 1)
+                {
+                    const float2 w1 = fft_twiddle(sA, sB, j2 * tw_mul);
+                    float2 w = w1;
+#pragma unroll
+                    for (int k = 1; k < R; k++)
+                        {
+                            v[k] = cmul(v[k], w);
+                            if (k + 1 < R) w = cmul(w, w1);
+                        }
+                }
+#pragma unroll
+            for (int k = 0; k < R; k++) p[k * ms] = v[k];
+        }
+    __syncthreads();
+}
+
+template <bool INV>
+__device__ __forceinline__ void fft_smem_stage_any(int R, float2* x, int m_blk, int n_s, unsigned inv_ms, int n, const float2* sA, const float2* sB)
+{
+    switch (R)
+        {
+        case 2: fft_smem_stage<2, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
+        case 3: fft_smem_stage<3, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
+        case 4: fft_smem_stage<4, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
+        case 5: fft_smem_stage<5, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
+        default: fft_smem_stage<7, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
+        }
+}
+
+// all shared-memory stages of one block of plan.m points, forward: natural -> digit-reversed
+__device__ __forceinline__ void fft_smem_forward(const FftPlan& pl, float2* x, const float2* sA, const float2* sB)
+{
+    int n_s = pl.m;
+    for (int s = 0; s < pl.n_stages; s++)
+        {
+            fft_smem_stage_any<false>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], pl.n, sA, sB);
+            n_s /= pl.radix[s];
+        }
+}
+
+// inverse: digit-reversed -> natural (stages in reverse order)
+__device__ __forceinline__ void fft_smem_inverse(const FftPlan& pl, float2* x, const float2* sA, const float2* sB)
+{
+    int n_s = 1;
+    for (int s = pl.n_stages - 1; s >= 0; s--)
+        {
+            n_s *= pl.radix[s];
+            fft_smem_stage_any<true>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], pl.n, sA, sB);
+        }
+}
+
+// twiddle tables global -> shared (all threads), followed by a barrier in the caller
+__device__ __forceinline__ void fft_load_tables(const FftPlan& pl, const float2* gA, const float2* gB, float2* sA, float2* sB)
+{
+    for (int i = threadIdx.x; i < pl.n_hi; i += blockDim.x) sA[i] = gA[i];
+    for (int i = threadIdx.x; i < FFT_TW_LO; i += blockDim.x) sB[i] = gB[i];
+}
+}  // namespace gb200

@@ -1,0 +1,228 @@
+// PCPS acquisition kernels (K2) for sm_100a — see acq_fft.cuh for the FFT scheme.
+//
+// Reference path: pcps_acquisition::acquisition_core, src/algorithms/acquisition/gnuradio_blocks/pcps_acquisition.cc:600-697
+//   forward  : volk_32fc_x2_multiply_32fc(in, wipeoff[bin]) :643 + d_fft_if->execute() :647   -> acq_fwd_kernel
+//   inverse  : multiply by d_fft_codes :650 + d_ifft->execute() :653 + magnitude_squared / add :657-665
+//              + per-bin volk_gnsssdr_32f_index_max_32u :505-514                                  -> acq_inv_kernel
+//   statistic: max_to_input_power_statistic :496-528 / first_vs_second_peak_statistic :531-597   -> acq_stats_kernel
+// The forward transform of (input x wipe-off[bin]) does not depend on the PRN, so it is computed once per Doppler bin
+// and shared by every PRN (the reference recomputes it per channel).
+#pragma once
+#include "acq_fft.cuh"
+
+namespace gb200
+{
+struct AcqCell  // reduction of one (slot, bin, part) over code phase
+{
+    float vmax;
+    int imax;
+    float sum;
+    int pad_;
+};
+
+struct AcqParams
+{
+    FftPlan plan;
+    int consumed;        // input samples, zero-padded to plan.n
+    int n_bins;
+    int neff;            // code phases searched
+    int out_offset;      // first output sample searched (fft_size/2 with bit_transition, else 0)
+    int n_parts;         // cells per (slot, bin): 1, or chunks of the global inverse stage
+    int dwell_index;
+    int keep_grid;
+    int doppler_base;    // -doppler_max + doppler_center
+    int doppler_step;
+    int use_cfar;
+    int samples_per_chip;
+    int num_dwells;      // dwells accumulated so far, including this one
+    float samples_per_code;
+};
+
+__device__ __forceinline__ float2 acq_phasor(unsigned long long u)
+{
+    const int a = (int)(u >> 32);
+    float s, c;
+    sincospif((float)a * 4.656612873077393e-10f, &s, &c);
+    return make_float2(c, s);
+}
+
+template <int IQ>
+__device__ __forceinline__ float2 acq_load_iq(const void* base, int s)
+{
+    if (IQ == GB200_IQ_CF32) return __ldg(reinterpret_cast<const float2*>(base) + s);
+    if (IQ == GB200_IQ_CS16)
+        {
+            const short2 v = __ldg(reinterpret_cast<const short2*>(base) + s);
+            return make_float2((float)v.x, (float)v.y);  // volk_gnsssdr_16ic_convert_32fc, pcps_acquisition.cc:610
+        }
+    const char2 v = __ldg(reinterpret_cast<const char2*>(base) + s);
+    return make_float2((float)v.x, (float)v.y);
+}
+
+// sample n of (zero-padded input) x wipe-off of one Doppler bin.
+//   phase_row != NULL (default, the reference's law): the wipe-off is (cosf, sinf) of the fp32 phase the reference
+//     accumulates by repeated addition (update_local_carrier, pcps_acquisition.cc:232-245 ->
+//     volk_gnsssdr_s32f_sincos_32fc_generic, kernels/volk_gnsssdr/volk_gnsssdr_s32f_sincos_32fc.h:390-401); the
+//     accumulated phases are tabulated once per Doppler grid by acq_phase_table_kernel;
+//   phase_row == NULL (exact mode): exp(-j*2*pi*f_bin*n/fs) from dphi = frac(-f_bin/fs) in 64-bit fixed-point turns.
+template <int IQ>
+__device__ __forceinline__ float2 acq_wiped_sample(const void* iq, int n, int consumed, unsigned long long dphi, const float* __restrict__ phase_row)
+{
+    if (n >= consumed) return make_float2(0.0f, 0.0f);
+    const float2 x = acq_load_iq<IQ>(iq, n);
+    if (phase_row)
+        {
+            float s, c;
+            sincosf(__ldg(phase_row + n), &s, &c);
+            return cmul(x, make_float2(c, s));
+        }
+    if (dphi == 0ull) return x;
+    return cmul(x, acq_phasor(dphi * (unsigned long long)n));
+}
+
+// fp32 phase accumulation of the reference, one thread per Doppler bin: tab[bin][n] = phase before sample n
+__global__ void acq_phase_table_kernel(const float* __restrict__ inc, int n_bins, int n, float* __restrict__ tab)
+{
+    const int bin = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bin >= n_bins) return;
+    const float d = inc[bin];
+    float ph = 0.0f;
+    float* row = tab + (size_t)bin * n;
+    for (int i = 0; i < n; i++)
+        {
+            row[i] = ph;
+            ph = __fadd_rn(ph, d);
+        }
+}
+
+// Forward transform of one shared-memory block.  grid = (g_radix, batch).
+//   SRC_IQ = true : block 0 only (g_radix == 1): input = raw IQ x wipe-off of bin blockIdx.y
+//   SRC_IQ = false: input = cf32 buffer src[batch][N] (output of the global stage, or a zero-padded code replica)
+// Output dst[batch][N] in digit-reversed order, optionally conjugated (code spectra, pcps_acquisition.cc:207).
+template <int IQ, bool SRC_IQ>
+__global__ void __launch_bounds__(1024) acq_fwd_kernel(FftPlan pl, const void* __restrict__ src, int consumed, const unsigned long long* __restrict__ dphi, const float* __restrict__ phase_tab,
+    const float2* __restrict__ gA, const float2* __restrict__ gB, float2* __restrict__ dst, int conj_out)
+{
+    extern __shared__ __align__(16) float2 sm[];
+    float2* x = sm;
+    float2* sA = sm + pl.m;
+    float2* sB = sA + pl.n_hi;
+    fft_load_tables(pl, gA, gB, sA, sB);
+    const size_t base = (size_t)blockIdx.y * pl.n + (size_t)blockIdx.x * pl.m;
+    if (SRC_IQ)
+        {
+            const unsigned long long d = dphi[blockIdx.y];
+            const float* prow = phase_tab ? phase_tab + (size_t)blockIdx.y * consumed : nullptr;
+            for (int i = threadIdx.x; i < pl.m; i += blockDim.x) x[i] = acq_wiped_sample<IQ>(src, i, consumed, d, prow);
+        }
+    else
+        {
+            const float2* s = reinterpret_cast<const float2*>(src) + base;
+            for (int i = threadIdx.x; i < pl.m; i += blockDim.x) x[i] = s[i];
+        }
+    __syncthreads();
+    fft_smem_forward(pl, x, sA, sB);
+    float2* d = dst + base;
+    for (int i = threadIdx.x; i < pl.m; i += blockDim.x)
+        {
+            float2 v = x[i];
+            if (conj_out) v.y = -v.y;
+            d[i] = v;
+        }
+}
+
+// First DIF stage through global memory (transforms longer than one SM's shared memory): radix R = plan.g_radix over
+// stride m.  grid = (ceil(m / blockDim), batch).  dst[batch][k1*m + j2] = (sum_j1 in[j1*m + j2] W_R^{j1 k1}) * W_N^{j2 k1}
+template <int IQ, bool SRC_IQ>
+__global__ void __launch_bounds__(256) acq_gstage_fwd_kernel(FftPlan pl, const void* __restrict__ src, int consumed, const unsigned long long* __restrict__ dphi, const float* __restrict__ phase_tab,
+    const float2* __restrict__ gA, const float2* __restrict__ gB, float2* __restrict__ dst)
+{
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= pl.m) return;
+    const int R = pl.g_radix, unit = pl.n / R;
+    float2 v[8];
+    for (int j1 = 0; j1 < R; j1++)
+        {
+            const int n = j1 * pl.m + j2;
+            if (SRC_IQ)
+                v[j1] = acq_wiped_sample<IQ>(src, n, consumed, dphi[blockIdx.y], phase_tab ? phase_tab + (size_t)blockIdx.y * consumed : nullptr);
+            else
+                v[j1] = reinterpret_cast<const float2*>(src)[(size_t)blockIdx.y * pl.n + n];
+        }
+    float2* d = dst + (size_t)blockIdx.y * pl.n;
+    for (int k1 = 0; k1 < R; k1++)
+        {
+            float2 acc = v[0];
+            for (int j1 = 1; j1 < R; j1++) acc = cadd(acc, cmul(v[j1], fft_twiddle(gA, gB, ((j1 * k1) % R) * unit)));
+            const long long e = (long long)j2 * k1;  // < N
+            d[k1 * pl.m + j2] = k1 ? cmul(acc, fft_twiddle(gA, gB, (int)e)) : acc;
+        }
+}
+
+// block-wide reduction of (max value, first index of the maximum, sum); result valid on thread 0
+__device__ __forceinline__ void acq_block_reduce(float& v, int& idx, float& sum)
+{
+    __shared__ float s_v[32];
+    __shared__ int s_i[32];
+    __shared__ float s_s[32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        {
+            const float ov = __shfl_down_sync(0xffffffffu, v, o);
+            const int oi = __shfl_down_sync(0xffffffffu, idx, o);
+            sum += __shfl_down_sync(0xffffffffu, sum, o);
+            if (ov > v || (ov == v && oi < idx))
+                {
+                    v = ov;
+                    idx = oi;
+                }
+        }
+    const int w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    if ((threadIdx.x & 31) == 0)
+        {
+            s_v[w] = v;
+            s_i[w] = idx;
+            s_s[w] = sum;
+        }
+    __syncthreads();
+    if (threadIdx.x < 32)
+        {
+            v = threadIdx.x < nw ? s_v[threadIdx.x] : -1.0f;
+            idx = threadIdx.x < nw ? s_i[threadIdx.x] : 0x7fffffff;
+            sum = threadIdx.x < nw ? s_s[threadIdx.x] : 0.0f;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                {
+                    const float ov = __shfl_down_sync(0xffffffffu, v, o);
+                    const int oi = __shfl_down_sync(0xffffffffu, idx, o);
+                    sum += __shfl_down_sync(0xffffffffu, sum, o);
+                    if (ov > v || (ov == v && oi < idx))
+                        {
+                            v = ov;
+                            idx = oi;
+                        }
+                }
+        }
+}
+
+// |y|^2 of output sample n, dwell accumulation into the kept grid (pcps_acquisition.cc:657-665), running max / sum
+__device__ __forceinline__ void acq_consume(const AcqParams& p, float2 y, int n, float* __restrict__ grid_row, float& best, int& besti, float& sum)
+{
+    const int i = n - p.out_offset;
+    if (i < 0 || i >= p.neff) return;
+    float g = y.x * y.x + y.y * y.y;
+    if (grid_row)
+        {
+            if (p.dwell_index > 0) g = grid_row[i] + g;
+            grid_row[i] = g;
+        }
+    sum += g;
+    if (g > best)
+        {
+            best = g;
+            besti = i;
+        }
+}
+}  // namespace gb200
+
+#include "acq_kernel2.cuh"

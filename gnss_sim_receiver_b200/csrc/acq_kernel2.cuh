@@ -1,0 +1,216 @@
+// Inverse side of the acquisition search (included by acq_kernel.cuh).
+#pragma once
+
+namespace gb200
+{
+// grid = (g_radix, n_bins, n_slots).  x = X[bin] .* C[slot] on block blockIdx.x, inverse shared-memory stages, then
+//   MODE 0: (g_radix == 1) |.|^2, grid accumulation, max / argmax / sum  -> cells[(slot_i * n_bins + bin)]
+//   MODE 1: (g_radix  > 1) store the block to scratch[(slot_i * n_bins + bin)][N] for the global inverse stage
+//   MODE 2: test hook — no code product, store the natural-order complex output to scratch
+template <int MODE>
+__global__ void __launch_bounds__(1024) acq_inv_kernel(AcqParams p, const float2* __restrict__ X, const float2* __restrict__ Cs, const int* __restrict__ slots,
+    const float2* __restrict__ gA, const float2* __restrict__ gB, float2* __restrict__ scratch, float* __restrict__ grid, AcqCell* __restrict__ cells)
+{
+    extern __shared__ __align__(16) float2 sm[];
+    const FftPlan& pl = p.plan;
+    float2* x = sm;
+    float2* sA = sm + pl.m;
+    float2* sB = sA + pl.n_hi;
+    fft_load_tables(pl, gA, gB, sA, sB);
+    const int bin = blockIdx.y, si = blockIdx.z;
+    const size_t blk_off = (size_t)blockIdx.x * pl.m;
+    const float2* xs = X + (size_t)bin * pl.n + blk_off;
+    if (MODE == 2)
+        {
+            for (int i = threadIdx.x; i < pl.m; i += blockDim.x) x[i] = xs[i];
+        }
+    else
+        {
+            const float2* cs = Cs + (size_t)slots[si] * pl.n + blk_off;
+            for (int i = threadIdx.x; i < pl.m; i += blockDim.x) x[i] = cmul(xs[i], cs[i]);  // volk_32fc_x2_multiply_32fc, :650
+        }
+    __syncthreads();
+    fft_smem_inverse(pl, x, sA, sB);
+    const size_t cell = (size_t)si * p.n_bins + bin;
+    if (MODE != 0)
+        {
+            float2* d = scratch + cell * pl.n + blk_off;
+            for (int i = threadIdx.x; i < pl.m; i += blockDim.x) d[i] = x[i];
+            return;
+        }
+    float* grow = p.keep_grid ? grid + ((size_t)slots[si] * p.n_bins + bin) * p.neff : nullptr;
+    float best = -1.0f, sum = 0.0f;
+    int besti = 0x7fffffff;
+    for (int i = threadIdx.x; i < pl.m; i += blockDim.x) acq_consume(p, x[i], i, grow, best, besti, sum);
+    acq_block_reduce(best, besti, sum);
+    if (threadIdx.x == 0)
+        {
+            AcqCell c;
+            c.vmax = best;
+            c.imax = besti;
+            c.sum = sum;
+            c.pad_ = 0;
+            cells[cell] = c;
+        }
+}
+
+// Last DIT stage through global memory: y[j1*m + j2] = sum_k1 conj(W_N^{j2 k1}) z_k1[j2] conj(W_R^{j1 k1}), followed by the
+// same epilogue.  grid = (n_parts, n_bins, n_slots); part = a contiguous range of j2.
+__global__ void __launch_bounds__(256) acq_gstage_inv_kernel(AcqParams p, const float2* __restrict__ scratch, const int* __restrict__ slots,
+    const float2* __restrict__ gA, const float2* __restrict__ gB, float* __restrict__ grid, AcqCell* __restrict__ cells, float2* __restrict__ raw_out)
+{
+    const FftPlan& pl = p.plan;
+    const int R = pl.g_radix, unit = pl.n / R;
+    const int bin = blockIdx.y, si = blockIdx.z;
+    const size_t cell = (size_t)si * p.n_bins + bin;
+    const float2* z = scratch + cell * pl.n;
+    float* grow = (p.keep_grid && !raw_out) ? grid + ((size_t)slots[si] * p.n_bins + bin) * p.neff : nullptr;
+    const int per = (pl.m + gridDim.x - 1) / gridDim.x;
+    const int lo = blockIdx.x * per, hi = min(pl.m, lo + per);
+    float best = -1.0f, sum = 0.0f;
+    int besti = 0x7fffffff;
+    // a thread owns whole butterflies; the R outputs of one butterfly are R samples m apart, visited in increasing n
+    // across the j1 loop only per thread, so ties are resolved by (value, index) in the reduction
+    for (int j2 = lo + threadIdx.x; j2 < hi; j2 += blockDim.x)
+        {
+            float2 v[8];
+            for (int k1 = 0; k1 < R; k1++)
+                {
+                    const float2 t = z[k1 * pl.m + j2];
+                    v[k1] = k1 ? cmulc(t, fft_twiddle(gA, gB, (int)((long long)j2 * k1))) : t;
+                }
+            for (int j1 = 0; j1 < R; j1++)
+                {
+                    float2 acc = v[0];
+                    for (int k1 = 1; k1 < R; k1++) acc = cadd(acc, cmulc(v[k1], fft_twiddle(gA, gB, ((j1 * k1) % R) * unit)));
+                    const int n = j1 * pl.m + j2;
+                    if (raw_out)
+                        raw_out[cell * pl.n + n] = acc;
+                    else
+                        {
+                            // strict '>' inside acq_consume keeps the first maximum only if visited in increasing index
+                            // order; here indices of one thread are not monotone across j2, so compare (value, index)
+                            const int i = n - p.out_offset;
+                            if (i >= 0 && i < p.neff)
+                                {
+                                    float g = acc.x * acc.x + acc.y * acc.y;
+                                    if (grow)
+                                        {
+                                            if (p.dwell_index > 0) g = grow[i] + g;
+                                            grow[i] = g;
+                                        }
+                                    sum += g;
+                                    if (g > best || (g == best && i < besti))
+                                        {
+                                            best = g;
+                                            besti = i;
+                                        }
+                                }
+                        }
+                }
+        }
+    if (raw_out) return;
+    acq_block_reduce(best, besti, sum);
+    if (threadIdx.x == 0)
+        {
+            AcqCell c;
+            c.vmax = best;
+            c.imax = besti;
+            c.sum = sum;
+            c.pad_ = 0;
+            cells[cell * p.n_parts + blockIdx.x] = c;
+        }
+}
+
+// One CTA per slot: maximum over (bin, part) with "first Doppler bin, then first code phase" tie rule
+// (pcps_acquisition.cc:505-514), then the test statistic and the Gnss_Synchro fields (:518-527 / :565-596, :691-696).
+__global__ void __launch_bounds__(256) acq_stats_kernel(AcqParams p, const AcqCell* __restrict__ cells, const int* __restrict__ slots, const float* __restrict__ grid,
+    gb200_acq_result* __restrict__ results)
+{
+    __shared__ float s_best;
+    __shared__ int s_key;
+    const int si = blockIdx.x;
+    const AcqCell* c = cells + (size_t)si * p.n_bins * p.n_parts;
+    // key = bin * neff + index : lexicographic (bin, index) order
+    float best = -1.0f, dummy = 0.0f;
+    int key = 0x7fffffff;
+    for (int i = threadIdx.x; i < p.n_bins * p.n_parts; i += blockDim.x)
+        {
+            const int bin = i / p.n_parts;
+            const float v = c[i].vmax;
+            const int k = bin * p.neff + c[i].imax;
+            // the reference starts from grid_maximum = 0 and uses strict '>': an all-zero grid leaves (0, 0)
+            if (v > best || (v == best && k < key))
+                {
+                    best = v;
+                    key = k;
+                }
+        }
+    acq_block_reduce(best, key, dummy);
+    if (threadIdx.x == 0)
+        {
+            if (!(best > 0.0f))
+                {
+                    best = 0.0f;
+                    key = 0;
+                }
+            s_best = best;
+            s_key = key;
+        }
+    __syncthreads();
+    best = s_best;
+    key = s_key;
+    const int bin = key / p.neff, idx = key - bin * p.neff;
+    float denom = 0.0f;
+    if (p.use_cfar)
+        {
+            const int opp = (bin + p.n_bins / 2) % p.n_bins;  // :518
+            float s = 0.0f;
+            if (threadIdx.x == 0)
+                {
+                    for (int k = 0; k < p.n_parts; k++) s += c[opp * p.n_parts + k].sum;
+                    denom = (float)((double)(s / (float)p.neff) / 2.0 / p.num_dwells);  // :519 (float / int, then double)
+                }
+        }
+    else
+        {
+            // second peak of the winning bin outside +-samples_per_chip around the first (:565-593); the reference scans
+            // d_fft_size entries of which only the first neff are ever written, the rest are zero
+            const int nfull = p.plan.n;
+            int ex1 = idx - p.samples_per_chip, ex2 = idx + p.samples_per_chip;
+            if (ex1 < 0)
+                ex1 = nfull + ex1;
+            else if (ex2 >= nfull)
+                ex2 = ex2 - nfull;
+            const float* row = grid + ((size_t)slots[si] * p.n_bins + bin) * p.neff;
+            float b2 = -1.0f, d2 = 0.0f;
+            int i2 = 0x7fffffff;
+            for (int i = threadIdx.x; i < p.neff; i += blockDim.x)
+                {
+                    // excluded: the circular range [ex1, ex2) walked by the reference's do/while
+                    const bool excl = ex1 <= ex2 ? (i >= ex1 && i < ex2) : (i >= ex1 || i < ex2);
+                    const float v = excl ? 0.0f : row[i];
+                    if (v > b2)
+                        {
+                            b2 = v;
+                            i2 = i;
+                        }
+                }
+            acq_block_reduce(b2, i2, d2);
+            denom = b2;
+        }
+    if (threadIdx.x == 0)
+        {
+            gb200_acq_result r;
+            r.indext = (unsigned)idx;
+            r.doppler_index = bin;
+            r.doppler_hz = p.doppler_base + p.doppler_step * bin;
+            r.peak = best;
+            r.input_power = denom;
+            r.test_statistics = best / denom;
+            r.acq_delay_samples = fmodf((float)idx, p.samples_per_code);
+            r.acq_doppler_hz = (float)r.doppler_hz;
+            results[si] = r;
+        }
+}
+}  // namespace gb200

@@ -176,6 +176,11 @@ int gb200_acq_destroy(gb200_acq* h);
 int gb200_acq_set_local_code(gb200_acq* h, int slot, const gb200_cf32* code, int n_code);
 /* set_doppler_max/step/center + update_grid_doppler_wipeoffs — pcps_acquisition.cc:248-302 */
 int gb200_acq_set_doppler_grid(gb200_acq* h, int doppler_max, int doppler_step, int doppler_center);
+/* Doppler wipe-off law.  0 (default): the reference's — (cosf, sinf) of an fp32 phase accumulated by repeated addition
+ * (update_local_carrier :232-245 -> volk_gnsssdr_s32f_sincos_32fc_generic), so the magnitude grid matches the reference's
+ * to ~1e-6; 1: exact phase exp(-j*2*pi*f*n/fs) (about 1e-4 of the peak away from the reference's own table, and closer
+ * to the float64 truth). */
+int gb200_acq_set_wipeoff_mode(gb200_acq* h, int exact);
 int gb200_acq_num_doppler_bins(const gb200_acq* h);
 int gb200_acq_neff(const gb200_acq* h);
 /* One dwell of acquisition_core for every slot in `slots` (NULL = 0..n_slots-1): `iq_host` holds

@@ -76,7 +76,9 @@ def test_signal_like_input_many_channels():
     for c in range(nch):
         r64 = O.mc_real_codes_f64(ring[offs[c]:offs[c] + lens[c]], codes[c], shifts[c], remc[c], step[c], remcode[c], cstep[c], mimic_inc=True)
         assert rel_err(got[c], r64) < TOL, c
-        assert rel_err(got[c], ref[c]) < TOL, c
+        # noise-only input: the sequential fp32 reference is itself ~1e-4 from the float64 truth, and the GPU cannot be
+        # closer to it than it is to the truth (triangle inequality)
+        assert rel_err(got[c], ref[c]) < TOL + rel_err(ref[c], r64), c
     # replay is deterministic: same bits
     eng.enqueue(cmds)
     again = eng.collect()[:, :nt]
