@@ -149,6 +149,98 @@ def cpu_reference_tracking(budget_s=12.0):
     return {"value": value, "unit": "channel-Msps/s", "cores": cores, "kind": kind, "sample": sample}, secs
 
 
+ACQ_DMAX, ACQ_DSTEP, ACQ_PRNS = 10000, 250, 32
+
+
+def gps_code_sampled(chips, fs, n):
+    """gps_l1_ca_code_gen_complex_sampled (src/algorithms/libs/gps_sdr_signal_replica.cc:145-187): fp32 index law
+    aux = ts*(i+1)/tc, chip = int(aux + 1) - 1, last sample forced to the last chip; this fork puts the chips in the
+    imaginary part (:127-139)."""
+    f32 = np.float32
+    ts, tc = f32(1.0) / f32(fs), f32(1.0) / f32(1.023e6)
+    i = np.arange(n, dtype=np.float32)
+    aux = (ts * (i + f32(1.0))) / tc
+    k = (aux + f32(1.0)).astype(np.int64) - 1
+    k[-1] = 1022
+    return (1j * chips[k]).astype(np.complex64)
+
+
+def cpu_reference_acq(budget_s=10.0):
+    """CPU arm for acquisition: the oracle's restatement of acquisition_core (FFTW/VOLK are not in the reference tree, so the
+    FFT is the oracle's own mixed-radix C; kind = "port"), OpenMP over Doppler bins on all host cores."""
+    import _oracle as O
+    cores = os.cpu_count() or 1
+    n = N_BLK
+    conf = O.acq_conf(FS, n, n, ACQ_DMAX, ACQ_DSTEP, float(n), int(np.ceil(FS / 1.023e6)))
+    sig = iq_stream(n, seed=5)
+    fc = O.acq_set_local_code(conf, gps_code_sampled(gps_codes()[0], FS, n))
+    O.acq_dwell(conf, sig, fc, nthreads=cores)
+    t0 = time.perf_counter()
+    sweeps = 0
+    while time.perf_counter() - t0 < budget_s:
+        O.acq_dwell(conf, sig, fc, nthreads=cores)
+        sweeps += 1
+    secs = time.perf_counter() - t0
+    return {"value": sweeps * conf.num_doppler_bins / secs, "unit": "cells/s", "cores": cores, "kind": "port",
+            "sample": f"{sweeps} PRN sweeps x {conf.num_doppler_bins} Doppler bins, fft {n}, oracle C FFT (FFTW stand-in), OpenMP {cores} threads"}
+
+
+def run_acq(args, rank, world, local, dist, flush):
+    """C3 acquisition sweep on every rank (one antenna stream per GPU): 32 PRN x 80 Doppler bins, fft 25000, CFAR."""
+    import torch
+    from gnss_sim_receiver_b200 import _capi
+    from gnss_sim_receiver_b200.acquisition import AcquisitionEngine
+    lib = _capi.lib()
+    K, W = args.steps, max(args.warmup, 3)
+    n = N_BLK
+    eng = AcquisitionEngine(fs_in=FS, fft_size=n, samples_per_code=float(n), samples_per_chip=int(np.ceil(FS / 1.023e6)), max_prns=ACQ_PRNS, device=local)
+    eng.set_doppler_grid(ACQ_DMAX, ACQ_DSTEP)
+    codes = gps_codes()
+    for p in range(ACQ_PRNS):
+        eng.set_local_code(p, gps_code_sampled(codes[p], FS, n))
+    bins = eng.num_doppler_bins
+    pinned = torch.from_numpy(iq_stream((K + W) * n, seed=3 + rank)).pin_memory()
+    host = pinned.numpy()
+    e2e_t = 0.0
+    for i in range(K + W):
+        flush.zero_()
+        barrier(dist) if i == W else torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = eng.run(host[i * n:(i + 1) * n])
+        dt = time.perf_counter() - t0
+        if i >= W:
+            e2e_t += dt
+    e2e_t = reduce_max(dist, local, e2e_t)
+    for _ in range(W):
+        eng.replay(1)
+    barrier(dist)
+    l0 = lib.gb200_launch_count()
+    dev_ms = 0.0
+    for _ in range(K):
+        flush.zero_()
+        torch.cuda.synchronize()
+        dev_ms += eng.replay(1)
+    launches = lib.gb200_launch_count() - l0
+    dev_ms = reduce_max(dist, local, dev_ms)
+    eng.close()
+    if rank != 0:
+        return None
+    cells = ACQ_PRNS * bins * world
+    hbm, _, which = peaks()
+    per_gpu_cells_s = ACQ_PRNS * bins / (dev_ms / K / 1e3)
+    bytes_per_cell = 16 * n  # SURVEY 8d: fc32 input 8N + conj code spectrum 8N, single dwell
+    achieved = per_gpu_cells_s * bytes_per_cell / 1e9
+    return {
+        "metric": "acq PRNxDoppler cells/s", "value": cells * K / (dev_ms / 1e3), "unit": "cells/s", "ms_per_sweep": dev_ms / K,
+        "config": {"workload": f"C3 acquisition sweep: GPS L1 C/A {FS / 1e6:g} MS/s gr_complex, fft {n}, {ACQ_PRNS} PRN x {bins} Doppler bins (+-{ACQ_DMAX} Hz / {ACQ_DSTEP} Hz), CFAR, 1 dwell, one sweep per GPU"},
+        "e2e": {"value": cells * K / e2e_t, "unit": "cells/s", "h2d_bytes_per_step": n * 8, "d2h_bytes_per_step": ACQ_PRNS * C.sizeof(_capi.AcqResult)},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
+                     "note": f"algorithmic bytes per cell = 16*N = {bytes_per_cell} (SURVEY 8d); peak = {which} HBM copy bandwidth"},
+        "cpu_baseline": cpu_reference_acq(8.0),
+    }
+
+
 def dist_setup(n_gpus):
     """One process per GPU (torchrun env) — torch.distributed is plumbing for the barrier and the max over ranks."""
     rank = int(os.environ.get("RANK", "0"))
@@ -240,6 +332,8 @@ def run_ours(args):
     dev_ms = reduce_max(dist, local, dev_ms)
     sustained_ms = reduce_max(dist, local, sustained_ms)
     clocks = sampler.summary() if rank == 0 else None
+    eng.close()
+    acq = run_acq(args, rank, world, local, dist, flush)
     ch_samples_per_step = float(np.sum(w["len"])) * world
     value = ch_samples_per_step * K / 1e6 / (dev_ms / 1e3)
     e2e_value = ch_samples_per_step * K / 1e6 / e2e_t
@@ -260,7 +354,7 @@ def run_ours(args):
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak, "traffic": None,
                      "note": f"FP32-FMA pipe roofline (SURVEY 8d): {FLOP_PER_CH_SAMPLE} flop per channel-sample; peak = 148 SM x 128 lanes x 2 x sm_max_mhz ({which}); kernel moves ~0 HBM bytes per unit",
                      "sustained_ms_per_step": sustained_ms},
-        "cpu_baseline": cpu, "clocks": clocks,
+        "cpu_baseline": cpu, "clocks": clocks, "acq": acq,
     }
     print(json.dumps(line))
 
