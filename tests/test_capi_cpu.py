@@ -1,0 +1,72 @@
+"""CPU-side checks of the drop-in boundary (no compute calls without a GPU):
+the C-ABI library loads, exports every symbol include/gnss_b200.h declares, fails loudly without a device, and the
+product never touches oracle/."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "gnss_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gb200_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_library_and_binding_agree(capi):
+    names = _declared()
+    assert len(names) >= 28
+    lib = capi.lib()
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/gnss_b200.h but not exported by libgnss_b200.so"
+    assert sorted(capi.SYMBOLS) == names, set(capi.SYMBOLS) ^ set(names)
+    out = subprocess.run(["nm", "-D", "--defined-only", capi.LIB_PATH], capture_output=True, text=True).stdout
+    exported = set(re.findall(r" T (gb200_[a-z0-9_]+)", out))
+    assert set(names) <= exported
+
+
+def test_struct_layouts_match_header(capi):
+    assert C.sizeof(capi.TrkConfig) == 32 and C.sizeof(capi.TrkCmd) == 112
+    assert C.sizeof(capi.AcqConfig) == 48 and C.sizeof(capi.AcqResult) == 32
+    assert capi.TrkCmd.sample_offset.offset == 16 and capi.TrkCmd.shifts_chips.offset == 48
+
+
+def test_sass_is_sm100a_only(capi):
+    out = subprocess.run(["cuobjdump", "-lelf", capi.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_(\d+a?)", out))
+    assert archs == {"100a"}, archs
+
+
+def test_no_device_is_a_loud_error_not_a_fallback(capi):
+    lib = capi.lib()
+    if lib.gb200_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    h = C.c_void_p()
+    cfg = capi.TrkConfig(0, 4, 1023, 0, 1 << 16, 1 << 14, 4)
+    assert lib.gb200_trk_create(C.byref(cfg), C.byref(h)) == -2  # GB200_ENODEVICE
+    assert b"no CPU fallback" in lib.gb200_last_error()
+    acfg = capi.AcqConfig(0, 0, 4000, 4000, 0, 1, 4, 1, 4, 4000.0, 4e6)
+    assert lib.gb200_acq_create(C.byref(acfg), C.byref(h)) == -2
+    with pytest.raises(capi.GB200Error):
+        from gnss_sim_receiver_b200.tracking import TrackingEngine
+        TrackingEngine()
+
+
+def test_product_never_references_the_oracle():
+    pkg = os.path.join(ROOT, "gnss_sim_receiver_b200")
+    bad = []
+    for dp, _, fs in os.walk(pkg):
+        if os.path.basename(dp) == "build":
+            continue
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".inc", ".h", ".cc", ".cpp", ".hpp")) or f == "Makefile":
+                txt = open(os.path.join(dp, f), errors="replace").read()
+                if re.search(r"liboracle|libgnssref|_oracle\b|oracle/", txt) and f != "__init__.py":
+                    bad.append(os.path.join(dp, f))
+    assert not bad, bad
+    hdr = open(os.path.join(ROOT, "include", "gnss_b200.h")).read()
+    assert "oracle" not in hdr
