@@ -56,6 +56,7 @@ SYMBOLS = {
     "gb200_trk_enqueue": (C.c_int, [_vp, _vp, C.c_int]),
     "gb200_trk_collect": (C.c_int, [_vp, _vp]),
     "gb200_trk_replay": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
+    "gb200_trk_last_kernel": (C.c_char_p, [_vp]),
     "gb200_acq_create": (C.c_int, [C.POINTER(AcqConfig), C.POINTER(_vp)]),
     "gb200_acq_destroy": (C.c_int, [_vp]),
     "gb200_acq_set_local_code": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),

@@ -1,5 +1,5 @@
 // Tracking multicorrelator engine: C ABI (include/gnss_b200.h) over trk_kernel.cuh.
-#include "trk_kernel.cuh"
+#include "trk_kernel2.cuh"
 #include <algorithm>
 #include <cmath>
 #include <complex>
@@ -31,6 +31,9 @@ struct gb200_trk
     float* d_partials{nullptr};
     unsigned* d_counters{nullptr};
     size_t partial_ctas{0};
+    TrkGroup* h_groups{nullptr};  // pinned
+    TrkGroup* d_groups{nullptr};
+    int last_path{0}, last_groups{0}, last_R{16}, last_G{4};  // path 0: chunked kernel, 1: run-based kernel
     // last enqueued launch (for collect / replay)
     int last_n{0}, last_T{0}, last_chunks{0}, last_cplx{0};
     size_t last_smem{0};
@@ -41,6 +44,7 @@ struct gb200_trk
 namespace
 {
 constexpr double TWO_PI = 6.283185307179586476925286766559;
+constexpr int RING_SLACK = 4096;
 
 // fraction of a turn in [0,1) -> 64-bit fixed point
 inline unsigned long long turns_to_fix(double turns)
@@ -87,8 +91,49 @@ int padded_taps(int t)
     return 16;
 }
 
+template <int T, int IQ, int R, int G>
+cudaError_t launch_run_one(gb200_trk* h)
+{
+    constexpr int EB = IqRow<IQ>::EB;
+    const size_t smem = 2 * (size_t)TRK2_THREADS * (R * EB + 16) + (size_t)(R + 1) * TRK2_THREADS * sizeof(float2) + (size_t)G * TRK2_TAB * sizeof(float2);
+    cudaError_t e = cudaFuncSetAttribute(trk_run_kernel<T, IQ, R, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    trk_run_kernel<T, IQ, R, G><<<h->last_groups, TRK2_THREADS, smem, h->stream>>>(h->d_cmds, h->d_groups, reinterpret_cast<const unsigned char*>(h->d_ring), h->d_out);
+    count_launch();
+    return cudaGetLastError();
+}
+
+template <int T, int IQ>
+cudaError_t launch_run_RG(gb200_trk* h)
+{
+    if (h->last_R == 16) return h->last_G == 4 ? launch_run_one<T, IQ, 16, 4>(h) : launch_run_one<T, IQ, 16, 1>(h);
+    return h->last_G == 4 ? launch_run_one<T, IQ, 8, 4>(h) : launch_run_one<T, IQ, 8, 1>(h);
+}
+
+template <int IQ>
+cudaError_t launch_run_T(gb200_trk* h)
+{
+    switch (h->last_T)
+        {
+        case 3: return launch_run_RG<3, IQ>(h);
+        case 5: return launch_run_RG<5, IQ>(h);
+        default: return launch_run_RG<11, IQ>(h);
+        }
+}
+
+cudaError_t launch_run(gb200_trk* h)
+{
+    switch (h->cfg.iq_dtype)
+        {
+        case GB200_IQ_CF32: return launch_run_T<GB200_IQ_CF32>(h);
+        case GB200_IQ_CS16: return launch_run_T<GB200_IQ_CS16>(h);
+        default: return launch_run_T<GB200_IQ_CS8>(h);
+        }
+}
+
 cudaError_t launch(gb200_trk* h)
 {
+    if (h->last_path == 1) return launch_run(h);
     const int T = h->last_T, n = h->last_n, ch = h->last_chunks;
     const size_t sm = h->last_smem;
     if (h->last_cplx)
@@ -133,8 +178,11 @@ int gb200_trk_create(const gb200_trk_config* cfg, gb200_trk** out)
     GB_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     GB_CUDA(cudaEventCreate(&h->ev0));
     GB_CUDA(cudaEventCreate(&h->ev1));
-    GB_CUDA(cudaMalloc(&h->d_ring, (size_t)(cfg->ring_samples + cfg->max_block) * h->elem_bytes));
-    GB_CUDA(cudaMemsetAsync(h->d_ring, 0, (size_t)(cfg->ring_samples + cfg->max_block) * h->elem_bytes, h->stream));
+    // + RING_SLACK: the run-based kernel stages whole tiles, which may extend past the last window (masked, but must be mapped)
+    GB_CUDA(cudaMalloc(&h->d_ring, (size_t)(cfg->ring_samples + cfg->max_block + RING_SLACK) * h->elem_bytes));
+    GB_CUDA(cudaMemsetAsync(h->d_ring, 0, (size_t)(cfg->ring_samples + cfg->max_block + RING_SLACK) * h->elem_bytes, h->stream));
+    GB_CUDA(cudaMallocHost(&h->h_groups, (size_t)cfg->max_cmds * sizeof(TrkGroup)));
+    GB_CUDA(cudaMalloc(&h->d_groups, (size_t)cfg->max_cmds * sizeof(TrkGroup)));
     GB_CUDA(cudaMalloc(&h->d_codes, (size_t)cfg->max_channels * cfg->max_code_len * sizeof(float2)));
     h->code_len.assign(cfg->max_channels, 0);
     h->code_cplx.assign(cfg->max_channels, 0);
@@ -165,6 +213,8 @@ int gb200_trk_destroy(gb200_trk* h)
     cudaFreeHost(h->h_out);
     cudaFree(h->d_partials);
     cudaFree(h->d_counters);
+    cudaFreeHost(h->h_groups);
+    cudaFree(h->d_groups);
     cudaEventDestroy(h->ev0);
     cudaEventDestroy(h->ev1);
     cudaStreamDestroy(h->stream);

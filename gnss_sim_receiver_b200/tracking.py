@@ -105,6 +105,10 @@ class TrackingEngine:
         check(self._lib.gb200_trk_collect(self._h, out.ctypes.data))
         return out
 
+    @property
+    def last_kernel(self):
+        return self._lib.gb200_trk_last_kernel(self._h).decode()
+
     def replay(self, iters):
         ms = C.c_float()
         check(self._lib.gb200_trk_replay(self._h, iters, C.byref(ms)))

@@ -128,6 +128,9 @@ int gb200_trk_collect(gb200_trk* h, gb200_cf32* out);
 /* Re-launch the most recently enqueued command set `iters` times with inputs and commands
  * resident on the device; *ms_per_iter = CUDA-event time / iters on the engine's stream. */
 int gb200_trk_replay(gb200_trk* h, int iters, float* ms_per_iter);
+/* name of the kernel variant the last enqueue selected (diagnostics / bench reporting), e.g.
+ * "trk_correlate_kernel<T=11,chunks=2>" or "trk_run_kernel<T=11,R=16,G=4>" */
+const char* gb200_trk_last_kernel(const gb200_trk* h);
 
 /* ======================================================================
  * PCPS acquisition engine
