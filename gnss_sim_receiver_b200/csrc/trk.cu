@@ -46,6 +46,12 @@ namespace
 constexpr double TWO_PI = 6.283185307179586476925286766559;
 constexpr int RING_SLACK = 4096;
 
+// samples per run of the run-based kernel for a sample type (long / short variant)
+constexpr int trk_run_len(int iq, bool long_run)
+{
+    return iq == GB200_IQ_CF32 ? (long_run ? 18 : 10) : iq == GB200_IQ_CS16 ? (long_run ? 20 : 12) : (long_run ? 24 : 8);
+}
+
 // fraction of a turn in [0,1) -> 64-bit fixed point
 inline unsigned long long turns_to_fix(double turns)
 {
@@ -91,23 +97,37 @@ int padded_taps(int t)
     return 16;
 }
 
-template <int T, int IQ, int R, int G>
+template <int T, int IQ, int CH, int G>
 cudaError_t launch_run_one(gb200_trk* h)
 {
     constexpr int EB = IqRow<IQ>::EB;
-    const size_t smem = 2 * (size_t)TRK2_THREADS * (R * EB + 16) + (size_t)(R + 1) * TRK2_THREADS * sizeof(float2) + (size_t)G * TRK2_TAB * sizeof(float2);
-    cudaError_t e = cudaFuncSetAttribute(trk_run_kernel<T, IQ, R, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    constexpr int R = CH * 16 / EB;
+    const size_t smem = (size_t)TRK2_THREADS * R * EB + (size_t)(R + 2) * TRK2_THREADS * sizeof(float2) + (size_t)G * TRK2_TAB * sizeof(float2);
+    cudaError_t e = cudaFuncSetAttribute(trk_run_kernel<T, IQ, CH, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    trk_run_kernel<T, IQ, R, G><<<h->last_groups, TRK2_THREADS, smem, h->stream>>>(h->d_cmds, h->d_groups, reinterpret_cast<const unsigned char*>(h->d_ring), h->d_out);
+    trk_run_kernel<T, IQ, CH, G><<<h->last_groups, TRK2_THREADS, smem, h->stream>>>(h->d_cmds, h->d_groups, reinterpret_cast<const unsigned char*>(h->d_ring), h->d_out);
     count_launch();
     return cudaGetLastError();
 }
 
+template <int T, int IQ, int CH>
+cudaError_t launch_run_G(gb200_trk* h)
+{
+    switch (h->last_G)
+        {
+        case 4: return launch_run_one<T, IQ, CH, 4>(h);
+        case 2: return launch_run_one<T, IQ, CH, 2>(h);
+        default: return launch_run_one<T, IQ, CH, 1>(h);
+        }
+}
+
+// run lengths: an odd number of 16-byte chunks (see trk_kernel2.cuh); long and short variant per sample type
 template <int T, int IQ>
 cudaError_t launch_run_RG(gb200_trk* h)
 {
-    if (h->last_R == 16) return h->last_G == 4 ? launch_run_one<T, IQ, 16, 4>(h) : launch_run_one<T, IQ, 16, 1>(h);
-    return h->last_G == 4 ? launch_run_one<T, IQ, 8, 4>(h) : launch_run_one<T, IQ, 8, 1>(h);
+    constexpr int CH_LONG = IQ == GB200_IQ_CF32 ? 9 : IQ == GB200_IQ_CS16 ? 5 : 3;
+    constexpr int CH_SHORT = IQ == GB200_IQ_CF32 ? 5 : IQ == GB200_IQ_CS16 ? 3 : 1;
+    return h->last_R == trk_run_len(IQ, true) ? launch_run_G<T, IQ, CH_LONG>(h) : launch_run_G<T, IQ, CH_SHORT>(h);
 }
 
 template <int IQ>

@@ -1,13 +1,15 @@
 // Tracking multicorrelator, run-based kernel (K1b) for sm_100a — used when the code advances by less than one table entry
-// over a run of R samples (R * code_step <= 0.9: e.g. GPS L1 at >= 10 MS/s, Galileo E1 at >= 20 MS/s).
+// over a run of R samples (R * code_step <= 0.9: e.g. GPS L1 at >= 12 MS/s, Galileo E1 at >= 25 MS/s).
 //
 // Same contract as trk_kernel.cuh (Cpu_Multicorrelator_Real_Codes::Carrier_wipeoff_multicorrelator_resampler,
 // src/algorithms/tracking/libs/cpu_multicorrelator_real_codes.cc:103-126), different work decomposition:
 //   * a CTA owns a GROUP of up to G commands whose windows overlap in the IQ ring and walks the ring tile by tile; each
-//     tile (128 rows of R samples) is staged ONCE into shared memory by TMA bulk copies (cp.async.bulk + mbarrier, two stages)
-//     and shared by the G commands and all their taps;
-//   * a thread owns one run of R consecutive samples: it wipes the carrier off once, keeps the R prefix sums of the wiped
-//     samples, and for every tap finds the single chip boundary inside the run, so a tap costs O(1) per run instead of O(R):
+//     tile (128 runs of R samples, contiguous) is staged ONCE into shared memory by one TMA bulk copy (cp.async.bulk +
+//     mbarrier) and shared by the G commands and all their taps.  R is chosen so that a run is an ODD number of 16-byte
+//     chunks (cf32: 18 or 10 samples, int16: 20 or 12, int8: 24 or 8): consecutive threads' runs then start in different
+//     bank groups and the per-thread 128-bit reads of the plain contiguous tile are conflict-free without padding;
+//   * a thread owns one run: it wipes the carrier off once, keeps the R prefix sums of the wiped samples, and for every
+//     tap finds the single chip boundary inside the run, so a tap costs O(1) per run instead of O(R):
 //       out_t += c[idx] * P[k_t] + c[idx+1] * (S - P[k_t])
 //     where k_t = number of samples of the run that still see table entry idx.  k_t comes from the reference's exact fp32
 //     index law (volk_gnsssdr_32f_xn_resampler_32f_xn.h:73): an estimate from the fractional distance to the next integer,
@@ -16,6 +18,7 @@
 //   * accumulators stay in registers across all tiles of a command: one block reduce per command, no cross-CTA partials.
 #pragma once
 #include "trk_kernel.cuh"
+#include <type_traits>
 
 namespace gb200
 {
@@ -50,68 +53,97 @@ struct IqRow<GB200_IQ_CS8>
     static constexpr int EB = 2;
 };
 
-// sample i of a staged row -> float2
+// one 16-byte chunk of a staged run -> 16/EB complex samples
 template <int IQ>
-__device__ __forceinline__ float2 trk2_row_sample(const unsigned char* row, int i)
+__device__ __forceinline__ void trk2_unpack(const uint4 v, float2* x)
 {
-    if (IQ == GB200_IQ_CF32) return reinterpret_cast<const float2*>(row)[i];
-    if (IQ == GB200_IQ_CS16)
+    if (IQ == GB200_IQ_CF32)
         {
-            const short2 v = reinterpret_cast<const short2*>(row)[i];
-            return make_float2((float)v.x, (float)v.y);
+            x[0] = make_float2(__uint_as_float(v.x), __uint_as_float(v.y));
+            x[1] = make_float2(__uint_as_float(v.z), __uint_as_float(v.w));
         }
-    const char2 v = reinterpret_cast<const char2*>(row)[i];
-    return make_float2((float)v.x, (float)v.y);
+    else if (IQ == GB200_IQ_CS16)
+        {
+            const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int i = 0; i < 4; i++) x[i] = make_float2((float)(short)(w[i] & 0xffffu), (float)(short)(w[i] >> 16));
+        }
+    else
+        {
+            const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                {
+                    x[2 * i] = make_float2((float)(signed char)(w[i] & 0xffu), (float)(signed char)((w[i] >> 8) & 0xffu));
+                    x[2 * i + 1] = make_float2((float)(signed char)((w[i] >> 16) & 0xffu), (float)(signed char)(w[i] >> 24));
+                }
+        }
 }
 
-template <int T, int IQ, int R, int G>
+template <int T>
+struct Trk2Cmd  // per-command constants, staged once per CTA
+{
+    unsigned long long u0, du;
+    long long ws;
+    const float* code;
+    float2 inc;
+    float step, rem, inv_step, shift_min;
+    int n, L, out_index, pad_;
+    float sh[T];
+};
+
+// T taps, IQ sample type, CH = 16-byte chunks per run (odd), G = commands per group
+template <int T, int IQ, int CH, int G>
 __global__ void __launch_bounds__(TRK2_THREADS) trk_run_kernel(const TrkDevCmd* __restrict__ cmds, const TrkGroup* __restrict__ groups,
     const unsigned char* __restrict__ ring, float* __restrict__ out)
 {
     constexpr int EB = IqRow<IQ>::EB;
-    constexpr int ROW_BYTES = R * EB;
-    constexpr int ROW_STRIDE = ROW_BYTES + 16;  // padding keeps the per-thread 128-bit row reads conflict-free
+    constexpr int SPC = 16 / EB;  // samples per chunk
+    constexpr int R = CH * SPC;   // samples per run
     constexpr int TILE = TRK2_THREADS * R;
-    constexpr int STAGE_BYTES = TRK2_THREADS * ROW_STRIDE;
+    constexpr int TILE_BYTES = TILE * EB;
     constexpr float MAGIC = 12582912.0f;
+    constexpr int MAGICBITS = 0x4B400000;
 
     extern __shared__ __align__(128) unsigned char smem[];
-    unsigned char* s_rows = smem;                                                    // 2 stages
-    float2* s_prefix = reinterpret_cast<float2*>(smem + 2 * STAGE_BYTES);             // [R + 1][128]
-    float2* s_tab = s_prefix + (R + 1) * TRK2_THREADS;                               // [G][TRK2_TAB] (c[j], c[j+1])
-    __shared__ __align__(8) uint64_t s_bar[2];
+    const uint4* s_rows = reinterpret_cast<const uint4*>(smem);
+    float2* s_prefix = reinterpret_cast<float2*>(smem + TILE_BYTES);  // [R + 2][128]
+    float2* s_tab = s_prefix + (R + 2) * TRK2_THREADS;               // [G][TRK2_TAB] (c[j], c[j+1])
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ Trk2Cmd<T> s_cmd[G];
     __shared__ float s_red[TRK2_THREADS / 32][2 * T];
 
     const TrkGroup& grp = groups[blockIdx.x];
     const int tid = threadIdx.x;
     const int n_tiles = grp.n_tiles;
+    const int n_g = grp.n_cmds;
 
     if (tid == 0)
         {
-            mbar_init(&s_bar[0], 1);
-            mbar_init(&s_bar[1], 1);
+            mbar_init(&s_bar, 1);
             fence_barrier_init();
+        }
+    if (tid < n_g)
+        {
+            const TrkDevCmd& c = cmds[grp.cmd[tid]];
+            Trk2Cmd<T>& s = s_cmd[tid];
+            s.u0 = c.u0;
+            s.du = c.du;
+            s.ws = grp.ws[tid];
+            s.code = reinterpret_cast<const float*>(c.code);
+            s.inc = trk_phasor(c.du);
+            s.step = c.code_step;
+            s.rem = c.rem_code;
+            s.inv_step = __frcp_rn(c.code_step);
+            s.shift_min = c.shift_min;
+            s.n = c.n;
+            s.L = c.L;
+            s.out_index = grp.cmd[tid];
+#pragma unroll
+            for (int t = 0; t < T; t++) s.sh[t] = c.shifts[t];
         }
     s_prefix[tid] = make_float2(0.0f, 0.0f);  // P[0]
     __syncthreads();
-
-    auto issue_tile = [&](int tile, int stage) {
-        if (tid == 0) mbar_expect_tx(&s_bar[stage], TRK2_THREADS * ROW_BYTES);
-        __syncwarp();
-        // every thread copies its own row: global is contiguous, shared is padded
-        const unsigned char* src = ring + ((size_t)grp.tile0 + (size_t)tile * TILE + (size_t)tid * R) * EB;
-        bulk_g2s(s_rows + stage * STAGE_BYTES + tid * ROW_STRIDE, src, ROW_BYTES, &s_bar[stage]);
-    };
-    // thread 0's expect_tx must precede the copies of other warps: order with a barrier on the first issues only
-    if (n_tiles > 0)
-        {
-            if (tid == 0) mbar_expect_tx(&s_bar[0], TRK2_THREADS * ROW_BYTES);
-            if (n_tiles > 1 && tid == 0) mbar_expect_tx(&s_bar[1], TRK2_THREADS * ROW_BYTES);
-            __syncthreads();
-            const unsigned char* src = ring + ((size_t)grp.tile0 + (size_t)tid * R) * EB;
-            bulk_g2s(s_rows + tid * ROW_STRIDE, src, ROW_BYTES, &s_bar[0]);
-            if (n_tiles > 1) bulk_g2s(s_rows + STAGE_BYTES + tid * ROW_STRIDE, src + (size_t)TILE * EB, ROW_BYTES, &s_bar[1]);
-        }
 
     float acc_re[G][T], acc_im[G][T];
 #pragma unroll
@@ -121,100 +153,117 @@ __global__ void __launch_bounds__(TRK2_THREADS) trk_run_kernel(const TrkDevCmd* 
 
     for (int tile = 0; tile < n_tiles; tile++)
         {
-            const int stage = tile & 1;
-            // ---- code-pair windows of this tile for every command of the group
+            const long long tile_start = grp.tile0 + (long long)tile * TILE;
+            if (tid == 0)
+                {
+                    mbar_expect_tx(&s_bar, TILE_BYTES);
+                    bulk_g2s(smem, ring + (size_t)tile_start * EB, TILE_BYTES, &s_bar);
+                }
+            // ---- code-pair windows of this tile for every command of the group (overlaps the copy)
             int bias[G];
 #pragma unroll
             for (int g = 0; g < G; g++)
                 {
                     bias[g] = 0;
-                    if (g < grp.n_cmds)
+                    if (g < n_g)
                         {
-                            const TrkDevCmd& c = cmds[grp.cmd[g]];
-                            const long long n0 = grp.tile0 + (long long)tile * TILE - grp.ws[g];  // sample index of the tile's first sample
+                            const Trk2Cmd<T>& c = s_cmd[g];
+                            const long long n0 = tile_start - c.ws;  // sample index of the tile's first sample
                             if (n0 < c.n && n0 + TILE > 0)
                                 {
                                     const float nlo = (float)max(n0, (long long)-R);
-                                    const int idx_lo = trk_raw_index(c.code_step, nlo, c.shift_min, c.rem_code);
-                                    bias[g] = 0x4B400000 + idx_lo;
-                                    int k = math_mod(idx_lo + tid, c.L);
-                                    const int adv = TRK2_THREADS % c.L;
-                                    const float* code = reinterpret_cast<const float*>(c.code);
+                                    const int idx_lo = trk_raw_index(c.step, nlo, c.shift_min, c.rem);
+                                    bias[g] = MAGICBITS + idx_lo;
+                                    const int L = c.L;
+                                    int k = math_mod(idx_lo + tid, L);
+                                    const int adv = TRK2_THREADS % L;
                                     for (int j = tid; j < TRK2_TAB; j += TRK2_THREADS)
                                         {
-                                            const int k1 = (k + 1 == c.L) ? 0 : k + 1;
-                                            s_tab[g * TRK2_TAB + j] = make_float2(__ldg(code + k), __ldg(code + k1));
+                                            const int k1 = (k + 1 == L) ? 0 : k + 1;
+                                            s_tab[g * TRK2_TAB + j] = make_float2(__ldg(c.code + k), __ldg(c.code + k1));
                                             k += adv;
-                                            if (k >= c.L) k -= c.L;
+                                            if (k >= L) k -= L;
                                         }
                                 }
                         }
                 }
-            mbar_wait(&s_bar[stage], (tile >> 1) & 1);
+            mbar_wait(&s_bar, tile & 1);
             __syncthreads();
-            const unsigned char* row = s_rows + stage * STAGE_BYTES + tid * ROW_STRIDE;
+            const uint4* row = s_rows + tid * CH;
 #pragma unroll
             for (int g = 0; g < G; g++)
                 {
-                    if (g >= grp.n_cmds) continue;
-                    const TrkDevCmd& c = cmds[grp.cmd[g]];
-                    const long long n0 = grp.tile0 + (long long)tile * TILE - grp.ws[g];
-                    const long long nr_ll = n0 + (long long)tid * R;
-                    if (nr_ll + R <= 0 || nr_ll >= c.n) continue;  // run outside the window
-                    const int nr = (int)nr_ll;
+                    if (g >= n_g) continue;
+                    const Trk2Cmd<T>& c = s_cmd[g];
+                    const long long nr_ll = tile_start - c.ws + (long long)tid * R;
                     const int n = c.n;
-                    const float step = c.code_step, rem = c.rem_code;
+                    if (nr_ll + R <= 0 || nr_ll >= n) continue;  // run outside the window
+                    const int nr = (int)nr_ll;
                     // ---- carrier wipe-off + prefix sums of the run
                     float2 ph = trk_phasor(c.u0 + c.du * (unsigned long long)(long long)nr);
-                    const float2 inc = trk_phasor(c.du);
+                    const float2 inc = c.inc;
                     float2 P = make_float2(0.0f, 0.0f);
-                    const bool full = nr >= 0 && nr + R <= n;
+                    auto wipe = [&](auto full_tag) {
+                        constexpr bool FULL = decltype(full_tag)::value;
 #pragma unroll
-                    for (int i = 0; i < R; i++)
-                        {
-                            float2 x = trk2_row_sample<IQ>(row, i);
-                            if (!full && (nr + i < 0 || nr + i >= n)) x = make_float2(0.0f, 0.0f);
-                            P.x += x.x * ph.x - x.y * ph.y;
-                            P.y += x.x * ph.y + x.y * ph.x;
-                            const float pr = ph.x * inc.x - ph.y * inc.y;
-                            ph.y = ph.x * inc.y + ph.y * inc.x;
-                            ph.x = pr;
-                            s_prefix[(i + 1) * TRK2_THREADS + tid] = P;
-                        }
-                    // ---- taps: one chip boundary per run at most
+                        for (int ch = 0; ch < CH; ch++)
+                            {
+                                float2 x[SPC];
+                                trk2_unpack<IQ>(row[ch], x);
+#pragma unroll
+                                for (int j = 0; j < SPC; j++)
+                                    {
+                                        const int i = ch * SPC + j;
+                                        if (!FULL && (nr + i < 0 || nr + i >= n)) x[j] = make_float2(0.0f, 0.0f);
+                                        P.x += x[j].x * ph.x - x[j].y * ph.y;
+                                        P.y += x[j].x * ph.y + x[j].y * ph.x;
+                                        const float pr = ph.x * inc.x - ph.y * inc.y;
+                                        ph.y = ph.x * inc.y + ph.y * inc.x;
+                                        ph.x = pr;
+                                        s_prefix[(i + 1) * TRK2_THREADS + tid] = P;
+                                    }
+                            }
+                    };
+                    if (nr >= 0 && nr + R <= n)
+                        wipe(std::true_type{});
+                    else
+                        wipe(std::false_type{});
+                    s_prefix[(R + 1) * TRK2_THREADS + tid] = P;  // k = R + 1 reads the same total: no clamp in the tap loop
+                    // ---- taps: at most one table-entry boundary per run
                     const float nf = (float)nr;
+                    const float nfm = nf - MAGIC;  // exact
+                    const float step = c.step, rem = c.rem, inv_step = c.inv_step;
                     const float a0 = __fmul_rn(step, nf);
-                    const float inv_step = __frcp_rn(step);
                     const float2* tab = s_tab + g * TRK2_TAB;
+                    const int tab_bias = bias[g];
 #pragma unroll
                     for (int t = 0; t < T; t++)
                         {
-                            const float sh = c.shifts[t];
-                            const float x0 = __fsub_rn(__fadd_rn(a0, sh), rem);
-                            const float m0 = __fadd_rd(x0, MAGIC);  // mantissa holds floor(x0)
+                            const float sh = c.sh[t];
+                            const float x0 = __fsub_rn(__fadd_rn(a0, sh), rem);                 // the reference's law at the run start
+                            const float m0 = __fadd_rd(x0, MAGIC);                             // mantissa holds floor(x0)
                             const float fl = __fsub_rn(m0, MAGIC);
-                            const float frac = __fsub_rn(__fadd_rn(fl, 1.0f), x0);  // distance to the next table entry, (0, 1]
-                            const float kq = fminf(__fsub_rn(__fadd_rn(frac * inv_step, MAGIC), MAGIC), (float)R);  // min(rint(estimate), R)
-                            const float xq = __fsub_rn(__fadd_rn(__fmul_rn(step, nf + kq), sh), rem);  // the exact law at the candidate
+                            const float dn = fmaf(__fsub_rn(fl, x0), inv_step, inv_step);       // samples until the next table entry
+                            const float kqm = fminf(__fadd_rn(dn, MAGIC), MAGIC + (float)R);    // MAGIC + min(rint(dn), R)
+                            const float nfq = __fadd_rn(kqm, nfm);                             // nf + kq, exact
+                            const float xq = __fsub_rn(__fadd_rn(__fmul_rn(step, nfq), sh), rem);  // the law at the candidate
                             const float mq = __fadd_rd(xq, MAGIC);
-                            int k = (int)kq + (__float_as_int(mq) > __float_as_int(m0) ? 0 : 1);
-                            k = min(k, R);
-                            const float2 cc = tab[__float_as_int(m0) - bias[g]];
-                            const float2 Pk = s_prefix[k * TRK2_THREADS + tid];
+                            const int kb = __float_as_int(kqm) + (__float_as_int(mq) > __float_as_int(m0) ? 0 : 1);
+                            const float2 cc = tab[__float_as_int(m0) - tab_bias];
+                            const float2 Pk = s_prefix[(kb - MAGICBITS) * TRK2_THREADS + tid];
                             const float d = cc.x - cc.y;
                             acc_re[g][t] += cc.y * P.x + d * Pk.x;
                             acc_im[g][t] += cc.y * P.y + d * Pk.y;
                         }
                 }
-            __syncthreads();  // rows of this stage and the code windows are free again
-            if (tile + 2 < n_tiles) issue_tile(tile + 2, stage);
+            __syncthreads();  // the tile and the code windows are free again
         }
 
     // ---- one block reduce per command
 #pragma unroll
     for (int g = 0; g < G; g++)
         {
-            if (g >= grp.n_cmds) break;
+            if (g >= n_g) break;
 #pragma unroll
             for (int t = 0; t < T; t++)
                 {
@@ -240,7 +289,7 @@ __global__ void __launch_bounds__(TRK2_THREADS) trk_run_kernel(const TrkDevCmd* 
                     float v = 0.0f;
 #pragma unroll
                     for (int w = 0; w < TRK2_THREADS / 32; w++) v += s_red[w][tid];
-                    out[(size_t)grp.cmd[g] * (2 * TRK_OUT_STRIDE) + tid] = v;
+                    out[(size_t)s_cmd[g].out_index * (2 * TRK_OUT_STRIDE) + tid] = v;
                 }
             __syncthreads();
         }
