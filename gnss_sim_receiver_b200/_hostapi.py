@@ -1,0 +1,191 @@
+"""ctypes binding of the host C++ layer's C door (gnss_sim_receiver_b200/host/b200_host_capi.h, libgnss_b200_host.so).
+
+Plumbing for tests/ and bench.py.  The library is built in-tree by gnss_sim_receiver_b200/host/Makefile; a missing
+library raises ImportError with the build command.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _capi
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgnss_b200_host.so")
+
+
+class TrkRecord(C.Structure):
+    _fields_ = [("channel", C.c_int32), ("prn", C.c_uint32), ("valid", C.c_int32), ("correlation_length_ms", C.c_int32),
+                ("prompt_i", C.c_double), ("prompt_q", C.c_double), ("cn0_db_hz", C.c_double), ("carrier_doppler_hz", C.c_double),
+                ("carrier_phase_rads", C.c_double), ("code_phase_samples", C.c_double), ("tracking_sample_counter", C.c_uint64)]
+
+
+class AcqStatus(C.Structure):
+    _fields_ = [("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double), ("acq_samplestamp_samples", C.c_uint64),
+                ("test_statistics", C.c_float), ("threshold", C.c_float), ("mag", C.c_float), ("input_power", C.c_float),
+                ("state", C.c_int32), ("active", C.c_int32), ("last_event", C.c_int32), ("indext", C.c_uint32), ("doppler_index", C.c_int32)]
+
+
+REC_DTYPE = np.dtype([("channel", "<i4"), ("prn", "<u4"), ("valid", "<i4"), ("correlation_length_ms", "<i4"), ("prompt_i", "<f8"), ("prompt_q", "<f8"),
+                      ("cn0_db_hz", "<f8"), ("carrier_doppler_hz", "<f8"), ("carrier_phase_rads", "<f8"), ("code_phase_samples", "<f8"),
+                      ("tracking_sample_counter", "<u8")])
+assert REC_DTYPE.itemsize == C.sizeof(TrkRecord)
+
+_vp, _f, _d, _i, _s = C.c_void_p, C.c_float, C.c_double, C.c_int, C.c_char_p
+SYMBOLS = {
+    "gb200h_last_error": (_s, []),
+    "gb200h_conf_get": (_s, [_s, _s, _s]),
+    "gb200h_dll_pll_conf": (_s, [_s, _s]),
+    "gb200h_acq_conf": (_s, [_s, _s, _d, _d, _i]),
+    "gb200h_factory": (_s, [_s, _s]),
+    "gb200h_pll_cloop_two_quadrant_atan": (_d, [_f, _f]),
+    "gb200h_pll_four_quadrant_atan": (_d, [_f, _f]),
+    "gb200h_fll_four_quadrant_atan": (_d, [_f, _f, _f, _f, _d, _d]),
+    "gb200h_fll_diff_atan": (_d, [_f, _f, _f, _f, _d, _d]),
+    "gb200h_dll_nc_e_minus_l_normalized": (_d, [_f] * 7),
+    "gb200h_dll_nc_vemlp_normalized": (_d, [_f] * 8),
+    "gb200h_sinboc_slope_abs": (_d, [_d]),
+    "gb200h_sinboc_yintercept_abs": (_d, [_d]),
+    "gb200h_cn0_m2m4_estimator": (_f, [_vp, _i, _f]),
+    "gb200h_cn0_svn_estimator": (_f, [_vp, _i, _f]),
+    "gb200h_carrier_lock_detector": (_f, [_vp, _i]),
+    "gb200h_tracking_loop_filter_run": (None, [_f, _f, _i, _i, _f, _vp, _vp, _i]),
+    "gb200h_fll_pll_filter_run": (None, [_f, _f, _i, _f, _vp, _vp, _f, _vp, _i]),
+    "gb200h_exponential_smoother_run": (None, [_f, _i, _f, _f, _vp, _vp, _i]),
+    "gb200h_gps_l1_ca_code_gen_float": (_i, [_vp, C.c_uint, C.c_uint]),
+    "gb200h_gps_l1_ca_code_gen_complex_sampled": (_i, [_vp, _i, C.c_uint, _i, C.c_uint]),
+    "gb200h_bank_create": (_i, [_s, _s, _i, _i, C.POINTER(_vp)]),
+    "gb200h_bank_destroy": (None, [_vp]),
+    "gb200h_bank_set_codes": (_i, [_vp, _i, _vp, _vp, _i]),
+    "gb200h_bank_start": (_i, [_vp, _i, C.c_uint, _d, _d, C.c_uint64, C.c_uint64]),
+    "gb200h_bank_push": (_i, [_vp, _vp, C.c_int64]),
+    "gb200h_bank_step": (_i, [_vp, _vp, _i]),
+    "gb200h_bank_channel_state": (_i, [_vp, _i, _vp]),
+    "gb200h_bank_launches": (C.c_uint64, [_vp]),
+    "gb200h_bank_run_threaded": (_i, [_vp, _vp, C.c_int64, C.c_uint64, _i, _vp, _i]),
+    "gb200h_acq_create": (_i, [_s, _s, C.c_uint, C.POINTER(_vp)]),
+    "gb200h_acq_destroy": (None, [_vp]),
+    "gb200h_acq_arm": (_i, [_vp, _f]),
+    "gb200h_acq_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
+    "gb200h_acq_get_status": (_i, [_vp, C.POINTER(AcqStatus)]),
+}
+
+_LIB = None
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _capi.lib()  # the CUDA C-ABI library first (the host library links against it)
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: build it with `make -C gnss_sim_receiver_b200/host`")
+        _LIB = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            f = getattr(_LIB, name)
+            f.restype, f.argtypes = res, args
+    return _LIB
+
+
+class HostError(RuntimeError):
+    pass
+
+
+def check(rc):
+    if rc < 0:
+        raise HostError(lib().gb200h_last_error().decode(errors="replace"))
+    return rc
+
+
+def kv(text):
+    """'a=1;b=x;' -> dict"""
+    if isinstance(text, bytes):
+        text = text.decode()
+    return dict(item.split("=", 1) for item in text.strip(";").split(";") if "=" in item)
+
+
+class TrackingBank:
+    """N tracking blocks (adapter selected by `<role>.implementation` in the .conf text) over one GPU engine."""
+
+    def __init__(self, conf_text, role, n_channels, max_engine_channels=0):
+        self._lib = lib()
+        self._h = _vp()
+        check(self._lib.gb200h_bank_create(conf_text.encode(), role.encode(), n_channels, max_engine_channels, C.byref(self._h)))
+        self.n = n_channels
+        self._rec = np.zeros(max(4 * n_channels, 64), dtype=REC_DTYPE)
+
+    def close(self):
+        if self._h:
+            self._lib.gb200h_bank_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_codes(self, ch, tracking_code, data_code=None):
+        t = np.ascontiguousarray(tracking_code, dtype=np.float32)
+        d = None if data_code is None else np.ascontiguousarray(data_code, dtype=np.float32)
+        check(self._lib.gb200h_bank_set_codes(self._h, ch, t.ctypes.data, None if d is None else d.ctypes.data, len(t)))
+
+    def start(self, ch, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, nitems_read):
+        check(self._lib.gb200h_bank_start(self._h, ch, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, nitems_read))
+
+    def push(self, iq):
+        iq = np.ascontiguousarray(iq)
+        n = iq.size if np.iscomplexobj(iq) else iq.size // 2
+        check(self._lib.gb200h_bank_push(self._h, iq.ctypes.data, n))
+
+    def step(self):
+        n = check(self._lib.gb200h_bank_step(self._h, self._rec.ctypes.data, len(self._rec)))
+        return self._rec[:n].copy()
+
+    def run_threaded(self, iq, first_index, n_threads):
+        iq = np.ascontiguousarray(iq)
+        n = iq.size if np.iscomplexobj(iq) else iq.size // 2
+        rec = np.zeros(self.n * (n // 1000 + 8), dtype=REC_DTYPE)
+        k = check(self._lib.gb200h_bank_run_threaded(self._h, iq.ctypes.data, n, first_index, n_threads, rec.ctypes.data, len(rec)))
+        return rec[:k]
+
+    def channel_state(self, ch):
+        v = np.zeros(8)
+        check(self._lib.gb200h_bank_channel_state(self._h, ch, v.ctypes.data))
+        return dict(zip(["state", "carrier_doppler_hz", "cn0_db_hz", "carrier_lock_test", "code_freq_chips", "rem_code_phase_samples", "nitems_read", "prn_length"], v))
+
+    @property
+    def launches(self):
+        return self._lib.gb200h_bank_launches(self._h)
+
+
+class AcquisitionBlock:
+    """One GpsL1CaPcpsAcquisitionB200 adapter + block, driven like Channel/ChannelFsm drive it."""
+
+    def __init__(self, conf_text, role, prn):
+        self._lib = lib()
+        self._h = _vp()
+        check(self._lib.gb200h_acq_create(conf_text.encode(), role.encode(), prn, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self._lib.gb200h_acq_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def arm(self, threshold_if_no_pfa=0.0):
+        check(self._lib.gb200h_acq_arm(self._h, threshold_if_no_pfa))
+
+    def work(self, items, chunk=2048):
+        items = np.ascontiguousarray(items)
+        n = items.size if np.iscomplexobj(items) else items.size // 2
+        return check(self._lib.gb200h_acq_work(self._h, items.ctypes.data, n, chunk))
+
+    def status(self):
+        s = AcqStatus()
+        check(self._lib.gb200h_acq_get_status(self._h, C.byref(s)))
+        return s

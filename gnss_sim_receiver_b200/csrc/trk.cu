@@ -1,5 +1,8 @@
 // Tracking multicorrelator engine: C ABI (include/gnss_b200.h) over trk_kernel.cuh.
 #include "trk_kernel2.cuh"
+#include "host_pool.h"
+#include <chrono>
+#include <mutex>
 #include <algorithm>
 #include <cmath>
 #include <complex>
@@ -296,6 +299,13 @@ int gb200_trk_push_iq(gb200_trk* h, const void* iq_host, int64_t n_samples, uint
 int gb200_trk_push_iq_device(gb200_trk* h, const void* iq_dev, int64_t n_samples, uint64_t* first_index)
 {
     return push_impl(h, iq_dev, n_samples, first_index, cudaMemcpyDeviceToDevice);
+}
+
+int gb200_trk_skip(gb200_trk* h, int64_t n_samples)
+{
+    if (!h || n_samples < 0) return set_error(GB200_EINVAL, "bad argument");
+    h->head += (uint64_t)n_samples;
+    return GB200_OK;
 }
 
 uint64_t gb200_trk_head(const gb200_trk* h) { return h ? h->head : 0; }

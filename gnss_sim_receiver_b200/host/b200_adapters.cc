@@ -1,0 +1,216 @@
+#include "b200_adapters.h"
+#include "b200_gnss_codes.h"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <iostream>
+
+namespace gb200h
+{
+// ------------------------------------------------------------------ tracking
+// Parameter handling of adapters/gps_l1_ca_dll_pll_tracking.cc:42-93 and adapters/galileo_e1_dll_pll_veml_tracking.cc:42-90
+B200DllPllTracking::B200DllPllTracking(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams,
+    char system, const char* signal, const char* implementation, double code_rate_cps, double code_length_chips, int max_extend_symbols)
+    : role_(role), implementation_(implementation), item_size_(sizeof(gr_complex)), in_streams_(in_streams), out_streams_(out_streams)
+{
+    trk_params_.SetFromConfiguration(configuration, role_);
+    trk_params_.vector_length = static_cast<uint32_t>(std::round(trk_params_.fs_in / (code_rate_cps / code_length_chips)));
+    if (trk_params_.extend_correlation_symbols < 1)
+        {
+            trk_params_.extend_correlation_symbols = 1;
+            std::cout << "WARNING: " << implementation << ". extend_correlation_symbols must be bigger than 0. Coherent integration has been set to 1 symbol\n";
+        }
+    else if (max_extend_symbols > 0 && trk_params_.extend_correlation_symbols > max_extend_symbols)
+        {
+            trk_params_.extend_correlation_symbols = max_extend_symbols;
+            std::cout << "WARNING: " << implementation << ". extend_correlation_symbols must be lower than " << max_extend_symbols + 1 << ". Coherent integration has been set to "
+                      << max_extend_symbols << " symbols\n";
+        }
+    if (system == 'G' && std::string(signal) == "1C")
+        {
+            trk_params_.track_pilot = configuration->property(role_ + ".track_pilot", false);
+            if (trk_params_.track_pilot)
+                {
+                    trk_params_.track_pilot = false;
+                    std::cout << "WARNING: GPS L1 C/A does not have pilot signal. Data tracking has been enabled\n";
+                }
+        }
+    if (system == 'E' && std::string(signal) == "1B" && !trk_params_.track_pilot && trk_params_.extend_correlation_symbols > 1)
+        {
+            trk_params_.extend_correlation_symbols = 1;
+            std::cout << "WARNING: Galileo E1. Extended coherent integration is not allowed when tracking the data component. Coherent integration has been set to 4 ms (1 symbol)\n";
+        }
+    if (trk_params_.extend_correlation_symbols > 1 && (trk_params_.pll_bw_narrow_hz > trk_params_.pll_bw_hz || trk_params_.dll_bw_narrow_hz > trk_params_.dll_bw_hz))
+        std::cout << "WARNING: " << implementation << ". PLL or DLL narrow tracking bandwidth is higher than wide tracking one\n";
+    trk_params_.system = system;
+    std::memcpy(trk_params_.signal, signal, 3);
+
+    // the engine ingests gr_complex, cshort and cbyte rings; the per-channel block takes the stream's item type
+    const int iq = item_type_iq(trk_params_.item_type);
+    if (iq >= 0)
+        {
+            item_size_ = item_type_size(trk_params_.item_type);
+            tracking_ = std::make_shared<b200_dll_pll_veml_tracking>(trk_params_);
+        }
+    else
+        {
+            item_size_ = 0;  // Channel::connect throws on item_size() == 0 (channel.cc:118-122)
+            std::cerr << "WARNING: " << trk_params_.item_type << " unknown tracking item type.\n";
+        }
+    if (in_streams_ > 1) std::cerr << "ERROR: This implementation only supports one input stream\n";
+    if (out_streams_ > 1) std::cerr << "ERROR: This implementation only supports one output stream\n";
+}
+
+void B200DllPllTracking::start_tracking()
+{
+    if (!tracking_) return;
+    if (!tracking_->tracking_code().empty() && tracking_->code_table_entries() > 0)
+        {
+            // attach to the GPU engine of the configured device on first use
+            EngineConfig ec;
+            ec.device = trk_params_.device;
+            ec.iq_dtype = item_type_iq(trk_params_.item_type);
+            ec.max_block = static_cast<int>(2 * trk_params_.vector_length);
+            ec.ring_samples = std::max<int64_t>(int64_t{1} << 22, 64LL * trk_params_.vector_length);
+            tracking_->set_engine(B200CorrelatorEngine::instance(ec));
+        }
+    tracking_->start_tracking();
+}
+void B200DllPllTracking::stop_tracking()
+{
+    if (tracking_) tracking_->stop_tracking();
+}
+void B200DllPllTracking::set_channel(unsigned int channel)
+{
+    channel_ = channel;
+    if (tracking_) tracking_->set_channel(channel);
+}
+void B200DllPllTracking::set_gnss_synchro(Gnss_Synchro* p)
+{
+    if (tracking_) tracking_->set_gnss_synchro(p);
+}
+void B200DllPllTracking::connect(gr::top_block_sptr top_block)
+{
+    if (top_block) { /* nothing to connect, now the tracking uses gr_sync_decimator (adapters/gps_l1_ca_dll_pll_tracking.cc:133-139) */ }
+}
+void B200DllPllTracking::disconnect(gr::top_block_sptr top_block)
+{
+    if (top_block) { /* nothing to disconnect */ }
+}
+// Outside GNSS-SDR the "block" handle is the b200 block object itself; inside GNSS-SDR it is the gr::block wrapper of
+// INTEGRATION.md that forwards general_work to it.
+gr::basic_block_sptr B200DllPllTracking::get_left_block() { return tracking_; }
+gr::basic_block_sptr B200DllPllTracking::get_right_block() { return tracking_; }
+
+// ------------------------------------------------------------------ acquisition (adapters/gps_l1_ca_pcps_acquisition.cc:39-236)
+GpsL1CaPcpsAcquisitionB200::GpsL1CaPcpsAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams)
+    : role_(role), in_streams_(in_streams), out_streams_(out_streams)
+{
+    acq_parameters_.ms_per_code = 1;
+    acq_parameters_.SetFromConfiguration(configuration, role, 1.023e6, 1000000.0);  // GPS_L1_CA_CODE_RATE_CPS, GPS_L1_CA_OPT_ACQ_FS_SPS
+    doppler_max_ = static_cast<unsigned int>(acq_parameters_.doppler_max);
+    doppler_step_ = static_cast<unsigned int>(acq_parameters_.doppler_step);
+    item_type_ = acq_parameters_.item_type;
+    item_size_ = acq_parameters_.it_size;
+    code_length_ = static_cast<unsigned int>(std::floor(static_cast<double>(acq_parameters_.resampled_fs) / (1.023e6 / 1023.0)));
+    vector_length_ = static_cast<unsigned int>(std::floor(acq_parameters_.sampled_ms * acq_parameters_.samples_per_ms) * (acq_parameters_.bit_transition_flag ? 2.0 : 1.0));
+    code_.assign(vector_length_, std::complex<float>(0, 0));
+    sampled_ms_ = acq_parameters_.sampled_ms;
+    if (item_type_iq(item_type_) >= 0)
+        acquisition_ = std::make_shared<b200_pcps_acquisition>(acq_parameters_);
+    else
+        {
+            item_size_ = 0;
+            std::cerr << "WARNING: " << item_type_ << " unknown acquisition item type\n";
+        }
+    if (in_streams_ > 1) std::cerr << "ERROR: This implementation only supports one input stream\n";
+    if (out_streams_ > 0) std::cerr << "ERROR: This implementation does not provide an output stream\n";
+}
+
+void GpsL1CaPcpsAcquisitionB200::stop_acquisition() { acquisition_->set_active(false); }
+void GpsL1CaPcpsAcquisitionB200::set_threshold(float threshold)
+{
+    threshold_ = threshold;
+    acquisition_->set_threshold(threshold_);
+}
+void GpsL1CaPcpsAcquisitionB200::set_doppler_max(unsigned int doppler_max)
+{
+    doppler_max_ = doppler_max;
+    acquisition_->set_doppler_max(doppler_max_);
+}
+void GpsL1CaPcpsAcquisitionB200::set_doppler_step(unsigned int doppler_step)
+{
+    doppler_step_ = doppler_step;
+    acquisition_->set_doppler_step(doppler_step_);
+}
+void GpsL1CaPcpsAcquisitionB200::set_doppler_center(int doppler_center)
+{
+    doppler_center_ = doppler_center;
+    acquisition_->set_doppler_center(doppler_center_);
+}
+void GpsL1CaPcpsAcquisitionB200::set_gnss_synchro(Gnss_Synchro* p)
+{
+    gnss_synchro_ = p;
+    acquisition_->set_gnss_synchro(gnss_synchro_);
+}
+void GpsL1CaPcpsAcquisitionB200::set_channel(unsigned int channel)
+{
+    channel_ = channel;
+    acquisition_->set_channel(channel_);
+}
+void GpsL1CaPcpsAcquisitionB200::set_channel_fsm(std::weak_ptr<ChannelFsm> channel_fsm)
+{
+    channel_fsm_ = std::move(channel_fsm);
+    acquisition_->set_channel_fsm(channel_fsm_);
+}
+signed int GpsL1CaPcpsAcquisitionB200::mag() { return static_cast<signed int>(acquisition_->mag()); }
+void GpsL1CaPcpsAcquisitionB200::init() { acquisition_->init(); }
+
+// one code period of the sampled replica, repeated sampled_ms times (:151-170)
+void GpsL1CaPcpsAcquisitionB200::set_local_code()
+{
+    std::vector<std::complex<float>> code(code_length_);
+    const auto fs = static_cast<int32_t>(acq_parameters_.use_automatic_resampler ? acq_parameters_.resampled_fs : acq_parameters_.fs_in);
+    gps_l1_ca_code_gen_complex_sampled(code.data(), static_cast<int>(code_length_), gnss_synchro_->PRN, fs, 0);
+    for (unsigned int i = 0; i < sampled_ms_ && (i + 1) * code_length_ <= vector_length_; i++) std::copy_n(code.data(), code_length_, code_.data() + i * code_length_);
+    acquisition_->set_local_code(code_.data());
+}
+void GpsL1CaPcpsAcquisitionB200::reset() { acquisition_->set_active(true); }
+void GpsL1CaPcpsAcquisitionB200::set_state(int state) { acquisition_->set_state(state); }
+void GpsL1CaPcpsAcquisitionB200::set_resampler_latency(uint32_t latency_samples) { acquisition_->set_resampler_latency(latency_samples); }
+void GpsL1CaPcpsAcquisitionB200::connect(gr::top_block_sptr top_block)
+{
+    if (top_block) { /* gr_complex, cshort and cbyte are ingested directly: no converter blocks to connect (cf. :187-203) */ }
+}
+void GpsL1CaPcpsAcquisitionB200::disconnect(gr::top_block_sptr top_block)
+{
+    if (top_block) { /* nothing to disconnect */ }
+}
+gr::basic_block_sptr GpsL1CaPcpsAcquisitionB200::get_left_block() { return acquisition_; }
+gr::basic_block_sptr GpsL1CaPcpsAcquisitionB200::get_right_block() { return acquisition_; }
+
+// ------------------------------------------------------------------ factory chain
+std::unique_ptr<TrackingInterface> GetB200TrkBlock(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
+{
+    const std::string impl = c->property(role + ".implementation", std::string("Pass_Through"));
+    if (impl == "GPS_L1_CA_DLL_PLL_Tracking_B200") return std::make_unique<GpsL1CaDllPllTrackingB200>(c, role, in, out);
+    if (impl == "Galileo_E1_DLL_PLL_VEML_Tracking_B200") return std::make_unique<GalileoE1DllPllVemlTrackingB200>(c, role, in, out);
+    if (impl == "GPS_L5_DLL_PLL_Tracking_B200") return std::make_unique<GpsL5DllPllTrackingB200>(c, role, in, out);
+    if (impl == "Galileo_E5a_DLL_PLL_Tracking_B200") return std::make_unique<GalileoE5aDllPllTrackingB200>(c, role, in, out);
+    return nullptr;
+}
+
+std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
+{
+    const std::string impl = c->property(role + ".implementation", std::string("Pass_Through"));
+    if (impl == "GPS_L1_CA_PCPS_Acquisition_B200") return std::make_unique<GpsL1CaPcpsAcquisitionB200>(c, role, in, out);
+    return nullptr;
+}
+
+std::unique_ptr<GNSSBlockInterface> GetB200Block(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
+{
+    if (auto t = GetB200TrkBlock(c, role, in, out)) return t;
+    if (auto a = GetB200AcqBlock(c, role, in, out)) return a;
+    return nullptr;
+}
+}  // namespace gb200h

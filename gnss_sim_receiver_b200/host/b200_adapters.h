@@ -1,0 +1,132 @@
+// Adapters: the plugin boundary of the two hot paths.  Each class implements the reference's
+// TrackingInterface / AcquisitionInterface with the reference constructor signature
+//   (const ConfigurationInterface*, const std::string& role, unsigned in_streams, unsigned out_streams)
+// (adapters/gps_l1_ca_dll_pll_tracking.cc:34-37, adapters/gps_l1_ca_pcps_acquisition.cc:39-43) and is selected by the
+// `.implementation` string of its role.  GetB200Block() is the string chain INTEGRATION.md adds to
+// GNSSBlockFactory::GetBlock / GetTrkBlock / GetAcqBlock (src/core/receiver/gnss_block_factory.cc:1340-1346).
+#ifndef GB200_ADAPTERS_H
+#define GB200_ADAPTERS_H
+
+#include "b200_dll_pll_veml_tracking.h"
+#include "b200_pcps_acquisition.h"
+#include "gnss_sdr_compat.h"
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace gb200h
+{
+// ---- tracking: one adapter class, parameterised by signal, with the thin named subclasses the factory instantiates
+class B200DllPllTracking : public TrackingInterface
+{
+public:
+    B200DllPllTracking(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams,
+        char system, const char* signal, const char* implementation, double code_rate_cps, double code_length_chips, int max_extend_symbols);
+    std::string role() override { return role_; }
+    std::string implementation() override { return implementation_; }
+    size_t item_size() override { return item_size_; }
+    void connect(gr::top_block_sptr top_block) override;
+    void disconnect(gr::top_block_sptr top_block) override;
+    gr::basic_block_sptr get_left_block() override;
+    gr::basic_block_sptr get_right_block() override;
+    void start_tracking() override;
+    void stop_tracking() override;
+    void set_gnss_synchro(Gnss_Synchro* p_gnss_synchro) override;
+    void set_channel(unsigned int channel) override;
+    // the block this adapter wraps (what get_left_block() exposes inside GNSS-SDR)
+    std::shared_ptr<b200_dll_pll_veml_tracking> block() { return tracking_; }
+    const Dll_Pll_Conf& conf() const { return trk_params_; }
+
+protected:
+    Dll_Pll_Conf trk_params_;
+    std::shared_ptr<b200_dll_pll_veml_tracking> tracking_;
+    std::string role_, implementation_;
+    size_t item_size_;
+    unsigned int channel_{0}, in_streams_, out_streams_;
+};
+
+class GpsL1CaDllPllTrackingB200 : public B200DllPllTracking
+{
+public:
+    GpsL1CaDllPllTrackingB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams)
+        : B200DllPllTracking(configuration, role, in_streams, out_streams, 'G', "1C", "GPS_L1_CA_DLL_PLL_Tracking_B200", 1.023e6, 1023.0, 20)
+    {
+    }
+};
+
+class GalileoE1DllPllVemlTrackingB200 : public B200DllPllTracking
+{
+public:
+    GalileoE1DllPllVemlTrackingB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams)
+        : B200DllPllTracking(configuration, role, in_streams, out_streams, 'E', "1B", "Galileo_E1_DLL_PLL_VEML_Tracking_B200", 1.023e6, 4092.0, 0)
+    {
+    }
+};
+
+class GpsL5DllPllTrackingB200 : public B200DllPllTracking
+{
+public:
+    GpsL5DllPllTrackingB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams)
+        : B200DllPllTracking(configuration, role, in_streams, out_streams, 'G', "L5", "GPS_L5_DLL_PLL_Tracking_B200", 10.23e6, 10230.0, 10)
+    {
+    }
+};
+
+class GalileoE5aDllPllTrackingB200 : public B200DllPllTracking
+{
+public:
+    GalileoE5aDllPllTrackingB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams)
+        : B200DllPllTracking(configuration, role, in_streams, out_streams, 'E', "5X", "Galileo_E5a_DLL_PLL_Tracking_B200", 10.23e6, 10230.0, 20)
+    {
+    }
+};
+
+// ---- acquisition
+class GpsL1CaPcpsAcquisitionB200 : public AcquisitionInterface
+{
+public:
+    GpsL1CaPcpsAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+    std::string role() override { return role_; }
+    std::string implementation() override { return "GPS_L1_CA_PCPS_Acquisition_B200"; }
+    size_t item_size() override { return item_size_; }
+    void connect(gr::top_block_sptr top_block) override;
+    void disconnect(gr::top_block_sptr top_block) override;
+    gr::basic_block_sptr get_left_block() override;
+    gr::basic_block_sptr get_right_block() override;
+    void set_gnss_synchro(Gnss_Synchro* p_gnss_synchro) override;
+    void set_channel(unsigned int channel) override;
+    void set_channel_fsm(std::weak_ptr<ChannelFsm> channel_fsm) override;
+    void set_threshold(float threshold) override;
+    void set_doppler_max(unsigned int doppler_max) override;
+    void set_doppler_step(unsigned int doppler_step) override;
+    void set_doppler_center(int doppler_center) override;
+    void init() override;
+    void set_local_code() override;
+    void set_state(int state) override;
+    signed int mag() override;
+    void reset() override;
+    void stop_acquisition() override;
+    void set_resampler_latency(uint32_t latency_samples) override;
+    std::shared_ptr<b200_pcps_acquisition> block() { return acquisition_; }
+    const Acq_Conf& conf() const { return acq_parameters_; }
+
+private:
+    Acq_Conf acq_parameters_;
+    std::shared_ptr<b200_pcps_acquisition> acquisition_;
+    std::vector<std::complex<float>> code_;
+    std::weak_ptr<ChannelFsm> channel_fsm_;
+    Gnss_Synchro* gnss_synchro_{nullptr};
+    std::string role_, item_type_;
+    size_t item_size_;
+    float threshold_{0.0F};
+    int doppler_center_{0};
+    unsigned int vector_length_, code_length_, channel_{0}, doppler_max_, doppler_step_, sampled_ms_, in_streams_, out_streams_;
+};
+
+// The `.implementation` strings this tree serves; nullptr for any other string (the caller falls through to the
+// reference's own chain).
+std::unique_ptr<GNSSBlockInterface> GetB200Block(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+std::unique_ptr<TrackingInterface> GetB200TrkBlock(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+}  // namespace gb200h
+#endif

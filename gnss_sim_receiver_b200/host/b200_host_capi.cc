@@ -1,0 +1,503 @@
+#include "b200_host_capi.h"
+#include "b200_adapters.h"
+#include "b200_configuration.h"
+#include "b200_gnss_codes.h"
+#include "b200_tracking_bank.h"
+#include <algorithm>
+#include <cstring>
+#include <sstream>
+#include <thread>
+
+using namespace gb200h;
+
+namespace
+{
+thread_local std::string t_err, t_ret;
+int fail(const std::exception& e)
+{
+    t_err = e.what();
+    return -1;
+}
+cf32 c(float re, float im) { return cf32(re, im); }
+}  // namespace
+
+extern "C" {
+
+const char* gb200h_last_error(void) { return t_err.c_str(); }
+
+const char* gb200h_conf_get(const char* conf_text, const char* name, const char* def)
+{
+    B200Configuration cfg;
+    cfg.load_string(conf_text);
+    t_ret = cfg.property(std::string(name), std::string(def));
+    return t_ret.c_str();
+}
+
+const char* gb200h_dll_pll_conf(const char* conf_text, const char* role)
+{
+    B200Configuration cfg;
+    cfg.load_string(conf_text);
+    Dll_Pll_Conf p;
+    p.SetFromConfiguration(&cfg, role);
+    std::ostringstream o;
+    o.precision(9);
+    o << "item_type=" << p.item_type << ";fs_in=" << p.fs_in << ";pll_bw_hz=" << p.pll_bw_hz << ";dll_bw_hz=" << p.dll_bw_hz << ";pll_bw_narrow_hz=" << p.pll_bw_narrow_hz
+      << ";dll_bw_narrow_hz=" << p.dll_bw_narrow_hz << ";fll_bw_hz=" << p.fll_bw_hz << ";early_late_space_chips=" << p.early_late_space_chips
+      << ";very_early_late_space_chips=" << p.very_early_late_space_chips << ";early_late_space_narrow_chips=" << p.early_late_space_narrow_chips
+      << ";very_early_late_space_narrow_chips=" << p.very_early_late_space_narrow_chips << ";pll_filter_order=" << p.pll_filter_order << ";dll_filter_order=" << p.dll_filter_order
+      << ";fll_filter_order=" << p.fll_filter_order << ";extend_correlation_symbols=" << p.extend_correlation_symbols << ";cn0_samples=" << p.cn0_samples << ";cn0_min=" << p.cn0_min
+      << ";max_code_lock_fail=" << p.max_code_lock_fail << ";max_carrier_lock_fail=" << p.max_carrier_lock_fail << ";carrier_lock_th=" << p.carrier_lock_th
+      << ";pull_in_time_s=" << p.pull_in_time_s << ";bit_synchronization_time_limit_s=" << p.bit_synchronization_time_limit_s << ";track_pilot=" << p.track_pilot
+      << ";high_dyn=" << p.high_dyn << ";carrier_aiding=" << p.carrier_aiding << ";enable_fll_pull_in=" << p.enable_fll_pull_in << ";smoother_length=" << p.smoother_length
+      << ";cn0_smoother_samples=" << p.cn0_smoother_samples << ";cn0_smoother_alpha=" << p.cn0_smoother_alpha << ";dump=" << p.dump << ";device=" << p.device << ";";
+    t_ret = o.str();
+    return t_ret.c_str();
+}
+
+const char* gb200h_acq_conf(const char* conf_text, const char* role, double chip_rate, double opt_freq, int ms_per_code)
+{
+    B200Configuration cfg;
+    cfg.load_string(conf_text);
+    Acq_Conf p;
+    p.ms_per_code = static_cast<uint32_t>(ms_per_code);
+    try
+        {
+            p.SetFromConfiguration(&cfg, role, chip_rate, opt_freq);
+        }
+    catch (const std::invalid_argument& e)
+        {
+            t_ret = std::string("invalid_argument=") + e.what() + ";";
+            return t_ret.c_str();
+        }
+    std::ostringstream o;
+    o.precision(9);
+    o << "item_type=" << p.item_type << ";it_size=" << p.it_size << ";fs_in=" << p.fs_in << ";resampled_fs=" << p.resampled_fs << ";doppler_max=" << p.doppler_max
+      << ";doppler_step=" << p.doppler_step << ";sampled_ms=" << p.sampled_ms << ";max_dwells=" << p.max_dwells << ";pfa=" << p.pfa << ";pfa2=" << p.pfa2
+      << ";bit_transition_flag=" << p.bit_transition_flag << ";use_CFAR_algorithm_flag=" << p.use_CFAR_algorithm_flag << ";samples_per_ms=" << p.samples_per_ms
+      << ";samples_per_chip=" << p.samples_per_chip << ";samples_per_code=" << p.samples_per_code << ";resampler_ratio=" << p.resampler_ratio << ";blocking=" << p.blocking
+      << ";make_2_steps=" << p.make_2_steps << ";";
+    t_ret = o.str();
+    return t_ret.c_str();
+}
+
+const char* gb200h_factory(const char* conf_text, const char* role)
+{
+    B200Configuration cfg;
+    cfg.load_string(conf_text);
+    t_ret.clear();
+    try
+        {
+            // construct the tracking adapters only: the acquisition adapter needs a GPU at construction
+            const std::string impl = cfg.property(std::string(role) + ".implementation", std::string(""));
+            if (auto t = GetB200TrkBlock(&cfg, role, 1, 1))
+                t_ret = t->implementation() + ";item_size=" + std::to_string(t->item_size()) + ";role=" + t->role() + ";";
+            else if (impl == "GPS_L1_CA_PCPS_Acquisition_B200")
+                t_ret = impl + ";acquisition;";
+        }
+    catch (const std::exception& e)
+        {
+            t_ret = std::string("error=") + e.what();
+        }
+    return t_ret.c_str();
+}
+
+double gb200h_pll_cloop_two_quadrant_atan(float re, float im) { return pll_cloop_two_quadrant_atan(c(re, im)); }
+double gb200h_pll_four_quadrant_atan(float re, float im) { return pll_four_quadrant_atan(c(re, im)); }
+double gb200h_fll_four_quadrant_atan(float r1, float i1, float r2, float i2, double t1, double t2) { return fll_four_quadrant_atan(c(r1, i1), c(r2, i2), t1, t2); }
+double gb200h_fll_diff_atan(float r1, float i1, float r2, float i2, double t1, double t2) { return fll_diff_atan(c(r1, i1), c(r2, i2), t1, t2); }
+double gb200h_dll_nc_e_minus_l_normalized(float er, float ei, float lr, float li, float spc, float slope, float y_intercept)
+{
+    return dll_nc_e_minus_l_normalized(c(er, ei), c(lr, li), spc, slope, y_intercept);
+}
+double gb200h_dll_nc_vemlp_normalized(float ver, float vei, float er, float ei, float lr, float li, float vlr, float vli)
+{
+    return dll_nc_vemlp_normalized(c(ver, vei), c(er, ei), c(lr, li), c(vlr, vli));
+}
+double gb200h_sinboc_slope_abs(double x) { return sinboc11_slope_abs(x); }
+double gb200h_sinboc_yintercept_abs(double x) { return sinboc11_y_intercept_abs(x); }
+float gb200h_cn0_m2m4_estimator(const float* p, int length, float T) { return cn0_m2m4_estimator(reinterpret_cast<const cf32*>(p), length, T); }
+float gb200h_cn0_svn_estimator(const float* p, int length, float T) { return cn0_svn_estimator(reinterpret_cast<const cf32*>(p), length, T); }
+float gb200h_carrier_lock_detector(const float* p, int length) { return carrier_lock_detector(reinterpret_cast<const cf32*>(p), length); }
+
+void gb200h_tracking_loop_filter_run(float update_interval, float bw, int order, int include_last, float init, const float* in, float* out, int n)
+{
+    Tracking_loop_filter f(update_interval, bw, order, include_last != 0);
+    f.initialize(init);
+    for (int i = 0; i < n; i++) out[i] = f.apply(in[i]);
+}
+
+void gb200h_fll_pll_filter_run(float fll_bw, float pll_bw, int order, float init_doppler, const float* fll_in, const float* pll_in, float T, float* out, int n)
+{
+    Tracking_FLL_PLL_filter f;
+    f.set_params(fll_bw, pll_bw, order);
+    f.initialize(init_doppler);
+    for (int i = 0; i < n; i++) out[i] = f.get_carrier_error(fll_in[i], pll_in[i], T);
+}
+
+void gb200h_exponential_smoother_run(float alpha, int init_samples, float min_value, float offset, const float* in, float* out, int n)
+{
+    Exponential_Smoother s;
+    s.set_alpha(alpha);
+    s.set_samples_for_initialization(init_samples);
+    s.set_min_value(min_value);
+    s.set_offset(offset);
+    for (int i = 0; i < n; i++) out[i] = s.smooth(in[i]);
+}
+
+int gb200h_gps_l1_ca_code_gen_float(float* dest, unsigned prn, unsigned chip_shift)
+{
+    try
+        {
+            gps_l1_ca_code_gen_float(dest, prn, chip_shift);
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int gb200h_gps_l1_ca_code_gen_complex_sampled(float* dest_ri, int n, unsigned prn, int fs, unsigned chip_shift)
+{
+    try
+        {
+            gps_l1_ca_code_gen_complex_sampled(reinterpret_cast<std::complex<float>*>(dest_ri), n, prn, fs, chip_shift);
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ tracking bank
+struct gb200h_bank
+{
+    B200Configuration cfg;
+    std::string role;
+    std::shared_ptr<B200CorrelatorEngine> engine;
+    std::unique_ptr<B200TrackingBank> bank;
+    std::vector<std::unique_ptr<Gnss_Synchro>> synchros;
+    std::vector<B200TrackingBank::Output> outs;
+};
+
+namespace
+{
+void to_record(int ch, const Gnss_Synchro& s, gb200h_trk_record* r)
+{
+    r->channel = ch;
+    r->prn = s.PRN;
+    r->valid = s.Flag_valid_symbol_output;
+    r->correlation_length_ms = s.correlation_length_ms;
+    r->prompt_i = s.Prompt_I;
+    r->prompt_q = s.Prompt_Q;
+    r->cn0_db_hz = s.CN0_dB_hz;
+    r->carrier_doppler_hz = s.Carrier_Doppler_hz;
+    r->carrier_phase_rads = s.Carrier_phase_rads;
+    r->code_phase_samples = s.Code_phase_samples;
+    r->tracking_sample_counter = s.Tracking_sample_counter;
+}
+}  // namespace
+
+extern "C" {
+
+int gb200h_bank_create(const char* conf_text, const char* role, int n_channels, int max_engine_channels, gb200h_bank** out)
+{
+    try
+        {
+            auto b = std::make_unique<gb200h_bank>();
+            b->cfg.load_string(conf_text);
+            b->role = role;
+            for (int i = 0; i < n_channels; i++)
+                {
+                    auto adapter = GetB200TrkBlock(&b->cfg, role, 1, 1);
+                    if (!adapter) throw std::runtime_error(std::string(role) + ".implementation is not a B200 tracking block");
+                    auto* a = static_cast<B200DllPllTracking*>(adapter.get());
+                    if (a->item_size() == 0) throw std::runtime_error("unsupported tracking item type");
+                    if (!b->engine)
+                        {
+                            EngineConfig ec;
+                            ec.device = a->conf().device;
+                            ec.iq_dtype = item_type_iq(a->conf().item_type);
+                            ec.max_channels = std::max(max_engine_channels, 4 * n_channels);  // bank slots + facade slots, pilot + data
+                            ec.max_code_len = 2 * a->block()->code_table_entries();
+                            ec.max_block = static_cast<int>(2 * a->conf().vector_length);
+                            ec.ring_samples = std::max<int64_t>(int64_t{1} << 21, 64LL * a->conf().vector_length);
+                            b->engine = std::make_shared<B200CorrelatorEngine>(ec);  // a private engine per bank
+                            b->bank = std::make_unique<B200TrackingBank>(b->engine);
+                        }
+                    b->synchros.push_back(std::make_unique<Gnss_Synchro>());
+                    auto blk = std::make_unique<b200_dll_pll_veml_tracking>(a->conf());
+                    blk->set_gnss_synchro(b->synchros.back().get());
+                    blk->set_channel(static_cast<uint32_t>(i));
+                    b->bank->add_channel(std::move(blk));
+                }
+            *out = b.release();
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+void gb200h_bank_destroy(gb200h_bank* b) { delete b; }
+
+int gb200h_bank_set_codes(gb200h_bank* b, int ch, const float* tracking_code, const float* data_code, int n_entries)
+{
+    try
+        {
+            if (tracking_code) b->bank->block(ch).set_tracking_code(tracking_code, n_entries);
+            if (data_code) b->bank->block(ch).set_data_code(data_code, n_entries);
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int gb200h_bank_start(gb200h_bank* b, int ch, unsigned prn, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t nitems_read)
+{
+    try
+        {
+            Gnss_Synchro& s = *b->synchros[ch];
+            const Dll_Pll_Conf& p = b->bank->block(ch).parameters();
+            s.System = p.system;
+            std::memcpy(s.Signal, p.signal, 3);
+            s.PRN = prn;
+            s.Channel_ID = ch;
+            s.Acq_delay_samples = acq_delay_samples;
+            s.Acq_doppler_hz = acq_doppler_hz;
+            s.Acq_samplestamp_samples = acq_samplestamp;
+            s.Flag_valid_acquisition = true;
+            b->bank->start_tracking(ch, nitems_read);
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int gb200h_bank_push(gb200h_bank* b, const void* iq, int64_t n_samples)
+{
+    try
+        {
+            b->bank->push(iq, n_samples);
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int gb200h_bank_step(gb200h_bank* b, gb200h_trk_record* records, int max_records)
+{
+    try
+        {
+            b->outs.clear();
+            b->bank->step(&b->outs);
+            const int n = std::min<int>(static_cast<int>(b->outs.size()), max_records);
+            for (int i = 0; i < n; i++) to_record(b->outs[i].channel, b->outs[i].synchro, &records[i]);
+            return n;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int gb200h_bank_channel_state(gb200h_bank* b, int ch, double* v)
+{
+    if (!b || ch < 0 || ch >= b->bank->size()) return -1;
+    const auto& k = b->bank->block(ch);
+    v[0] = k.state();
+    v[1] = k.carrier_doppler_hz();
+    v[2] = k.cn0_db_hz();
+    v[3] = k.carrier_lock_test();
+    v[4] = k.code_freq_chips();
+    v[5] = k.rem_code_phase_samples();
+    v[6] = static_cast<double>(b->bank->nitems_read(ch));
+    v[7] = k.current_prn_length_samples();
+    return 0;
+}
+
+uint64_t gb200h_bank_launches(gb200h_bank* b) { return b->engine->launches(); }
+
+// Thread-per-block shape: each thread owns a share of the channels and calls the blocking general_work on the common
+// host stream, exactly what the GNU Radio scheduler does with one thread per tracking block.
+int gb200h_bank_run_threaded(gb200h_bank* b, const void* iq, int64_t n_samples, uint64_t first_index, int n_threads, gb200h_trk_record* records, int max_records)
+{
+    try
+        {
+            const int nch = b->bank->size();
+            const int eb = b->engine->config().iq_dtype == GB200_IQ_CF32 ? 8 : b->engine->config().iq_dtype == GB200_IQ_CS16 ? 4 : 2;
+            n_threads = std::max(1, std::min(n_threads, nch));
+            for (int i = 0; i < nch; i++)
+                {
+                    b->bank->block(i).set_engine(b->engine);
+                    b->bank->block(i).upload_codes();
+                }
+            b->engine->set_expected_batch(n_threads);
+            std::vector<std::vector<B200TrackingBank::Output>> per(n_threads);
+            std::vector<std::string> errs(n_threads);
+            std::vector<std::thread> th;
+            for (int t = 0; t < n_threads; t++)
+                th.emplace_back([&, t] {
+                    try
+                        {
+                            // every thread walks the stream block by block; its channels keep their own read pointers
+                            std::vector<uint64_t> rd;
+                            for (int i = t; i < nch; i += n_threads) rd.push_back(b->bank->nitems_read(i));
+                            bool progress = true;
+                            while (progress)
+                                {
+                                    progress = false;
+                                    int k = 0;
+                                    for (int i = t; i < nch; i += n_threads, k++)
+                                        {
+                                            auto& blk = b->bank->block(i);
+                                            const int64_t avail = static_cast<int64_t>(first_index) + n_samples - static_cast<int64_t>(rd[k]);
+                                            if (avail < blk.required_samples() || rd[k] < first_index) continue;
+                                            Gnss_Synchro s{};
+                                            int consumed = 0;
+                                            const char* in = static_cast<const char*>(iq) + (rd[k] - first_index) * eb;
+                                            const int produced = blk.general_work(in, static_cast<int>(std::min<int64_t>(avail, blk.required_samples())), rd[k], &s, &consumed);
+                                            rd[k] += static_cast<uint64_t>(consumed);
+                                            if (produced) per[t].push_back({i, s});
+                                            progress = true;
+                                        }
+                                }
+                        }
+                    catch (const std::exception& e)
+                        {
+                            errs[t] = e.what();
+                        }
+                    // a finished thread no longer takes part in the batches
+                    static std::mutex m;
+                    std::lock_guard<std::mutex> lk(m);
+                    b->engine->set_expected_batch(0);
+                });
+            for (auto& x : th) x.join();
+            for (auto& e : errs)
+                if (!e.empty()) throw std::runtime_error(e);
+            int n = 0;
+            for (auto& v : per)
+                for (auto& o : v)
+                    if (n < max_records) to_record(o.channel, o.synchro, &records[n++]);
+            return n;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ acquisition block
+struct gb200h_acq
+{
+    B200Configuration cfg;
+    std::unique_ptr<GpsL1CaPcpsAcquisitionB200> adapter;
+    Gnss_Synchro synchro;
+    int last_event{0};
+};
+
+extern "C" {
+
+int gb200h_acq_create(const char* conf_text, const char* role, unsigned prn, gb200h_acq** out)
+{
+    try
+        {
+            auto a = std::make_unique<gb200h_acq>();
+            a->cfg.load_string(conf_text);
+            auto blk = GetB200AcqBlock(&a->cfg, role, 1, 0);
+            if (!blk) throw std::runtime_error(std::string(role) + ".implementation is not a B200 acquisition block");
+            a->adapter.reset(static_cast<GpsL1CaPcpsAcquisitionB200*>(blk.release()));
+            a->synchro.System = 'G';
+            std::memcpy(a->synchro.Signal, "1C", 3);
+            a->synchro.PRN = prn;
+            a->adapter->set_gnss_synchro(&a->synchro);
+            a->adapter->set_channel(0);
+            gb200h_acq* raw = a.get();
+            a->adapter->block()->set_event_sink([raw](int ev) { raw->last_event = ev; });
+            *out = a.release();
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+void gb200h_acq_destroy(gb200h_acq* a) { delete a; }
+
+int gb200h_acq_arm(gb200h_acq* a, float threshold_if_no_pfa)
+{
+    try
+        {
+            auto& ad = *a->adapter;
+            ad.set_doppler_max(static_cast<unsigned>(ad.conf().doppler_max));
+            ad.set_doppler_step(static_cast<unsigned>(ad.conf().doppler_step));
+            ad.set_threshold(threshold_if_no_pfa);
+            ad.init();
+            ad.set_local_code();
+            ad.block()->start();
+            a->last_event = 0;
+            ad.set_state(1);
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int64_t gb200h_acq_work(gb200h_acq* a, const void* items, int64_t n_items, int chunk)
+{
+    try
+        {
+            auto& blk = *a->adapter->block();
+            const size_t isz = a->adapter->item_size();
+            int64_t done = 0;
+            int idle_calls = 0;
+            while (done < n_items && idle_calls < 4)
+                {
+                    const int n = static_cast<int>(std::min<int64_t>(chunk, n_items - done));
+                    const int c = blk.general_work(static_cast<const char*>(items) + done * isz, n);
+                    done += c;
+                    if (!blk.active()) break;
+                    idle_calls = (c == 0) ? idle_calls + 1 : 0;
+                }
+            return done;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int gb200h_acq_get_status(gb200h_acq* a, gb200h_acq_status* s)
+{
+    auto& blk = *a->adapter->block();
+    s->acq_delay_samples = a->synchro.Acq_delay_samples;
+    s->acq_doppler_hz = a->synchro.Acq_doppler_hz;
+    s->acq_samplestamp_samples = a->synchro.Acq_samplestamp_samples;
+    s->test_statistics = blk.test_statistics();
+    s->threshold = blk.threshold();
+    s->mag = static_cast<float>(blk.mag());
+    s->input_power = blk.input_power();
+    s->state = blk.state();
+    s->active = blk.active();
+    s->last_event = a->last_event;
+    s->indext = blk.last_result().indext;
+    s->doppler_index = blk.last_result().doppler_index;
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,87 @@
+/* C door onto the C++ host layer (libgnss_b200_host.so) for tests/, bench.py and non-C++ embedders.
+ * Plain pointers and sizes; every function returns 0 / a count, or -1 with the message in gb200h_last_error().
+ * The GPU entry points (bank, acquisition block) fail when libgnss_b200.so cannot create its engines: no CPU fallback. */
+#ifndef GB200_HOST_CAPI_H
+#define GB200_HOST_CAPI_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* gb200h_last_error(void);
+
+/* ---- CPU-only pieces (checked against the reference's own objects in tests/test_host_cpu.py) */
+/* value of `name` in a .conf text, or `def` — B200Configuration::property(string) */
+const char* gb200h_conf_get(const char* conf_text, const char* name, const char* def);
+/* Dll_Pll_Conf / Acq_Conf after SetFromConfiguration, as "key=value;" text */
+const char* gb200h_dll_pll_conf(const char* conf_text, const char* role);
+const char* gb200h_acq_conf(const char* conf_text, const char* role, double chip_rate, double opt_freq, int ms_per_code);
+/* implementation()/item_size of the adapter GetB200Block selects for `role`, "" when the string is not ours */
+const char* gb200h_factory(const char* conf_text, const char* role);
+double gb200h_pll_cloop_two_quadrant_atan(float re, float im);
+double gb200h_pll_four_quadrant_atan(float re, float im);
+double gb200h_fll_four_quadrant_atan(float r1, float i1, float r2, float i2, double t1, double t2);
+double gb200h_fll_diff_atan(float r1, float i1, float r2, float i2, double t1, double t2);
+double gb200h_dll_nc_e_minus_l_normalized(float er, float ei, float lr, float li, float spc, float slope, float y_intercept);
+double gb200h_dll_nc_vemlp_normalized(float ver, float vei, float er, float ei, float lr, float li, float vlr, float vli);
+double gb200h_sinboc_slope_abs(double x);
+double gb200h_sinboc_yintercept_abs(double x);
+float gb200h_cn0_m2m4_estimator(const float* prompt_ri, int length, float T);
+float gb200h_cn0_svn_estimator(const float* prompt_ri, int length, float T);
+float gb200h_carrier_lock_detector(const float* prompt_ri, int length);
+void gb200h_tracking_loop_filter_run(float update_interval, float bw, int order, int include_last, float init, const float* in, float* out, int n);
+void gb200h_fll_pll_filter_run(float fll_bw, float pll_bw, int order, float init_doppler, const float* fll_in, const float* pll_in, float T, float* out, int n);
+void gb200h_exponential_smoother_run(float alpha, int init_samples, float min_value, float offset, const float* in, float* out, int n);
+int gb200h_gps_l1_ca_code_gen_float(float* dest, unsigned prn, unsigned chip_shift);
+int gb200h_gps_l1_ca_code_gen_complex_sampled(float* dest_ri, int n, unsigned prn, int fs, unsigned chip_shift);
+
+/* ---- tracking bank: N dll_pll_veml tracking blocks of one signal over one GPU engine */
+typedef struct gb200h_bank gb200h_bank;
+typedef struct
+{
+    int32_t channel;
+    uint32_t prn;
+    int32_t valid;        /* Flag_valid_symbol_output; 0 = loss-of-lock notification */
+    int32_t correlation_length_ms;
+    double prompt_i, prompt_q, cn0_db_hz, carrier_doppler_hz, carrier_phase_rads, code_phase_samples;
+    uint64_t tracking_sample_counter;
+} gb200h_trk_record;
+/* `role` names the tracking block in conf_text (e.g. "Tracking_1C"); its .implementation selects the adapter */
+int gb200h_bank_create(const char* conf_text, const char* role, int n_channels, int max_engine_channels, gb200h_bank** out);
+void gb200h_bank_destroy(gb200h_bank* b);
+/* optional code tables for signals generated outside this tree (Galileo E1, L5, E5a); before bank_start */
+int gb200h_bank_set_codes(gb200h_bank* b, int ch, const float* tracking_code, const float* data_code, int n_entries);
+int gb200h_bank_start(gb200h_bank* b, int ch, unsigned prn, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t nitems_read);
+int gb200h_bank_push(gb200h_bank* b, const void* iq, int64_t n_samples);
+/* runs rounds until no channel can advance; returns the number of records written (at most max_records) */
+int gb200h_bank_step(gb200h_bank* b, gb200h_trk_record* records, int max_records);
+/* v[0..7] = state, carrier_doppler_hz, cn0_db_hz, carrier_lock_test, code_freq_chips, rem_code_phase_samples, nitems_read, current_prn_length */
+int gb200h_bank_channel_state(gb200h_bank* b, int ch, double* v);
+uint64_t gb200h_bank_launches(gb200h_bank* b);
+/* per-channel blocking form from `n_threads` host threads (the GNU Radio thread-per-block shape): every thread runs
+ * general_work over the same host stream for its share of channels; returns the records like bank_step */
+int gb200h_bank_run_threaded(gb200h_bank* b, const void* iq, int64_t n_samples, uint64_t first_index, int n_threads, gb200h_trk_record* records, int max_records);
+
+/* ---- acquisition block (one channel) */
+typedef struct gb200h_acq gb200h_acq;
+typedef struct
+{
+    double acq_delay_samples, acq_doppler_hz;
+    uint64_t acq_samplestamp_samples;
+    float test_statistics, threshold, mag, input_power;
+    int32_t state, active, last_event; /* last_event: 0 none, 1 positive, 2 negative */
+    uint32_t indext;
+    int32_t doppler_index;
+} gb200h_acq_status;
+int gb200h_acq_create(const char* conf_text, const char* role, unsigned prn, gb200h_acq** out);
+void gb200h_acq_destroy(gb200h_acq* a);
+/* adapter calls, in the order Channel/ChannelFsm make them: set_doppler_*, set_threshold (pfa = 0), init, set_local_code, start, set_state(1) */
+int gb200h_acq_arm(gb200h_acq* a, float threshold_if_no_pfa);
+/* general_work over a host buffer of the configured item type: loops until every item is consumed or the block went idle; returns items consumed */
+int64_t gb200h_acq_work(gb200h_acq* a, const void* items, int64_t n_items, int chunk);
+int gb200h_acq_get_status(gb200h_acq* a, gb200h_acq_status* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -11,6 +11,11 @@ import numpy as np
 from . import _capi
 from ._capi import GB200_MAX_TAPS, IQ_CF32, IQ_CS16, IQ_CS8, TrkCmd, TrkConfig, check
 
+_CMD_DTYPE = np.dtype([("ch", "<i4"), ("n_samples", "<i4"), ("n_taps", "<i4"), ("flags", "<i4"), ("sample_offset", "<u8"),
+                       ("rem_carrier_phase_rad", "<f4"), ("phase_step_rad", "<f4"), ("phase_rate_step_rad", "<f4"),
+                       ("rem_code_phase_chips", "<f4"), ("code_phase_step_chips", "<f4"), ("code_phase_rate_step_chips", "<f4"),
+                       ("shifts_chips", "<f4", (GB200_MAX_TAPS,))])
+assert _CMD_DTYPE.itemsize == C.sizeof(TrkCmd)
 _IQ_NP = {IQ_CF32: (np.complex64, 8), IQ_CS16: (np.int16, 4), IQ_CS8: (np.int8, 2)}
 
 
@@ -72,29 +77,30 @@ class TrackingEngine:
 
     @staticmethod
     def make_cmds(ch, sample_offset, n_samples, shifts, rem_carr, phase_step, rem_code, code_step, phase_rate=None, code_rate=None, flags=0):
-        """Arrays (one entry per command) -> ctypes array of gb200_trk_cmd.  shifts: (n_cmds, n_taps)."""
+        """Arrays (one entry per command) -> ctypes array of gb200_trk_cmd.  shifts: (n_cmds, n_taps) or (1, n_taps)."""
         shifts = np.atleast_2d(np.asarray(shifts, dtype=np.float32))
         n = len(ch)
         arr = (TrkCmd * n)()
-        for i in range(n):
-            c = arr[i]
-            c.ch, c.n_samples, c.n_taps, c.flags = int(ch[i]), int(n_samples[i]), shifts.shape[1], int(flags)
-            c.sample_offset = int(sample_offset[i])
-            c.rem_carrier_phase_rad, c.phase_step_rad = float(rem_carr[i]), float(phase_step[i])
-            c.phase_rate_step_rad = 0.0 if phase_rate is None else float(phase_rate[i])
-            c.rem_code_phase_chips, c.code_phase_step_chips = float(rem_code[i]), float(code_step[i])
-            c.code_phase_rate_step_chips = 0.0 if code_rate is None else float(code_rate[i])
-            row = shifts[i if shifts.shape[0] > 1 else 0]
-            for t in range(shifts.shape[1]):
-                c.shifts_chips[t] = float(row[t])
+        v = np.frombuffer(arr, dtype=_CMD_DTYPE)  # field-by-field view of the same memory
+        v["ch"], v["n_samples"], v["n_taps"], v["flags"] = np.asarray(ch), np.asarray(n_samples), shifts.shape[1], flags
+        v["sample_offset"] = np.asarray(sample_offset, dtype=np.uint64)
+        v["rem_carrier_phase_rad"], v["phase_step_rad"] = np.asarray(rem_carr, dtype=np.float32), np.asarray(phase_step, dtype=np.float32)
+        v["rem_code_phase_chips"], v["code_phase_step_chips"] = np.asarray(rem_code, dtype=np.float32), np.asarray(code_step, dtype=np.float32)
+        if phase_rate is not None:
+            v["phase_rate_step_rad"] = np.asarray(phase_rate, dtype=np.float32)
+        if code_rate is not None:
+            v["code_phase_rate_step_chips"] = np.asarray(code_rate, dtype=np.float32)
+        v["shifts_chips"][:, : shifts.shape[1]] = shifts
+        arr._n_taps = shifts.shape[1]
         return arr
 
     # Carrier_wipeoff_multicorrelator_resampler for a batch of commands: (n_cmds, n_taps) complex64
     def correlate(self, cmds):
         n = len(cmds)
-        out = np.zeros((n, GB200_MAX_TAPS), dtype=np.complex64)
+        out = np.empty((n, GB200_MAX_TAPS), dtype=np.complex64)
         check(self._lib.gb200_trk_correlate(self._h, cmds, n, out.ctypes.data))
-        return out[:, : max(c.n_taps for c in cmds)]
+        nt = getattr(cmds, "_n_taps", None) or max(c.n_taps for c in cmds)
+        return out[:, :nt]
 
     def enqueue(self, cmds):
         self._n = len(cmds)

@@ -115,6 +115,10 @@ int gb200_trk_set_code_complex(gb200_trk* h, int ch, const gb200_cf32* code, int
 int gb200_trk_push_iq(gb200_trk* h, const void* iq_host, int64_t n_samples, uint64_t* first_index);
 /* same, from a device pointer on cfg.device (device->device copy on the engine's stream) */
 int gb200_trk_push_iq_device(gb200_trk* h, const void* iq_dev, int64_t n_samples, uint64_t* first_index);
+/* Advance the ring by n_samples without copying anything (the skipped samples read as undefined): used when no
+ * channel needs a stretch of the stream, e.g. all channels idle (state 0 of dll_pll_veml_tracking.cc:1746-1752 just
+ * consumes its input). */
+int gb200_trk_skip(gb200_trk* h, int64_t n_samples);
 /* absolute index one past the newest sample */
 uint64_t gb200_trk_head(const gb200_trk* h);
 
