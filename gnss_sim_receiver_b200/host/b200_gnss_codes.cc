@@ -4,7 +4,7 @@
 //   gps_l1_ca_code_gen_complex_sampled the acquisition replica: chips in the IMAGINARY part (0, +-1), sampled with the
 //                                      Borre index law  idx = int(fl(ts*(i+1))/tc + 1) - 1  in fp32, last sample forced to
 //                                      the last chip (:170-186)
-// tests/test_host_cpu.py checks both bit-exactly against the reference's generators (oracle/_ref).
+// tests/test_host_cpu.py checks both bit-exactly against the reference's generators (built by the test suite).
 #include "b200_gnss_codes.h"
 #include <array>
 #include <stdexcept>

@@ -20,7 +20,7 @@ double phase_unwrap(double phase_rad)
 }
 
 // The reference calls gr::fast_atan2f (GNU Radio's table-driven approximation, |err| < 1e-3 rad... documented as ~0.01 deg);
-// libm atan2f is used here, as in the oracle's shim.
+// libm atan2f is used here.
 double fll_four_quadrant_atan(cf32 a, cf32 b, double t1, double t2)
 {
     const float dot = a.real() * b.real() + a.imag() * b.imag();

@@ -2,7 +2,7 @@
 // Same names, argument meaning and arithmetic types (float/double) as the reference's tracking/libs:
 //   tracking_discriminators.cc:27-149, tracking_loop_filter.cc:26-265, tracking_FLL_PLL_filter.cc:23-99,
 //   lock_detectors.cc:54-148, exponential_smoother.cc:23-115.
-// tests/test_host_cpu.py checks every function against the reference's own objects (oracle/_ref) and against the
+// tests/test_host_cpu.py checks every function against the reference's own objects (built by the test suite) and against the
 // expected values of the reference's unit tests (discriminator_test.cc, tracking_loop_filter_test.cc).
 #ifndef GB200_TRACKING_LIBS_H
 #define GB200_TRACKING_LIBS_H
