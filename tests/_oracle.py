@@ -236,3 +236,76 @@ def acq_wipeoff(n, freq, fs):
     out = np.zeros(n, dtype=np.complex64)
     orc().orc_acq_wipeoff(_p(out), n, C.c_float(freq), C.c_double(fs))
     return out
+
+
+# ------------------------------------------------------------------ closed loop (synthetic IF + the reference-object loop)
+def gen_if(n, first_index, fs, codes, doppler_hz, delay_chips, phase0, cn0_dbhz, nav_bits=None, periods_per_bit=20,
+           f_chip=1.023e6, f_carrier=1575.42e6, noise_sigma=1.0, seed=1):
+    """complex64[n] of the stream starting at absolute sample `first_index` (oracle_loop.c: orc_gen_if); codes: (nsat, L)."""
+    codes = np.ascontiguousarray(codes, dtype=np.float32)
+    nsat, L = codes.shape
+    d = [np.ascontiguousarray(x, dtype=np.float64) for x in (doppler_hz, delay_chips, phase0, cn0_dbhz)]
+    out = np.empty(n, dtype=np.complex64)
+    if nav_bits is not None:
+        nav_bits = np.ascontiguousarray(nav_bits, dtype=np.int8)
+        nb, nbp = nav_bits.shape[1], nav_bits.ctypes.data_as(C.c_void_p)
+    else:
+        nb, nbp = 0, None
+    f = orc().orc_gen_if
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_double, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_double,
+                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_uint64]
+    f(out.ctypes.data, n, first_index, fs, nsat, codes.ctypes.data, L, f_chip, f_carrier, d[0].ctypes.data, d[1].ctypes.data, d[2].ctypes.data,
+      d[3].ctypes.data, nbp, nb, periods_per_bit, noise_sigma, seed)
+    return out
+
+
+class RefLoopParams(C.Structure):
+    _fields_ = [(k, C.c_double) for k in ("fs_in", "code_period", "chip_rate", "carrier_freq", "carrier_lock_th")] + \
+        [(k, C.c_float) for k in ("pll_bw", "dll_bw", "fll_bw", "pll_bw_narrow", "dll_bw_narrow", "el", "vel", "el_narrow", "vel_narrow",
+                                  "cn0_smoother_alpha", "lock_smoother_alpha")] + \
+        [(k, C.c_int32) for k in ("vector_length", "veml", "secondary", "track_pilot", "symbols_per_bit", "samples_per_chip", "code_length_chips",
+                                  "pll_order", "dll_order", "extend", "cn0_samples", "cn0_min", "max_code_lock_fail", "max_carrier_lock_fail",
+                                  "cn0_smoother_samples", "lock_smoother_samples", "carrier_aiding", "enable_fll_pull_in", "enable_fll_steady",
+                                  "interchange_iq", "arch", "correlation_length_ms")] + \
+        [(k, C.c_uint32) for k in ("pull_in_time_s", "bit_sync_time_limit_s", "secondary_code_length", "data_secondary_code_length")] + \
+        [("secondary_code", C.c_char * 256), ("data_secondary_code", C.c_char * 256)]
+
+
+REF_LOOP_REC = np.dtype([("channel", "<i4"), ("prn", "<u4"), ("valid", "<i4"), ("correlation_length_ms", "<i4"), ("prompt_i", "<f8"), ("prompt_q", "<f8"),
+                         ("cn0_db_hz", "<f8"), ("carrier_doppler_hz", "<f8"), ("carrier_phase_rads", "<f8"), ("code_phase_samples", "<f8"),
+                         ("tracking_sample_counter", "<u8")])
+
+
+class RefLoop:
+    """One tracking channel made of the reference's own objects (oracle/ref_loop.cc in oracle/_ref/libgnssref.so)."""
+
+    def __init__(self, params, tracking_code, data_code, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, nitems_read):
+        r = ref()
+        r.ref_loop_new.restype = C.c_void_p
+        r.ref_loop_new.argtypes = [C.POINTER(RefLoopParams), C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+        r.ref_loop_feed.restype = C.c_int
+        r.ref_loop_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int]
+        r.ref_loop_state.argtypes = [C.c_void_p, C.c_void_p]
+        r.ref_loop_free.argtypes = [C.c_void_p]
+        self._r = r
+        t = np.ascontiguousarray(tracking_code, dtype=np.float32)
+        d = None if data_code is None else np.ascontiguousarray(data_code, dtype=np.float32)
+        self._h = r.ref_loop_new(C.byref(params), t.ctypes.data, None if d is None else d.ctypes.data, len(t), prn, acq_delay_samples, acq_doppler_hz,
+                                 acq_samplestamp, nitems_read)
+        self._rec = np.zeros(4096, dtype=REF_LOOP_REC)
+
+    def feed(self, sig):
+        sig = np.ascontiguousarray(sig, dtype=np.complex64)
+        n = self._r.ref_loop_feed(self._h, sig.ctypes.data, len(sig), self._rec.ctypes.data, len(self._rec))
+        return self._rec[:n].copy()
+
+    def state(self):
+        v = np.zeros(8)
+        self._r.ref_loop_state(self._h, v.ctypes.data)
+        return dict(zip(["state", "carrier_doppler_hz", "cn0_db_hz", "carrier_lock_test", "code_freq_chips", "rem_code_phase_samples", "nitems_read", "prn_length"], v))
+
+    def close(self):
+        if self._h:
+            self._r.ref_loop_free(self._h)
+            self._h = None

@@ -1,0 +1,186 @@
+"""Closed tracking loop on identical synthetic IF (north_star: "tracking-loop lock and PRN/CN0 within 0.1 dB over 60 s").
+
+Product: B200TrackingBank (host C++ loop closure, gnss_sim_receiver_b200/host/) over the GPU multicorrelator, selected through
+the `.conf` implementation string.  Oracle: one loop per channel made of the reference's OWN objects (oracle/ref_loop.cc in
+oracle/_ref: Cpu_Multicorrelator_Real_Codes over the volk_gnsssdr protokernels, Tracking_loop_filter, Tracking_FLL_PLL_filter,
+discriminators, lock detectors, Exponential_Smoother), glue restated from dll_pll_veml_tracking.cc.
+
+Gates: every channel the oracle keeps locked stays locked in the product, same PRN set, same number of
+telemetry symbols with identical signs, CN0 (M2M4) within 0.1 dB, Doppler within 0.5 Hz RMS.
+Duration: GB200_LOOP_SECONDS (default 60).
+"""
+import os
+
+import numpy as np
+import pytest
+
+import _oracle as O
+
+needs_ref = pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built")
+
+FS = 4e6
+SECONDS = float(os.environ.get("GB200_LOOP_SECONDS", "60"))
+CHUNK = 400000  # 100 ms of stream per push
+
+CONF = """
+[GNSS-SDR]
+GNSS-SDR.internal_fs_sps=4000000
+Tracking_1C.implementation=GPS_L1_CA_DLL_PLL_Tracking_B200
+Tracking_1C.item_type=gr_complex
+Tracking_1C.pll_bw_hz=35.0
+Tracking_1C.dll_bw_hz=2.0
+Tracking_1C.early_late_space_chips=0.5
+Tracking_1C.pull_in_time_s=1
+Tracking_1C.cn0_samples=20
+Tracking_1C.cn0_min=25
+Tracking_1C.max_lock_fail=50
+Tracking_1C.max_carrier_lock_fail=5000
+Tracking_1C.carrier_lock_th=0.5
+"""
+
+
+def scenario(nsat, seed=11):
+    rng = np.random.default_rng(seed)
+    prns = rng.choice(np.arange(1, 33), nsat, replace=False)
+    sc = dict(prn=prns, doppler=rng.uniform(-4000, 4000, nsat), delay=rng.uniform(0, 1023, nsat), phase=rng.uniform(0, 2 * np.pi, nsat),
+              cn0=rng.uniform(40, 50, nsat), acq_err=rng.uniform(-15, 15, nsat))
+    bits = rng.choice(np.array([-1, 1], dtype=np.int8), (nsat, 3000))
+    # telemetry preamble 10001011: the block synchronises bits on it (every 300 bits in a real message; every 50 here so that
+    # short runs reach narrow tracking too)
+    pre = np.array([1, -1, -1, -1, 1, -1, 1, 1], dtype=np.int8)
+    for b in range(0, 3000, 50):
+        bits[:, b:b + 8] = pre
+    sc["bits"] = bits
+    sc["codes"] = np.stack([O.gps_l1_ca_code(int(p)) for p in prns])
+    # acquisition hand-over: code start of chip 0 in samples, modulo one code period
+    f_chip = 1.023e6 * (1 + sc["doppler"] / 1575.42e6)
+    sc["acq_delay"] = np.mod(sc["delay"] / f_chip * FS, FS / 1000.0)
+    return sc
+
+
+def ref_params(arch=0):
+    p = O.RefLoopParams()
+    p.fs_in, p.code_period, p.chip_rate, p.carrier_freq, p.carrier_lock_th = FS, 0.001, 1.023e6, 1575.42e6, 0.5
+    p.pll_bw, p.dll_bw, p.fll_bw, p.pll_bw_narrow, p.dll_bw_narrow = 35.0, 2.0, 35.0, 5.0, 0.75
+    p.el, p.vel, p.el_narrow, p.vel_narrow = 0.5, 0.5, 0.15, 0.5
+    p.cn0_smoother_alpha, p.lock_smoother_alpha = 0.002, 0.002
+    p.vector_length, p.veml, p.secondary, p.track_pilot, p.symbols_per_bit, p.samples_per_chip, p.code_length_chips = 4000, 0, 0, 0, 20, 1, 1023
+    p.pll_order, p.dll_order, p.extend = 3, 2, 1
+    p.cn0_samples, p.cn0_min, p.max_code_lock_fail, p.max_carrier_lock_fail = 20, 25, 50, 5000
+    p.cn0_smoother_samples, p.lock_smoother_samples = 200, 25
+    p.carrier_aiding, p.enable_fll_pull_in, p.enable_fll_steady, p.interchange_iq, p.arch, p.correlation_length_ms = 1, 0, 0, 0, arch, 1
+    p.pull_in_time_s, p.bit_sync_time_limit_s = 1, 20
+    pre = "".join(c * 20 for c in "10001011")
+    p.secondary_code_length, p.data_secondary_code_length = 160, 0
+    p.secondary_code = pre.encode()
+    return p
+
+
+def stream_chunks(sc, seconds):
+    n_total = int(seconds * FS)
+    for first in range(0, n_total, CHUNK):
+        n = min(CHUNK, n_total - first)
+        yield first, O.gen_if(n, first, FS, sc["codes"], sc["doppler"], sc["delay"], sc["phase"], sc["cn0"], nav_bits=sc["bits"], seed=77)
+
+
+def run_ref_loops(sc, seconds, arch=0):
+    nsat = len(sc["prn"])
+    loops = [O.RefLoop(ref_params(arch), sc["codes"][k], None, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+             for k in range(nsat)]
+    recs = [[] for _ in range(nsat)]
+    for _, x in stream_chunks(sc, seconds):
+        for k, lp in enumerate(loops):
+            recs[k].append(lp.feed(x))
+    states = [lp.state() for lp in loops]
+    for lp in loops:
+        lp.close()
+    return [np.concatenate(r) for r in recs], states
+
+
+@needs_ref
+def test_reference_object_loop_locks_on_the_synthetic_signal():
+    """Sanity of the oracle itself (CPU): 4 s, 2 channels — reaches narrow tracking, Doppler and CN0 near the truth."""
+    sc = scenario(2, seed=3)
+    recs, states = run_ref_loops(sc, 4.0)
+    for k in range(2):
+        assert states[k]["state"] == 4, states[k]
+        assert abs(states[k]["carrier_doppler_hz"] - sc["doppler"][k]) < 5.0
+        assert abs(states[k]["cn0_db_hz"] - sc["cn0"][k]) < 2.0
+        r = recs[k]
+        assert len(r) > 50 and np.all(r["valid"] == 1)
+        # telemetry symbols: 20 ms sums of the prompt reproduce the generated nav bits up to the PLL's half-cycle sign
+        sym = np.sign(r["prompt_i"])
+        f_chip = 1.023e6 * (1 + sc["doppler"][k] / 1575.42e6)
+        t_end = (r["tracking_sample_counter"].astype(np.float64) - 2000) / FS  # middle of the last code period of the bit
+        bit_idx = np.floor((t_end * f_chip - sc["delay"][k]) / (1023 * 20)).astype(int) % sc["bits"].shape[1]
+        truth = sc["bits"][k][bit_idx]
+        agree = np.mean(sym == truth)
+        assert agree > 0.99 or agree < 0.01, agree
+
+
+@pytest.mark.gpu
+@needs_ref
+def test_closed_loop_parity_vs_reference_objects():
+    from gnss_sim_receiver_b200 import _hostapi as H
+    nsat = 8
+    sc = scenario(nsat)
+    bank = H.TrackingBank(CONF, "Tracking_1C", nsat)
+    for k in range(nsat):
+        bank.start(k, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+    loops = [O.RefLoop(ref_params(0), sc["codes"][k], None, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+             for k in range(nsat)]
+    got, ref = [[] for _ in range(nsat)], [[] for _ in range(nsat)]
+    for _, x in stream_chunks(sc, SECONDS):
+        bank.push(x)
+        r = bank.step()
+        for k in range(nsat):
+            got[k].append(r[r["channel"] == k])
+            ref[k].append(loops[k].feed(x))
+    launches = bank.launches
+    for k in range(nsat):
+        g, r = np.concatenate(got[k]), np.concatenate(ref[k])
+        gs, rs = bank.channel_state(k), loops[k].state()
+        assert rs["state"] == 4, (k, rs)  # the oracle keeps every channel of this scenario locked ...
+        assert gs["state"] == 4, (k, gs)  # ... and so does the product
+        assert np.all(g["prn"] == sc["prn"][k]) and np.all(g["valid"] == 1) and np.all(r["valid"] == 1)
+        assert len(g) == len(r), (k, len(g), len(r))
+        assert np.array_equal(g["tracking_sample_counter"], r["tracking_sample_counter"]), k
+        assert np.array_equal(np.sign(g["prompt_i"]), np.sign(r["prompt_i"])), k
+        half = len(g) // 2
+        d_cn0 = np.max(np.abs(g["cn0_db_hz"][half:] - r["cn0_db_hz"][half:]))
+        d_dop = np.sqrt(np.mean((g["carrier_doppler_hz"][half:] - r["carrier_doppler_hz"][half:]) ** 2))
+        assert d_cn0 < 0.1, (k, d_cn0)   # dB
+        assert d_dop < 0.5, (k, d_dop)   # Hz RMS
+        assert abs(gs["cn0_db_hz"] - sc["cn0"][k]) < 2.0 and abs(gs["carrier_doppler_hz"] - sc["doppler"][k]) < 5.0
+    # one launch per code period for all channels (plus the odd extra round when read pointers straddle a push)
+    assert launches < 1.2 * SECONDS * 1000, launches
+    for lp in loops:
+        lp.close()
+    bank.close()
+
+
+@pytest.mark.gpu
+@needs_ref
+def test_thread_per_block_form_matches_the_lock_step_bank():
+    """The GNU Radio shape (one host thread per tracking block calling general_work through the per-channel facade, requests
+    batched by the engine) gives the same records as the lock-step bank."""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    nsat, seconds = 4, 1.5
+    sc = scenario(nsat, seed=5)
+    x = np.concatenate([c for _, c in stream_chunks(sc, seconds)])
+    a, b = H.TrackingBank(CONF, "Tracking_1C", nsat), H.TrackingBank(CONF, "Tracking_1C", nsat)
+    for bank in (a, b):
+        for k in range(nsat):
+            bank.start(k, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+    a.push(x)
+    ra = a.step()
+    rb = b.run_threaded(x, 0, nsat)
+    for k in range(nsat):
+        ga, gb = ra[ra["channel"] == k], rb[rb["channel"] == k]
+        assert len(ga) == len(gb) and len(ga) > 10
+        assert np.array_equal(ga["tracking_sample_counter"], gb["tracking_sample_counter"])
+        assert np.allclose(ga["prompt_i"], gb["prompt_i"], rtol=0, atol=1e-3 * np.max(np.abs(ga["prompt_i"])))
+        assert np.allclose(ga["carrier_doppler_hz"], gb["carrier_doppler_hz"], atol=1e-6)
+    assert b.launches < a.launches * 4  # requests of concurrent channels share launches
+    a.close()
+    b.close()
