@@ -36,6 +36,7 @@ struct gb200_trk
     size_t partial_ctas{0};
     TrkGroup* h_groups{nullptr};  // pinned
     TrkGroup* d_groups{nullptr};
+    std::vector<std::pair<long long, int>> order;  // scratch of plan_run_kernel
     int last_path{0}, last_groups{0}, last_R{16}, last_G{4};  // path 0: chunked kernel, 1: run-based kernel
     // last enqueued launch (for collect / replay)
     int last_n{0}, last_T{0}, last_chunks{0}, last_cplx{0};

@@ -144,7 +144,10 @@ def test_closed_loop_parity_vs_reference_objects():
         assert gs["state"] == 4, (k, gs)  # ... and so does the product
         assert np.all(g["prn"] == sc["prn"][k]) and np.all(g["valid"] == 1) and np.all(r["valid"] == 1)
         assert len(g) == len(r), (k, len(g), len(r))
-        assert np.array_equal(g["tracking_sample_counter"], r["tracking_sample_counter"]), k
+        # block lengths are floor(T_prn + remnant): a last-bit difference in the code NCO moves a boundary by one sample for a
+        # period, never more, and never accumulates (the remnant carries it)
+        d_cnt = np.abs(g["tracking_sample_counter"].astype(np.int64) - r["tracking_sample_counter"].astype(np.int64))
+        assert d_cnt.max() <= 1, (k, d_cnt.max())
         assert np.array_equal(np.sign(g["prompt_i"]), np.sign(r["prompt_i"])), k
         half = len(g) // 2
         d_cn0 = np.max(np.abs(g["cn0_db_hz"][half:] - r["cn0_db_hz"][half:]))

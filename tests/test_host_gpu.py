@@ -1,0 +1,131 @@
+"""Host C++ layer on the GPU: the acquisition adapter/block driven the way Channel + ChannelFsm drive the reference's
+(set_doppler_*, set_threshold, init, set_local_code, set_state(1), then general_work over the stream), checked against the
+oracle restatement of pcps_acquisition::acquisition_core on the same data-buffer contents; and the acq -> trk hand-over
+(Acq_delay_samples / Acq_doppler_hz / Acq_samplestamp_samples into start_tracking, dll_pll_veml_tracking.cc:643-660,1757-1788).
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import _oracle as O
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+from gen_if import quantise  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+FS = 4e6
+
+CONF = """
+GNSS-SDR.internal_fs_sps=4000000
+Acquisition_1C.implementation=GPS_L1_CA_PCPS_Acquisition_B200
+Acquisition_1C.item_type={item}
+Acquisition_1C.pfa={pfa}
+Acquisition_1C.doppler_max=10000
+Acquisition_1C.doppler_step=250
+Acquisition_1C.max_dwells={dwells}
+Acquisition_1C.blocking_on_standby=true
+Tracking_1C.implementation=GPS_L1_CA_DLL_PLL_Tracking_B200
+Tracking_1C.item_type=gr_complex
+Tracking_1C.early_late_space_chips=0.5
+Tracking_1C.pull_in_time_s=1
+Tracking_1C.cn0_samples=20
+Tracking_1C.cn0_min=25
+Tracking_1C.max_lock_fail=50
+Tracking_1C.max_carrier_lock_fail=5000
+Tracking_1C.carrier_lock_th=0.5
+"""
+
+
+def _stream(n, prn, doppler, delay, cn0, seed=9):
+    codes = np.stack([O.gps_l1_ca_code(prn)])
+    return O.gen_if(n, 0, FS, codes, [doppler], [delay], [0.7], [cn0], seed=seed)
+
+
+def _oracle(block, dwells=1, use_cfar=True):
+    conf = O.acq_conf(FS, 4000, 4000, 10000, 250, float(np.float32(4e6) * np.float32(0.001)), 4, use_cfar=use_cfar, max_dwells=dwells)
+    fc = O.acq_set_local_code(conf, O.gps_l1_ca_code_sampled(block["prn"], int(FS), 4000))
+    grid = None
+    r = None
+    for d, s in enumerate(block["dwells"]):
+        grid = O.acq_dwell(conf, s, fc, grid, d)
+        r = O.acq_statistic(conf, grid, d + 1)
+    return conf, r
+
+
+@pytest.mark.parametrize("item", ["gr_complex", "cshort", "cbyte"])
+def test_acquisition_block_positive_matches_oracle(item):
+    from gnss_sim_receiver_b200 import _hostapi as H
+    prn, doppler, delay = 10, 750.0, 600.0  # the reference's own synthetic acquisition case (gsoc2013 test :204-230)
+    x = _stream(3 * 4000, prn, doppler, delay, 47.0)
+    if item == "gr_complex":
+        items, buf = x, x[:4000]
+    else:
+        q = quantise(x, "ishort" if item == "cshort" else "ibyte")
+        items = q
+        buf = (q[0:8000:2].astype(np.float32) + 1j * q[1:8000:2].astype(np.float32)).astype(np.complex64)
+    a = H.AcquisitionBlock(CONF.format(item=item, pfa=0.01, dwells=1), "Acquisition_1C", prn)
+    a.arm()
+    consumed = a.work(items, chunk=1000)
+    s = a.status()
+    # the block buffered exactly the first consumed_samples items (state 1), then ran (state 2)
+    conf, ro = _oracle(dict(prn=prn, dwells=[buf]))
+    assert s.last_event == 1 and s.active == 0 and s.state == 0
+    assert (s.indext, s.doppler_index) == (ro.indext, ro.doppler_index)
+    assert s.acq_delay_samples == ro.acq_delay_samples and s.acq_doppler_hz == ro.acq_doppler_hz
+    assert abs(s.test_statistics - ro.test_statistics) <= 1e-3 * ro.test_statistics
+    assert s.acq_samplestamp_samples == 4000 and consumed == 4000
+    assert abs(s.threshold - O.acq_threshold(conf, 0.01)) <= 1e-5 * s.threshold
+    # truth: code start = delay / f_chip * fs samples, Doppler bin nearest to 750 Hz
+    assert abs(s.acq_delay_samples - 600.0 / 1.023e6 * FS) <= 2 and s.acq_doppler_hz == 750.0
+    a.close()
+
+
+def test_acquisition_block_negative_after_max_dwells():
+    from gnss_sim_receiver_b200 import _hostapi as H
+    rng = np.random.default_rng(4)
+    x = ((rng.standard_normal(5 * 4000) + 1j * rng.standard_normal(5 * 4000)) / np.sqrt(2)).astype(np.complex64)
+    a = H.AcquisitionBlock(CONF.format(item="gr_complex", pfa=0.001, dwells=2), "Acquisition_1C", 5)
+    a.arm()
+    a.work(x, chunk=4000)
+    s = a.status()
+    conf, ro = _oracle(dict(prn=5, dwells=[x[:4000], x[4000:8000]]), dwells=2)
+    assert s.last_event == 2 and s.active == 0 and s.state == 0  # negative acquisition after max_dwells (:803-818)
+    assert (s.indext, s.doppler_index) == (ro.indext, ro.doppler_index)
+    assert abs(s.test_statistics - ro.test_statistics) <= 1e-3 * ro.test_statistics
+    assert s.test_statistics <= s.threshold
+    a.close()
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built")
+def test_acquisition_to_tracking_handover():
+    """Acquire on the first millisecond, start tracking from the Gnss_Synchro the block filled, reach narrow tracking."""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    prn, doppler, delay, cn0 = 17, -2230.0, 311.4, 46.0
+    bits = np.ones((1, 3000), dtype=np.int8)
+    bits[0, ::2] = -1
+    pre = np.array([1, -1, -1, -1, 1, -1, 1, 1], dtype=np.int8)
+    for b in range(0, 3000, 50):
+        bits[0, b:b + 8] = pre
+    codes = np.stack([O.gps_l1_ca_code(prn)])
+    n = int(3.5 * FS)
+    x = O.gen_if(n, 0, FS, codes, [doppler], [delay], [1.1], [cn0], nav_bits=bits, seed=21)
+    a = H.AcquisitionBlock(CONF.format(item="gr_complex", pfa=0.01, dwells=1), "Acquisition_1C", prn)
+    a.arm()
+    a.work(x[:12000], chunk=2000)
+    s = a.status()
+    assert s.last_event == 1 and s.acq_doppler_hz == -2250.0
+    bank = H.TrackingBank(CONF.format(item="gr_complex", pfa=0.01, dwells=1), "Tracking_1C", 1)
+    bank.start(0, prn, s.acq_delay_samples, s.acq_doppler_hz, s.acq_samplestamp_samples, s.acq_samplestamp_samples)
+    recs = []
+    for first in range(0, n, 400000):
+        bank.push(x[first:first + 400000])
+        recs.append(bank.step())
+    st = bank.channel_state(0)
+    r = np.concatenate(recs)
+    assert st["state"] == 4, st
+    assert abs(st["carrier_doppler_hz"] - doppler) < 5.0 and abs(st["cn0_db_hz"] - cn0) < 2.0
+    assert len(r) > 50 and np.all(r["valid"] == 1) and np.all(r["prn"] == prn)
+    bank.close()
+    a.close()
