@@ -49,15 +49,47 @@ namespace
 {
 constexpr double TWO_PI = 6.283185307179586476925286766559;
 
+// Stage radices in DIF order, even factors first (the late, short-stride stages are the odd ones).  Pairs of equal small
+// factors are fused into one register-resident pass (16 = 4x4, 8 = 4x2, 9 = 3x3, 25 = 5x5; acq_fft.cuh: fft_smem_stage2):
+// 25000 = 8 * 25 * 25 * 5 takes 4 passes over shared memory instead of 7.  GB200_ACQ_PLAIN_RADIX=1 keeps the plain stages.
 bool factor_235(int n, std::vector<int>& radix)
 {
     radix.clear();
-    while (n % 4 == 0) { radix.push_back(4); n /= 4; }
-    while (n % 2 == 0) { radix.push_back(2); n /= 2; }
-    while (n % 3 == 0) { radix.push_back(3); n /= 3; }
-    while (n % 5 == 0) { radix.push_back(5); n /= 5; }
-    while (n % 7 == 0) { radix.push_back(7); n /= 7; }
-    return n == 1 && (int)radix.size() <= FFT_MAX_STAGES;
+    const bool fuse = getenv("GB200_ACQ_PLAIN_RADIX") == nullptr;
+    int c2 = 0, c3 = 0, c5 = 0, c7 = 0;
+    while (n % 2 == 0) { c2++; n /= 2; }
+    while (n % 3 == 0) { c3++; n /= 3; }
+    while (n % 5 == 0) { c5++; n /= 5; }
+    while (n % 7 == 0) { c7++; n /= 7; }
+    if (n != 1) return false;
+    if (fuse)
+        {
+            while (c2 >= 4) { radix.push_back(16); c2 -= 4; }
+            if (c2 == 3) { radix.push_back(8); c2 = 0; }
+        }
+    while (c2 >= 2) { radix.push_back(4); c2 -= 2; }
+    if (c2) radix.push_back(2);
+    if (fuse)
+        while (c3 >= 2) { radix.push_back(9); c3 -= 2; }
+    while (c3--) radix.push_back(3);
+    if (fuse)
+        while (c5 >= 2) { radix.push_back(25); c5 -= 2; }
+    while (c5--) radix.push_back(5);
+    while (c7--) radix.push_back(7);
+    return (int)radix.size() <= FFT_MAX_STAGES;
+}
+
+// the plain factors of a (possibly fused) stage radix, in the order the stage applies them
+void stage_factors(int r, int* f1, int* f2)
+{
+    switch (r)
+        {
+        case 16: *f1 = 4; *f2 = 4; break;
+        case 8: *f1 = 4; *f2 = 2; break;
+        case 9: *f1 = 3; *f2 = 3; break;
+        case 25: *f1 = 5; *f2 = 5; break;
+        default: *f1 = r; *f2 = 1; break;
+        }
 }
 
 int make_plan(gb200_acq* h, int max_smem)
@@ -89,7 +121,7 @@ int make_plan(gb200_acq* h, int max_smem)
             n_s /= radix[s];
         }
     h->smem = (size_t)pl.m * sizeof(float2) + tab_bytes;
-    h->threads = std::min(1024, std::max(128, ((pl.m / 8) + 63) / 64 * 64));
+    h->threads = std::min(512, std::max(128, ((pl.m / 8) + 63) / 64 * 64));  // 512: the fused radix-25 pass holds 25 points per thread (128 registers)
     // natural index -> position after the DIF stages (global stage first)
     h->pos_of_k.resize(N);
     for (int k = 0; k < N; k++)
@@ -102,7 +134,13 @@ int make_plan(gb200_acq* h, int max_smem)
                 size = m;
             };
             if (g > 1) digit(g);
-            for (int s = 0; s < pl.n_stages; s++) digit(pl.radix[s]);
+            for (int s = 0; s < pl.n_stages; s++)
+                {
+                    int f1, f2;
+                    stage_factors(pl.radix[s], &f1, &f2);
+                    digit(f1);
+                    if (f2 > 1) digit(f2);
+                }
             h->pos_of_k[k] = p;
         }
     return GB200_OK;

@@ -186,6 +186,100 @@ __device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, un
     __syncthreads();
 }
 
+// Two consecutive in-place stages (radix R1 on sub-blocks of n_s points, then radix R2 on their n_s / R1 point halves)
+// fused in registers: one pass over shared memory and one barrier instead of two.  The data layout before and after is
+// exactly that of the two separate stages, so plans may mix fused and plain stages freely.  A thread owns the R1 * R2
+// points  base + k * ms1 + k2 * ms2  (k < R1, k2 < R2).
+template <int R1, int R2, bool INV>
+__device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, int n, const float2* sA, const float2* sB)
+{
+    const int ms1 = n_s / R1, ms2 = ms1 / R2;
+    const int nb = m_blk / (R1 * R2);
+    const int tw1 = n / n_s, tw2 = n / ms1;
+    for (int id = threadIdx.x; id < nb; id += blockDim.x)
+        {
+            const int blk = id / ms2;
+            const int j = id - blk * ms2;
+            float2* p = x + blk * n_s + j;
+            float2 v[R1][R2];
+#pragma unroll
+            for (int k = 0; k < R1; k++)
+#pragma unroll
+                for (int k2 = 0; k2 < R2; k2++) v[k][k2] = p[k * ms1 + k2 * ms2];
+            // second-stage twiddles W_{ms1}^{j * k2} (shared by all k)
+            float2 wb[R2];
+            if (ms2 > 1)
+                {
+                    wb[1] = fft_twiddle(sA, sB, j * tw2);
+#pragma unroll
+                    for (int k2 = 2; k2 < R2; k2++) wb[k2] = cmul(wb[k2 - 1], wb[1]);
+                }
+            if (INV)
+                {
+#pragma unroll
+                    for (int k = 0; k < R1; k++)
+                        {
+                            float2 t[R2];
+#pragma unroll
+                            for (int k2 = 0; k2 < R2; k2++) t[k2] = (ms2 > 1 && k2 > 0) ? cmulc(v[k][k2], wb[k2]) : v[k][k2];
+                            Dft<R2, true>::run(t);
+#pragma unroll
+                            for (int k2 = 0; k2 < R2; k2++) v[k][k2] = t[k2];
+                        }
+                }
+#pragma unroll
+            for (int k2 = 0; k2 < R2; k2++)
+                {
+                    // first-stage twiddles W_{n_s}^{(k2 * ms2 + j) * k}
+                    const float2 w1 = fft_twiddle(sA, sB, (k2 * ms2 + j) * tw1);
+                    float2 t[R1];
+#pragma unroll
+                    for (int k = 0; k < R1; k++) t[k] = v[k][k2];
+                    if (INV)
+                        {
+                            float2 w = w1;
+#pragma unroll
+                            for (int k = 1; k < R1; k++)
+                                {
+                                    t[k] = cmulc(t[k], w);
+                                    if (k + 1 < R1) w = cmul(w, w1);
+                                }
+                        }
+                    Dft<R1, INV>::run(t);
+                    if (!INV)
+                        {
+                            float2 w = w1;
+#pragma unroll
+                            for (int k = 1; k < R1; k++)
+                                {
+                                    t[k] = cmul(t[k], w);
+                                    if (k + 1 < R1) w = cmul(w, w1);
+                                }
+                        }
+#pragma unroll
+                    for (int k = 0; k < R1; k++) v[k][k2] = t[k];
+                }
+            if (!INV)
+                {
+#pragma unroll
+                    for (int k = 0; k < R1; k++)
+                        {
+                            float2 t[R2];
+#pragma unroll
+                            for (int k2 = 0; k2 < R2; k2++) t[k2] = v[k][k2];
+                            Dft<R2, false>::run(t);
+#pragma unroll
+                            for (int k2 = 0; k2 < R2; k2++) v[k][k2] = (ms2 > 1 && k2 > 0) ? cmul(t[k2], wb[k2]) : t[k2];
+                        }
+                }
+#pragma unroll
+            for (int k = 0; k < R1; k++)
+#pragma unroll
+                for (int k2 = 0; k2 < R2; k2++) p[k * ms1 + k2 * ms2] = v[k][k2];
+        }
+    __syncthreads();
+}
+
 template <bool INV>
 __device__ __forceinline__ void fft_smem_stage_any(int R, float2* x, int m_blk, int n_s, unsigned inv_ms, int n, const float2* sA, const float2* sB)
 {
@@ -195,6 +289,10 @@ __device__ __forceinline__ void fft_smem_stage_any(int R, float2* x, int m_blk, 
         case 3: fft_smem_stage<3, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
         case 4: fft_smem_stage<4, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
         case 5: fft_smem_stage<5, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
+        case 8: fft_smem_stage2<4, 2, INV>(x, m_blk, n_s, n, sA, sB); break;    // fused pairs: same layout as the two plain stages
+        case 9: fft_smem_stage2<3, 3, INV>(x, m_blk, n_s, n, sA, sB); break;
+        case 16: fft_smem_stage2<4, 4, INV>(x, m_blk, n_s, n, sA, sB); break;
+        case 25: fft_smem_stage2<5, 5, INV>(x, m_blk, n_s, n, sA, sB); break;
         default: fft_smem_stage<7, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
         }
 }

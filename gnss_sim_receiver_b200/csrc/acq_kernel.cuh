@@ -100,7 +100,7 @@ __global__ void acq_phase_table_kernel(const float* __restrict__ inc, int n_bins
 //   SRC_IQ = false: input = cf32 buffer src[batch][N] (output of the global stage, or a zero-padded code replica)
 // Output dst[batch][N] in digit-reversed order, optionally conjugated (code spectra, pcps_acquisition.cc:207).
 template <int IQ, bool SRC_IQ>
-__global__ void __launch_bounds__(1024) acq_fwd_kernel(FftPlan pl, const void* __restrict__ src, int consumed, const unsigned long long* __restrict__ dphi, const float* __restrict__ phase_tab,
+__global__ void __launch_bounds__(512) acq_fwd_kernel(FftPlan pl, const void* __restrict__ src, int consumed, const unsigned long long* __restrict__ dphi, const float* __restrict__ phase_tab,
     const float2* __restrict__ gA, const float2* __restrict__ gB, float2* __restrict__ dst, int conj_out)
 {
     extern __shared__ __align__(16) float2 sm[];

@@ -109,7 +109,7 @@ def test_acquisition_to_tracking_handover():
     for b in range(0, 3000, 50):
         bits[0, b:b + 8] = pre
     codes = np.stack([O.gps_l1_ca_code(prn)])
-    n = int(3.5 * FS)
+    n = int(5 * FS)  # pull-in ends 2 s after the acquisition stamp (integer seconds, strict '<'), bit sync within 1 s after
     x = O.gen_if(n, 0, FS, codes, [doppler], [delay], [1.1], [cn0], nav_bits=bits, seed=21)
     a = H.AcquisitionBlock(CONF.format(item="gr_complex", pfa=0.01, dwells=1), "Acquisition_1C", prn)
     a.arm()
