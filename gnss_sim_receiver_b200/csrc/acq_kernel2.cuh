@@ -16,11 +16,47 @@ __global__ void __launch_bounds__(512) acq_inv_kernel(AcqParams p, const float2*
     float2* x = sm;
     float2* sA = sm + pl.m;
     float2* sB = sA + pl.n_hi;
-    fft_load_tables(pl, gA, gB, sA, sB);
     const int bin = blockIdx.y, si = blockIdx.z;
     const size_t blk_off = (size_t)blockIdx.x * pl.m;
     const float2* xs = X + (size_t)bin * pl.n + blk_off;
-    if (MODE == 2)
+    // Stage X[bin] with one TMA bulk copy (no register staging, the copy engine keeps the L2 pipe full) while the threads
+    // load the twiddle tables; then multiply in place by the code spectrum, read with 128-bit loads four deep.
+    __shared__ __align__(8) uint64_t s_bar;
+    const bool bulk = (pl.m & 1) == 0 && ((size_t)pl.n & 1) == 0;  // 16-byte alignment of every block start and length
+    if (bulk && threadIdx.x == 0)
+        {
+            mbar_init(&s_bar, 1);
+            fence_barrier_init();
+            mbar_expect_tx(&s_bar, (uint32_t)pl.m * 8u);
+            bulk_g2s(x, xs, (uint32_t)pl.m * 8u, &s_bar);
+        }
+    fft_load_tables(pl, gA, gB, sA, sB);
+    if (bulk)
+        {
+            __syncthreads();  // the barrier word is initialised before anyone polls it
+            mbar_wait(&s_bar, 0);
+            if (MODE != 2)
+                {
+                    const float4* cs4 = reinterpret_cast<const float4*>(Cs + (size_t)slots[si] * pl.n + blk_off);
+                    float4* x4 = reinterpret_cast<float4*>(x);
+                    const int n4 = pl.m >> 1, step = blockDim.x;
+                    for (int i0 = threadIdx.x; i0 < n4; i0 += 4 * step)
+                        {
+                            float4 c[4];
+#pragma unroll
+                            for (int u = 0; u < 4; u++)
+                                if (i0 + u * step < n4) c[u] = __ldg(cs4 + i0 + u * step);
+#pragma unroll
+                            for (int u = 0; u < 4; u++)
+                                if (i0 + u * step < n4)
+                                    {
+                                        const float4 a = x4[i0 + u * step];  // volk_32fc_x2_multiply_32fc, :650
+                                        x4[i0 + u * step] = make_float4(a.x * c[u].x - a.y * c[u].y, a.x * c[u].y + a.y * c[u].x, a.z * c[u].z - a.w * c[u].w, a.z * c[u].w + a.w * c[u].z);
+                                    }
+                        }
+                }
+        }
+    else if (MODE == 2)
         {
             for (int i = threadIdx.x; i < pl.m; i += blockDim.x) x[i] = xs[i];
         }

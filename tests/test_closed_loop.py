@@ -169,7 +169,7 @@ def test_thread_per_block_form_matches_the_lock_step_bank():
     """The GNU Radio shape (one host thread per tracking block calling general_work through the per-channel facade, requests
     batched by the engine) gives the same records as the lock-step bank."""
     from gnss_sim_receiver_b200 import _hostapi as H
-    nsat, seconds = 4, 1.5
+    nsat, seconds = 4, 4.0  # pull-in ends 2 s after the acquisition stamp, bit sync follows within 1 s
     sc = scenario(nsat, seed=5)
     x = np.concatenate([c for _, c in stream_chunks(sc, seconds)])
     a, b = H.TrackingBank(CONF, "Tracking_1C", nsat), H.TrackingBank(CONF, "Tracking_1C", nsat)
