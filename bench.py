@@ -257,12 +257,8 @@ def dist_setup(n_gpus):
 
 
 def reduce_max(dist, local, x):
-    if dist is None:
-        return x
-    import torch
-    t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    from gnss_sim_receiver_b200.sharding import reduce_max as _rm
+    return _rm(dist, x, device=f"cuda:{local}")
 
 
 def barrier(dist):

@@ -4,7 +4,7 @@
 tag=${1:-rXX}
 mkdir -p gpurun_out
 nproc > gpurun_out/${tag}_host.txt; lscpu | grep -i "model name" >> gpurun_out/${tag}_host.txt
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${tag}_pytest.log
+timeout 1800 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${tag}_pytest.log
 timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?" >> gpurun_out/${tag}_bench.err
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${tag}_bench_ref.json 2>> gpurun_out/${tag}_bench.err
 timeout 300 python tools/prof_trk.py 10240 3 > gpurun_out/${tag}_prof_trk.log 2>&1 && {
