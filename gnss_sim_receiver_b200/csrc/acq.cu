@@ -21,7 +21,9 @@ struct gb200_acq
     int doppler_max{0}, doppler_step{0}, doppler_center{0};
     int keep_grid{0}, user_keep{0};
     std::vector<int> pos_of_k;  // natural index -> digit-reversed position
-    float2 *d_twA{nullptr}, *d_twB{nullptr};
+    float2 *d_twA{nullptr}, *d_twB{nullptr};  // two-level W_N table for the global stages
+    float2* d_twT{nullptr};                   // per-stage tables of the shared-memory stages (FftPlan::tw_off)
+    std::vector<float2> tw_stage;
     void* d_iq{nullptr};
     float2* d_X{nullptr};        // [n_bins][N] forward spectra of the wiped input
     float2* d_C{nullptr};        // [max_prns][N] conjugated code spectra
@@ -52,10 +54,9 @@ constexpr double TWO_PI = 6.283185307179586476925286766559;
 // Stage radices in DIF order, even factors first (the late, short-stride stages are the odd ones).  Pairs of equal small
 // factors are fused into one register-resident pass (16 = 4x4, 8 = 4x2, 9 = 3x3, 25 = 5x5; acq_fft.cuh: fft_smem_stage2):
 // 25000 = 8 * 25 * 25 * 5 takes 4 passes over shared memory instead of 7.  GB200_ACQ_PLAIN_RADIX=1 keeps the plain stages.
-bool factor_235(int n, std::vector<int>& radix)
+bool factor_235(int n, std::vector<int>& radix, bool fuse)
 {
     radix.clear();
-    const bool fuse = getenv("GB200_ACQ_PLAIN_RADIX") == nullptr;
     int c2 = 0, c3 = 0, c5 = 0, c7 = 0;
     while (n % 2 == 0) { c2++; n /= 2; }
     while (n % 3 == 0) { c3++; n /= 3; }
@@ -92,35 +93,83 @@ void stage_factors(int r, int* f1, int* f2)
         }
 }
 
+// stage tables of a plan over blocks of m points (FftPlan::tw_off): returns the entry count, fills `tab` when given
+int build_stage_tables(FftPlan& pl, std::vector<float2>* tab)
+{
+    int off = 0, n_s = pl.m;
+    for (int s = 0; s < pl.n_stages; s++)
+        {
+            int f1, f2;
+            stage_factors(pl.radix[s], &f1, &f2);
+            const int ms1 = n_s / f1;
+            const int jmax = f2 > 1 ? ms1 / f2 : ms1;  // butterfly positions j < jmax
+            const int nh = (jmax + FFT_TW_STAGE_LO - 1) / FFT_TW_STAGE_LO;
+            pl.tw_off[s] = off;
+            pl.tw_nh[s] = nh;
+            const int n_tab = f2 > 1 ? 2 : 1;
+            if (tab)
+                for (int t = 0; t < n_tab; t++)
+                    {
+                        const double base = t == 0 ? (double)n_s : (double)ms1;  // W_{n_s}^j, W_{ms1}^j
+                        for (int l = 0; l < FFT_TW_STAGE_LO; l++)
+                            {
+                                const double a = -TWO_PI * (double)l / base;
+                                tab->push_back(make_float2((float)std::cos(a), (float)std::sin(a)));
+                            }
+                        for (int q = 0; q < nh; q++)
+                            {
+                                const double a = -TWO_PI * (double)(q * FFT_TW_STAGE_LO) / base;
+                                tab->push_back(make_float2((float)std::cos(a), (float)std::sin(a)));
+                            }
+                    }
+            off += n_tab * (FFT_TW_STAGE_LO + nh);
+            n_s /= pl.radix[s];
+        }
+    pl.n_tw = off;
+    return off;
+}
+
 int make_plan(gb200_acq* h, int max_smem)
 {
     const int N = h->cfg.fft_size;
     FftPlan& pl = h->plan;
+    if (N < 8) return set_error(GB200_EINVAL, "fft_size %d: at least 8 points", N);
     pl.n = N;
     pl.n_hi = (N + FFT_TW_LO - 1) / FFT_TW_LO;
-    const size_t tab_bytes = (size_t)(pl.n_hi + FFT_TW_LO) * sizeof(float2);
+    const bool fuse = getenv("GB200_ACQ_PLAIN_RADIX") == nullptr;
+    std::vector<int> radix;
     int g = 0;
-    for (int r = 1; r <= 8; r++)
-        if (N % r == 0 && (size_t)(N / r) * sizeof(float2) + tab_bytes <= (size_t)max_smem)
-            {
-                g = r;
-                break;
-            }
+    for (int r = 1; r <= 8 && !g; r++)
+        {
+            if (N % r) continue;
+            pl.m = N / r;
+            if (!factor_235(pl.m, radix, fuse)) return set_error(GB200_EINVAL, "fft_size %d has a prime factor other than 2, 3, 5, 7", N);
+            // the inverse kernel fuses the code product into its first stage and the search into its last: two stages at least
+            if (radix.size() < 2) factor_235(pl.m, radix, false);
+            if (radix.size() == 1 && radix[0] == 4) radix = {2, 2};
+            if (radix.size() < 2) continue;
+            pl.n_stages = (int)radix.size();
+            for (int s = 0; s < pl.n_stages; s++) pl.radix[s] = radix[s];
+            const size_t bytes = ((size_t)pl.m + build_stage_tables(pl, nullptr)) * sizeof(float2);
+            if (bytes <= (size_t)max_smem)
+                {
+                    g = r;
+                    h->smem = bytes;
+                }
+        }
     if (!g) return set_error(GB200_EINVAL, "fft_size %d: no split into <= 8 shared-memory blocks", N);
     pl.g_radix = g;
     pl.m = N / g;
-    std::vector<int> radix;
-    if (!factor_235(pl.m, radix)) return set_error(GB200_EINVAL, "fft_size %d has a prime factor other than 2, 3, 5, 7", N);
-    pl.n_stages = (int)radix.size();
     int n_s = pl.m;
     for (int s = 0; s < pl.n_stages; s++)
         {
-            pl.radix[s] = radix[s];
             const unsigned ms = (unsigned)(n_s / radix[s]);
             pl.inv_ms[s] = ms == 1 ? 0u : (unsigned)((0x100000000ull + ms - 1) / ms);
             n_s /= radix[s];
         }
-    h->smem = (size_t)pl.m * sizeof(float2) + tab_bytes;
+    pl.perm_rl = pl.radix[pl.n_stages - 1];
+    h->tw_stage.clear();
+    build_stage_tables(pl, &h->tw_stage);
     h->threads = std::min(512, std::max(128, ((pl.m / 8) + 63) / 64 * 64));  // 512: the fused radix-25 pass holds 25 points per thread (128 registers)
     // natural index -> position after the DIF stages (global stage first)
     h->pos_of_k.resize(N);
@@ -169,7 +218,7 @@ cudaError_t forward_iq(gb200_acq* h, int batch, float2* dst)
     if (pl.g_radix == 1)
         {
             if ((e = opt_in_smem(acq_fwd_kernel<IQ, true>, h->smem)) != cudaSuccess) return e;
-            acq_fwd_kernel<IQ, true><<<dim3(1, batch), h->threads, h->smem, h->stream>>>(pl, h->d_iq, h->cfg.consumed_samples, h->d_dphi, h->exact_wipeoff ? nullptr : h->d_phase, h->d_twA, h->d_twB, dst, 0);
+            acq_fwd_kernel<IQ, true><<<dim3(1, batch), h->threads, h->smem, h->stream>>>(pl, h->d_iq, h->cfg.consumed_samples, h->d_dphi, h->exact_wipeoff ? nullptr : h->d_phase, h->d_twT, dst, 0);
             count_launch();
             return cudaGetLastError();
         }
@@ -177,7 +226,7 @@ cudaError_t forward_iq(gb200_acq* h, int batch, float2* dst)
     count_launch();
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     if ((e = opt_in_smem(acq_fwd_kernel<0, false>, h->smem)) != cudaSuccess) return e;
-    acq_fwd_kernel<0, false><<<dim3(pl.g_radix, batch), h->threads, h->smem, h->stream>>>(pl, h->d_stage, 0, nullptr, nullptr, h->d_twA, h->d_twB, dst, 0);
+    acq_fwd_kernel<0, false><<<dim3(pl.g_radix, batch), h->threads, h->smem, h->stream>>>(pl, h->d_stage, 0, nullptr, nullptr, h->d_twT, dst, 0);
     count_launch();
     return cudaGetLastError();
 }
@@ -198,7 +247,7 @@ cudaError_t forward_cf32(gb200_acq* h, float2* dst, int conj_out)
             src = tmp;
         }
     if ((e = opt_in_smem(acq_fwd_kernel<0, false>, h->smem)) != cudaSuccess) return e;
-    acq_fwd_kernel<0, false><<<dim3(pl.g_radix, 1), h->threads, h->smem, h->stream>>>(pl, src, 0, nullptr, nullptr, h->d_twA, h->d_twB, dst, conj_out);
+    acq_fwd_kernel<0, false><<<dim3(pl.g_radix, 1), h->threads, h->smem, h->stream>>>(pl, src, 0, nullptr, nullptr, h->d_twT, dst, conj_out);
     count_launch();
     return cudaGetLastError();
 }

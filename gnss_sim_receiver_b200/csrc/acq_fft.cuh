@@ -27,7 +27,17 @@ struct FftPlan
     int n_hi;      // entries of twiddle table A
     int radix[FFT_MAX_STAGES];      // DIF order
     unsigned inv_ms[FFT_MAX_STAGES];  // ceil(2^32 / ms) (0 when ms == 1) for the per-stage butterfly -> (block, j2) split
+    // per-stage twiddle tables (shared-memory stages): stage s owns entries [tw_off[s], tw_off[s+1]) of the stage-table block,
+    // laid out  lo1[32] hi1[tw_nh] (base W_{n_s})  and, for fused stages,  lo2[32] hi2[tw_nh] (base W_{n_s / R1}):
+    // W^j = hi[j >> 5] * lo[j & 31], indexed by the butterfly position j, so a warp reads consecutive lo entries (no bank
+    // conflicts) and one or two hi entries (broadcast)
+    int tw_off[FFT_MAX_STAGES];
+    int tw_nh[FFT_MAX_STAGES];
+    int n_tw;      // entries of the stage-table block
+    int perm_rl;   // full radix of the last DIF stage: code spectra are stored [q][butterfly] within a block (see acq_inv_kernel)
 };
+
+constexpr int FFT_TW_STAGE_LO = 32;
 
 __device__ __forceinline__ float2 cmul(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 __device__ __forceinline__ float2 cmulc(float2 a, float2 b) { return make_float2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y); }  // a * conj(b)
@@ -44,6 +54,68 @@ __device__ __forceinline__ float2 rot90(float2 a)
 __device__ __forceinline__ float2 fft_twiddle(const float2* sA, const float2* sB, int e)
 {
     return cmul(sA[e >> FFT_TW_SHIFT], sB[e & (FFT_TW_LO - 1)]);
+}
+
+// W^j from one stage table (see FftPlan::tw_off)
+__device__ __forceinline__ float2 fft_stage_twiddle(const float2* t, int j)
+{
+    return cmul(t[FFT_TW_STAGE_LO + (j >> 5)], t[j & (FFT_TW_STAGE_LO - 1)]);
+}
+
+// W_M^k = exp(-2*pi*i*k/M) as literals (k is a compile-time constant after unrolling)
+template <int M>
+__device__ __forceinline__ float2 fft_wconst(int k);
+template <>
+__device__ __forceinline__ float2 fft_wconst<7>(int k)
+{
+    switch (k)
+        {
+        case 1: return make_float2(0.62348980185873359f, -0.7818314824680298f);
+        case 2: return make_float2(-0.22252093395631434f, -0.97492791218182362f);
+        case 3: return make_float2(-0.90096886790241903f, -0.43388373911755823f);
+        case 4: return make_float2(-0.90096886790241915f, 0.43388373911755801f);
+        case 5: return make_float2(-0.22252093395631459f, 0.97492791218182362f);
+        case 6: return make_float2(0.62348980185873337f, 0.78183148246802991f);
+        default: return make_float2(1.0f, 0.0f);
+        }
+}
+template <>
+__device__ __forceinline__ float2 fft_wconst<8>(int k)
+{
+    return k == 1 ? make_float2(0.70710678118654757f, -0.70710678118654746f) : make_float2(1.0f, 0.0f);
+}
+template <>
+__device__ __forceinline__ float2 fft_wconst<9>(int k)
+{
+    switch (k)
+        {
+        case 1: return make_float2(0.76604444311897801f, -0.64278760968653925f);
+        case 2: return make_float2(0.17364817766693041f, -0.98480775301220802f);
+        default: return make_float2(1.0f, 0.0f);
+        }
+}
+template <>
+__device__ __forceinline__ float2 fft_wconst<16>(int k)
+{
+    switch (k)
+        {
+        case 1: return make_float2(0.92387953251128674f, -0.38268343236508978f);
+        case 2: return make_float2(0.70710678118654757f, -0.70710678118654746f);
+        case 3: return make_float2(0.38268343236508984f, -0.92387953251128674f);
+        default: return make_float2(1.0f, 0.0f);
+        }
+}
+template <>
+__device__ __forceinline__ float2 fft_wconst<25>(int k)
+{
+    switch (k)
+        {
+        case 1: return make_float2(0.96858316112863108f, -0.24868988716485479f);
+        case 2: return make_float2(0.87630668004386358f, -0.48175367410171532f);
+        case 3: return make_float2(0.72896862742141155f, -0.68454710592868862f);
+        case 4: return make_float2(0.53582679497899655f, -0.84432792550201508f);
+        default: return make_float2(1.0f, 0.0f);
+        }
 }
 
 template <int R, bool INV>
@@ -110,42 +182,52 @@ struct Dft<5, INV>
     }
 };
 
-// generic O(R^2) butterfly with coefficients from the twiddle tables: W_R^q = W_N^{q * N / R}
-template <int R, bool INV>
-__device__ __forceinline__ void dft_generic(float2* v, const float2* sA, const float2* sB, int n)
-{
-    float2 y[R];
-    const int unit = n / R;
-#pragma unroll
-    for (int k = 0; k < R; k++)
-        {
-            float2 acc = v[0];
-#pragma unroll
-            for (int j = 1; j < R; j++)
-                {
-                    const float2 w = fft_twiddle(sA, sB, ((j * k) % R) * unit);
-                    acc = cadd(acc, INV ? cmulc(v[j], w) : cmul(v[j], w));
-                }
-            y[k] = acc;
-        }
-#pragma unroll
-    for (int k = 0; k < R; k++) v[k] = y[k];
-}
-
+// O(R^2) radix-7 butterfly with literal coefficients W_7^q
 template <bool INV>
 struct Dft<7, INV>
 {
-    static __device__ __forceinline__ void run(float2* v, const float2* sA, const float2* sB, int n) { dft_generic<7, INV>(v, sA, sB, n); }
+    static __device__ __forceinline__ void run(float2* v)
+    {
+        float2 y[7];
+#pragma unroll
+        for (int k = 0; k < 7; k++)
+            {
+                float2 acc = v[0];
+#pragma unroll
+                for (int j = 1; j < 7; j++)
+                    {
+                        const float2 w = fft_wconst<7>((j * k) % 7);
+                        acc = cadd(acc, INV ? cmulc(v[j], w) : cmul(v[j], w));
+                    }
+                y[k] = acc;
+            }
+#pragma unroll
+        for (int k = 0; k < 7; k++) v[k] = y[k];
+    }
 };
 
-// One in-place stage over a shared-memory block x[0..m_blk): sub-blocks of n_s points, radix R.
+// Hooks of a stage.  Pre: multiplier applied to the points as they are read (only on the first inverse stage, whose butterflies
+// own R contiguous points: point q of butterfly id).  Post: consumer that replaces the store (only on the last inverse stage,
+// whose outputs are in natural order: y[n]).
+struct FftNoPre
+{
+    static constexpr bool on = false;
+    __device__ __forceinline__ float2 operator()(int, int) const { return make_float2(1.0f, 0.0f); }
+};
+struct FftNoPost
+{
+    static constexpr bool on = false;
+    __device__ __forceinline__ void operator()(float2, int) {}
+};
+
+// One in-place stage over a shared-memory block x[0..m_blk): sub-blocks of n_s points, radix R; T = the stage's table.
 // Forward (DIF): butterfly, then twiddle W_{n_s}^{j2*k}.  Inverse (DIT): conj twiddle, then inverse butterfly.
-template <int R, bool INV>
-__device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, unsigned inv_ms, int n, const float2* sA, const float2* sB)
+template <int R, bool INV, class Pre, class Post>
+__device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, unsigned inv_ms, const float2* T, const Pre& pre, Post& post)
 {
     const int ms = n_s / R;
     const int nb = m_blk / R;
-    const int tw_mul = n / n_s;
+#pragma unroll(Pre::on ? 2 : 1)
     for (int id = threadIdx.x; id < nb; id += blockDim.x)
         {
             const int blk = ms == 1 ? id : (int)__umulhi((unsigned)id, inv_ms);  // id / ms (exact for id * ms < 2^32)
@@ -153,10 +235,10 @@ __device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, un
             float2* p = x + blk * n_s + j2;
             float2 v[R];
 #pragma unroll
-            for (int k = 0; k < R; k++) v[k] = p[k * ms];
+            for (int k = 0; k < R; k++) v[k] = Pre::on ? cmul(p[k * ms], pre(k, id)) : p[k * ms];
             if (INV && ms > 1)
                 {
-                    const float2 w1 = fft_twiddle(sA, sB, j2 * tw_mul);
+                    const float2 w1 = fft_stage_twiddle(T, j2);
                     float2 w = w1;
 #pragma unroll
                     for (int k = 1; k < R; k++)
@@ -165,13 +247,10 @@ __device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, un
                             if (k + 1 < R) w = cmul(w, w1);
                         }
                 }
-            if constexpr (R == 7)
-                Dft<7, INV>::run(v, sA, sB, n);
-            else
-                Dft<R, INV>::run(v);
+            Dft<R, INV>::run(v);
             if (!INV && ms > 1)
                 {
-                    const float2 w1 = fft_twiddle(sA, sB, j2 * tw_mul);
+                    const float2 w1 = fft_stage_twiddle(T, j2);
                     float2 w = w1;
 #pragma unroll
                     for (int k = 1; k < R; k++)
@@ -181,21 +260,28 @@ __device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, un
                         }
                 }
 #pragma unroll
-            for (int k = 0; k < R; k++) p[k * ms] = v[k];
+            for (int k = 0; k < R; k++)
+                {
+                    if (Post::on)
+                        post(v[k], blk * n_s + j2 + k * ms);
+                    else
+                        p[k * ms] = v[k];
+                }
         }
-    __syncthreads();
+    if (!Post::on) __syncthreads();
 }
 
-// Two consecutive in-place stages (radix R1 on sub-blocks of n_s points, then radix R2 on their n_s / R1 point halves)
+// Two consecutive in-place stages (radix R1 on sub-blocks of n_s points, then radix R2 on their n_s / R1 point parts)
 // fused in registers: one pass over shared memory and one barrier instead of two.  The data layout before and after is
 // exactly that of the two separate stages, so plans may mix fused and plain stages freely.  A thread owns the R1 * R2
-// points  base + k * ms1 + k2 * ms2  (k < R1, k2 < R2).
-template <int R1, int R2, bool INV>
-__device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, int n, const float2* sA, const float2* sB)
+// points  base + k * ms1 + k2 * ms2  (k < R1, k2 < R2).  First-stage twiddles of column k2 are
+// W_{n_s}^{(k2*ms2 + j) k} = (W_{n_s}^j * W_{R1 R2}^{k2})^k : one table look-up and R2 - 1 literal rotations per butterfly.
+template <int R1, int R2, bool INV, class Pre, class Post>
+__device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, const float2* T, int nh, const Pre& pre, Post& post)
 {
     const int ms1 = n_s / R1, ms2 = ms1 / R2;
     const int nb = m_blk / (R1 * R2);
-    const int tw1 = n / n_s, tw2 = n / ms1;
+    const float2* T2 = T + FFT_TW_STAGE_LO + nh;
     for (int id = threadIdx.x; id < nb; id += blockDim.x)
         {
             const int blk = id / ms2;
@@ -205,12 +291,14 @@ __device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, i
 #pragma unroll
             for (int k = 0; k < R1; k++)
 #pragma unroll
-                for (int k2 = 0; k2 < R2; k2++) v[k][k2] = p[k * ms1 + k2 * ms2];
+                for (int k2 = 0; k2 < R2; k2++) v[k][k2] = Pre::on ? cmul(p[k * ms1 + k2 * ms2], pre(k * R2 + k2, id)) : p[k * ms1 + k2 * ms2];
             // second-stage twiddles W_{ms1}^{j * k2} (shared by all k)
             float2 wb[R2];
+            float2 w10 = make_float2(1.0f, 0.0f);
             if (ms2 > 1)
                 {
-                    wb[1] = fft_twiddle(sA, sB, j * tw2);
+                    w10 = fft_stage_twiddle(T, j);
+                    wb[1] = fft_stage_twiddle(T2, j);
 #pragma unroll
                     for (int k2 = 2; k2 < R2; k2++) wb[k2] = cmul(wb[k2 - 1], wb[1]);
                 }
@@ -230,12 +318,12 @@ __device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, i
 #pragma unroll
             for (int k2 = 0; k2 < R2; k2++)
                 {
-                    // first-stage twiddles W_{n_s}^{(k2 * ms2 + j) * k}
-                    const float2 w1 = fft_twiddle(sA, sB, (k2 * ms2 + j) * tw1);
+                    const float2 wc = fft_wconst<R1 * R2>(k2);
+                    const float2 w1 = k2 == 0 ? w10 : (ms2 > 1 ? cmul(w10, wc) : wc);
                     float2 t[R1];
 #pragma unroll
                     for (int k = 0; k < R1; k++) t[k] = v[k][k2];
-                    if (INV)
+                    if (INV && (ms2 > 1 || k2 > 0))
                         {
                             float2 w = w1;
 #pragma unroll
@@ -246,7 +334,7 @@ __device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, i
                                 }
                         }
                     Dft<R1, INV>::run(t);
-                    if (!INV)
+                    if (!INV && (ms2 > 1 || k2 > 0))
                         {
                             float2 w = w1;
 #pragma unroll
@@ -275,54 +363,74 @@ __device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, i
 #pragma unroll
             for (int k = 0; k < R1; k++)
 #pragma unroll
-                for (int k2 = 0; k2 < R2; k2++) p[k * ms1 + k2 * ms2] = v[k][k2];
+                for (int k2 = 0; k2 < R2; k2++)
+                    {
+                        if (Post::on)
+                            post(v[k][k2], blk * n_s + j + k * ms1 + k2 * ms2);
+                        else
+                            p[k * ms1 + k2 * ms2] = v[k][k2];
+                    }
         }
-    __syncthreads();
+    if (!Post::on) __syncthreads();
 }
 
-template <bool INV>
-__device__ __forceinline__ void fft_smem_stage_any(int R, float2* x, int m_blk, int n_s, unsigned inv_ms, int n, const float2* sA, const float2* sB)
+template <bool INV, class Pre, class Post>
+__device__ __forceinline__ void fft_smem_stage_any(int R, float2* x, int m_blk, int n_s, unsigned inv_ms, const float2* T, int nh, const Pre& pre, Post& post)
 {
     switch (R)
         {
-        case 2: fft_smem_stage<2, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
-        case 3: fft_smem_stage<3, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
-        case 4: fft_smem_stage<4, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
-        case 5: fft_smem_stage<5, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
-        case 8: fft_smem_stage2<4, 2, INV>(x, m_blk, n_s, n, sA, sB); break;    // fused pairs: same layout as the two plain stages
-        case 9: fft_smem_stage2<3, 3, INV>(x, m_blk, n_s, n, sA, sB); break;
-        case 16: fft_smem_stage2<4, 4, INV>(x, m_blk, n_s, n, sA, sB); break;
-        case 25: fft_smem_stage2<5, 5, INV>(x, m_blk, n_s, n, sA, sB); break;
-        default: fft_smem_stage<7, INV>(x, m_blk, n_s, inv_ms, n, sA, sB); break;
+        case 2: fft_smem_stage<2, INV>(x, m_blk, n_s, inv_ms, T, pre, post); break;
+        case 3: fft_smem_stage<3, INV>(x, m_blk, n_s, inv_ms, T, pre, post); break;
+        case 4: fft_smem_stage<4, INV>(x, m_blk, n_s, inv_ms, T, pre, post); break;
+        case 5: fft_smem_stage<5, INV>(x, m_blk, n_s, inv_ms, T, pre, post); break;
+        case 8: fft_smem_stage2<4, 2, INV>(x, m_blk, n_s, T, nh, pre, post); break;    // fused pairs: same layout as the two plain stages
+        case 9: fft_smem_stage2<3, 3, INV>(x, m_blk, n_s, T, nh, pre, post); break;
+        case 16: fft_smem_stage2<4, 4, INV>(x, m_blk, n_s, T, nh, pre, post); break;
+        case 25: fft_smem_stage2<5, 5, INV>(x, m_blk, n_s, T, nh, pre, post); break;
+        default: fft_smem_stage<7, INV>(x, m_blk, n_s, inv_ms, T, pre, post); break;
         }
 }
 
 // all shared-memory stages of one block of plan.m points, forward: natural -> digit-reversed
-__device__ __forceinline__ void fft_smem_forward(const FftPlan& pl, float2* x, const float2* sA, const float2* sB)
+__device__ __forceinline__ void fft_smem_forward(const FftPlan& pl, float2* x, const float2* sT)
 {
     int n_s = pl.m;
+    FftNoPre pre;
+    FftNoPost post;
     for (int s = 0; s < pl.n_stages; s++)
         {
-            fft_smem_stage_any<false>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], pl.n, sA, sB);
+            fft_smem_stage_any<false>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], sT + pl.tw_off[s], pl.tw_nh[s], pre, post);
             n_s /= pl.radix[s];
         }
 }
 
-// inverse: digit-reversed -> natural (stages in reverse order)
-__device__ __forceinline__ void fft_smem_inverse(const FftPlan& pl, float2* x, const float2* sA, const float2* sB)
+// inverse: digit-reversed -> natural (stages in reverse order).  `pre` multiplies the input inside the first stage and
+// `post` consumes the natural-order output of the last one; with a single stage both hooks cannot be fused at once, so
+// the caller checks fft_can_fuse() first.
+__device__ __forceinline__ bool fft_can_fuse(const FftPlan& pl) { return pl.n_stages >= 2; }
+
+template <class Pre, class Post>
+__device__ __forceinline__ void fft_smem_inverse(const FftPlan& pl, float2* x, const float2* sT, const Pre& pre, Post& post)
 {
+    FftNoPre no_pre;
+    FftNoPost no_post;
     int n_s = 1;
     for (int s = pl.n_stages - 1; s >= 0; s--)
         {
             n_s *= pl.radix[s];
-            fft_smem_stage_any<true>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], pl.n, sA, sB);
+            const float2* T = sT + pl.tw_off[s];
+            if (Pre::on && s == pl.n_stages - 1)
+                fft_smem_stage_any<true>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], T, pl.tw_nh[s], pre, no_post);
+            else if (Post::on && s == 0)
+                fft_smem_stage_any<true>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], T, pl.tw_nh[s], no_pre, post);
+            else
+                fft_smem_stage_any<true>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], T, pl.tw_nh[s], no_pre, no_post);
         }
 }
 
-// twiddle tables global -> shared (all threads), followed by a barrier in the caller
-__device__ __forceinline__ void fft_load_tables(const FftPlan& pl, const float2* gA, const float2* gB, float2* sA, float2* sB)
+// stage tables global -> shared (all threads), followed by a barrier in the caller
+__device__ __forceinline__ void fft_load_tables(const FftPlan& pl, const float2* gT, float2* sT)
 {
-    for (int i = threadIdx.x; i < pl.n_hi; i += blockDim.x) sA[i] = gA[i];
-    for (int i = threadIdx.x; i < FFT_TW_LO; i += blockDim.x) sB[i] = gB[i];
+    for (int i = threadIdx.x; i < pl.n_tw; i += blockDim.x) sT[i] = gT[i];
 }
 }  // namespace gb200

@@ -98,16 +98,17 @@ __global__ void acq_phase_table_kernel(const float* __restrict__ inc, int n_bins
 // Forward transform of one shared-memory block.  grid = (g_radix, batch).
 //   SRC_IQ = true : block 0 only (g_radix == 1): input = raw IQ x wipe-off of bin blockIdx.y
 //   SRC_IQ = false: input = cf32 buffer src[batch][N] (output of the global stage, or a zero-padded code replica)
-// Output dst[batch][N] in digit-reversed order, optionally conjugated (code spectra, pcps_acquisition.cc:207).
+// Output dst[batch][N] in digit-reversed order.  code_out: conjugate (code spectra, pcps_acquisition.cc:207) and store each
+// block as [q][butterfly] of the first inverse stage (position id * RL + q -> q * (m / RL) + id), the order in which
+// acq_inv_kernel's first stage reads it with coalesced loads.
 template <int IQ, bool SRC_IQ>
 __global__ void __launch_bounds__(512) acq_fwd_kernel(FftPlan pl, const void* __restrict__ src, int consumed, const unsigned long long* __restrict__ dphi, const float* __restrict__ phase_tab,
-    const float2* __restrict__ gA, const float2* __restrict__ gB, float2* __restrict__ dst, int conj_out)
+    const float2* __restrict__ gT, float2* __restrict__ dst, int code_out)
 {
     extern __shared__ __align__(16) float2 sm[];
     float2* x = sm;
-    float2* sA = sm + pl.m;
-    float2* sB = sA + pl.n_hi;
-    fft_load_tables(pl, gA, gB, sA, sB);
+    float2* sT = sm + pl.m;
+    fft_load_tables(pl, gT, sT);
     const size_t base = (size_t)blockIdx.y * pl.n + (size_t)blockIdx.x * pl.m;
     if (SRC_IQ)
         {
@@ -121,14 +122,20 @@ __global__ void __launch_bounds__(512) acq_fwd_kernel(FftPlan pl, const void* __
             for (int i = threadIdx.x; i < pl.m; i += blockDim.x) x[i] = s[i];
         }
     __syncthreads();
-    fft_smem_forward(pl, x, sA, sB);
+    fft_smem_forward(pl, x, sT);
     float2* d = dst + base;
-    for (int i = threadIdx.x; i < pl.m; i += blockDim.x)
+    if (code_out)
         {
-            float2 v = x[i];
-            if (conj_out) v.y = -v.y;
-            d[i] = v;
+            const int rl = pl.perm_rl, nb = pl.m / rl;
+            for (int i = threadIdx.x; i < pl.m; i += blockDim.x)
+                {
+                    const int id = i / rl, q = i - id * rl;
+                    const float2 v = x[i];
+                    d[q * nb + id] = make_float2(v.x, -v.y);
+                }
+            return;
         }
+    for (int i = threadIdx.x; i < pl.m; i += blockDim.x) d[i] = x[i];
 }
 
 // First DIF stage through global memory (transforms longer than one SM's shared memory): radix R = plan.g_radix over
@@ -205,24 +212,44 @@ __device__ __forceinline__ void acq_block_reduce(float& v, int& idx, float& sum)
         }
 }
 
-// |y|^2 of output sample n, dwell accumulation into the kept grid (pcps_acquisition.cc:657-665), running max / sum
-__device__ __forceinline__ void acq_consume(const AcqParams& p, float2 y, int n, float* __restrict__ grid_row, float& best, int& besti, float& sum)
+// The multiplication by the conjugated code spectrum (volk_32fc_x2_multiply_32fc, pcps_acquisition.cc:650) as the input
+// hook of the first inverse stage: point q of butterfly id, spectra stored [q][butterfly] (see acq_fwd_kernel)
+struct AcqCodeProduct
 {
-    const int i = n - p.out_offset;
-    if (i < 0 || i >= p.neff) return;
-    float g = y.x * y.x + y.y * y.y;
-    if (grid_row)
-        {
-            if (p.dwell_index > 0) g = grid_row[i] + g;
-            grid_row[i] = g;
-        }
-    sum += g;
-    if (g > best)
-        {
-            best = g;
-            besti = i;
-        }
-}
+    static constexpr bool on = true;
+    const float2* c;
+    int nb;
+    __device__ __forceinline__ float2 operator()(int q, int id) const { return __ldg(c + q * nb + id); }
+};
+
+// |y|^2 of output sample n, dwell accumulation into the kept grid (pcps_acquisition.cc:657-665), running max / first index of
+// the max / sum, as the output hook of the last inverse stage.  Samples arrive in no particular order: ties go to the lower
+// index explicitly (volk_gnsssdr_32f_index_max_32u keeps the first maximum).
+struct AcqSink
+{
+    static constexpr bool on = true;
+    int out_offset, neff, accumulate;
+    float* grid_row;
+    float best, sum;
+    int besti;
+    __device__ __forceinline__ void operator()(float2 y, int n)
+    {
+        const int i = n - out_offset;
+        if (i < 0 || i >= neff) return;
+        float g = y.x * y.x + y.y * y.y;
+        if (grid_row)
+            {
+                if (accumulate) g = grid_row[i] + g;
+                grid_row[i] = g;
+            }
+        sum += g;
+        if (g > best || (g == best && i < besti))
+            {
+                best = g;
+                besti = i;
+            }
+    }
+};
 }  // namespace gb200
 
 #include "acq_kernel2.cuh"

@@ -3,91 +3,86 @@
 
 namespace gb200
 {
-// grid = (g_radix, n_bins, n_slots).  x = X[bin] .* C[slot] on block blockIdx.x, inverse shared-memory stages, then
-//   MODE 0: (g_radix == 1) |.|^2, grid accumulation, max / argmax / sum  -> cells[(slot_i * n_bins + bin)]
+// grid = (g_radix, n_bins, n_slots).  One CTA transforms block blockIdx.x of  X[bin] .* C[slot]  back to code phase:
+//   X[bin] is staged in shared memory by one TMA bulk copy (no register staging) while the threads load the stage tables;
+//   the product with the code spectrum happens inside the first inverse stage (coalesced loads of the permuted spectrum);
+//   MODE 0: (g_radix == 1) the last inverse stage feeds |.|^2, grid accumulation, max / argmax / sum straight from
+//           registers                                                      -> cells[(slot_i * n_bins + bin)]
 //   MODE 1: (g_radix  > 1) store the block to scratch[(slot_i * n_bins + bin)][N] for the global inverse stage
 //   MODE 2: test hook — no code product, store the natural-order complex output to scratch
 template <int MODE>
 __global__ void __launch_bounds__(512) acq_inv_kernel(AcqParams p, const float2* __restrict__ X, const float2* __restrict__ Cs, const int* __restrict__ slots,
-    const float2* __restrict__ gA, const float2* __restrict__ gB, float2* __restrict__ scratch, float* __restrict__ grid, AcqCell* __restrict__ cells)
+    const float2* __restrict__ gT, float2* __restrict__ scratch, float* __restrict__ grid, AcqCell* __restrict__ cells)
 {
     extern __shared__ __align__(16) float2 sm[];
     const FftPlan& pl = p.plan;
     float2* x = sm;
-    float2* sA = sm + pl.m;
-    float2* sB = sA + pl.n_hi;
+    float2* sT = sm + pl.m;
     const int bin = blockIdx.y, si = blockIdx.z;
     const size_t blk_off = (size_t)blockIdx.x * pl.m;
     const float2* xs = X + (size_t)bin * pl.n + blk_off;
-    // Stage X[bin] with one TMA bulk copy (no register staging, the copy engine keeps the L2 pipe full) while the threads
-    // load the twiddle tables; then multiply in place by the code spectrum, read with 128-bit loads four deep.
     __shared__ __align__(8) uint64_t s_bar;
     const bool bulk = (pl.m & 1) == 0 && ((size_t)pl.n & 1) == 0;  // 16-byte alignment of every block start and length
-    if (bulk && threadIdx.x == 0)
-        {
-            mbar_init(&s_bar, 1);
-            fence_barrier_init();
-            mbar_expect_tx(&s_bar, (uint32_t)pl.m * 8u);
-            bulk_g2s(x, xs, (uint32_t)pl.m * 8u, &s_bar);
-        }
-    fft_load_tables(pl, gA, gB, sA, sB);
     if (bulk)
         {
-            __syncthreads();  // the barrier word is initialised before anyone polls it
-            mbar_wait(&s_bar, 0);
-            if (MODE != 2)
+            if (threadIdx.x == 0)
                 {
-                    const float4* cs4 = reinterpret_cast<const float4*>(Cs + (size_t)slots[si] * pl.n + blk_off);
-                    float4* x4 = reinterpret_cast<float4*>(x);
-                    const int n4 = pl.m >> 1, step = blockDim.x;
-                    for (int i0 = threadIdx.x; i0 < n4; i0 += 4 * step)
-                        {
-                            float4 c[4];
-#pragma unroll
-                            for (int u = 0; u < 4; u++)
-                                if (i0 + u * step < n4) c[u] = __ldg(cs4 + i0 + u * step);
-#pragma unroll
-                            for (int u = 0; u < 4; u++)
-                                if (i0 + u * step < n4)
-                                    {
-                                        const float4 a = x4[i0 + u * step];  // volk_32fc_x2_multiply_32fc, :650
-                                        x4[i0 + u * step] = make_float4(a.x * c[u].x - a.y * c[u].y, a.x * c[u].y + a.y * c[u].x, a.z * c[u].z - a.w * c[u].w, a.z * c[u].w + a.w * c[u].z);
-                                    }
-                        }
+                    mbar_init(&s_bar, 1);
+                    fence_barrier_init();
+                    mbar_expect_tx(&s_bar, (uint32_t)pl.m * 8u);
+                    bulk_g2s(x, xs, (uint32_t)pl.m * 8u, &s_bar);
                 }
-        }
-    else if (MODE == 2)
-        {
-            for (int i = threadIdx.x; i < pl.m; i += blockDim.x) x[i] = xs[i];
         }
     else
         {
-            const float2* cs = Cs + (size_t)slots[si] * pl.n + blk_off;
-            for (int i = threadIdx.x; i < pl.m; i += blockDim.x) x[i] = cmul(xs[i], cs[i]);  // volk_32fc_x2_multiply_32fc, :650
+            for (int i = threadIdx.x; i < pl.m; i += blockDim.x) x[i] = xs[i];
         }
-    __syncthreads();
-    fft_smem_inverse(pl, x, sA, sB);
+    fft_load_tables(pl, gT, sT);
+    __syncthreads();  // tables (and the plain copy) visible; the barrier word is initialised before anyone polls it
+    if (bulk) mbar_wait(&s_bar, 0);
     const size_t cell = (size_t)si * p.n_bins + bin;
-    if (MODE != 0)
+    if (MODE == 2)
         {
-            float2* d = scratch + cell * pl.n + blk_off;
-            for (int i = threadIdx.x; i < pl.m; i += blockDim.x) d[i] = x[i];
-            return;
+            FftNoPre pre;
+            FftNoPost post;
+            fft_smem_inverse(pl, x, sT, pre, post);
         }
-    float* grow = p.keep_grid ? grid + ((size_t)slots[si] * p.n_bins + bin) * p.neff : nullptr;
-    float best = -1.0f, sum = 0.0f;
-    int besti = 0x7fffffff;
-    for (int i = threadIdx.x; i < pl.m; i += blockDim.x) acq_consume(p, x[i], i, grow, best, besti, sum);
-    acq_block_reduce(best, besti, sum);
-    if (threadIdx.x == 0)
+    else
         {
-            AcqCell c;
-            c.vmax = best;
-            c.imax = besti;
-            c.sum = sum;
-            c.pad_ = 0;
-            cells[cell] = c;
+            AcqCodeProduct pre;
+            pre.c = Cs + (size_t)slots[si] * pl.n + blk_off;
+            pre.nb = pl.m / pl.perm_rl;
+            if (MODE == 1)
+                {
+                    FftNoPost post;
+                    fft_smem_inverse(pl, x, sT, pre, post);
+                }
+            else
+                {
+                    AcqSink sink;
+                    sink.out_offset = p.out_offset;
+                    sink.neff = p.neff;
+                    sink.accumulate = p.dwell_index > 0;
+                    sink.grid_row = p.keep_grid ? grid + ((size_t)slots[si] * p.n_bins + bin) * p.neff : nullptr;
+                    sink.best = -1.0f;
+                    sink.sum = 0.0f;
+                    sink.besti = 0x7fffffff;
+                    fft_smem_inverse(pl, x, sT, pre, sink);
+                    acq_block_reduce(sink.best, sink.besti, sink.sum);
+                    if (threadIdx.x == 0)
+                        {
+                            AcqCell c;
+                            c.vmax = sink.best;
+                            c.imax = sink.besti;
+                            c.sum = sink.sum;
+                            c.pad_ = 0;
+                            cells[cell] = c;
+                        }
+                    return;
+                }
         }
+    float2* d = scratch + cell * pl.n + blk_off;
+    for (int i = threadIdx.x; i < pl.m; i += blockDim.x) d[i] = x[i];
 }
 
 // Last DIT stage through global memory: y[j1*m + j2] = sum_k1 conj(W_N^{j2 k1}) z_k1[j2] conj(W_R^{j1 k1}), followed by the
