@@ -24,6 +24,14 @@ struct gb200_acq
     float2 *d_twA{nullptr}, *d_twB{nullptr};  // two-level W_N table for the global stages
     float2* d_twT{nullptr};                   // per-stage tables of the shared-memory stages (FftPlan::tw_off)
     std::vector<float2> tw_stage;
+    // forward transforms of the wiped input may run as (global first factor) + (several small shared-memory blocks per bin):
+    // same digit order as `plan`, but 4-5 times as many CTAs, so all SMs work on the n_bins forward transforms
+    FftPlan plan_f{};
+    bool split_fwd{false};
+    int threads_f{0};
+    size_t smem_f{0};
+    float2* d_twT_f{nullptr};
+    std::vector<float2> tw_stage_f;
     void* d_iq{nullptr};
     float2* d_X{nullptr};        // [n_bins][N] forward spectra of the wiped input
     float2* d_C{nullptr};        // [max_prns][N] conjugated code spectra
@@ -129,6 +137,33 @@ int build_stage_tables(FftPlan& pl, std::vector<float2>* tab)
     return off;
 }
 
+// derived fields of a plan whose n, m, g_radix, n_stages and radix[] are set
+void finish_plan(FftPlan& pl)
+{
+    const bool blk_map = getenv("GB200_ACQ_NO_BLKMAP") == nullptr;
+    int n_s = pl.m;
+    pl.map_blk = 0;
+    for (int s = 0; s < pl.n_stages; s++)
+        {
+            const unsigned ms = (unsigned)(n_s / pl.radix[s]);  // butterfly positions per sub-block (ms2 of a fused stage)
+            const unsigned nblk = (unsigned)(pl.m / n_s);
+            pl.inv_ms[s] = ms == 1 ? 0u : (unsigned)((0x100000000ull + ms - 1) / ms);
+            pl.inv_nblk[s] = nblk <= 1 ? 0u : (unsigned)((0x100000000ull + nblk - 1) / nblk);
+            if (blk_map && ms > 1 && ms < 16 && (n_s & 1) && nblk >= 16) pl.map_blk |= 1u << s;
+            n_s /= pl.radix[s];
+        }
+    pl.perm_rl = pl.radix[pl.n_stages - 1];
+}
+
+// threads per CTA: the largest stage radix decides how many butterflies a pass has
+int plan_threads(const FftPlan& pl)
+{
+    int rmax = 2;
+    for (int s = 0; s < pl.n_stages; s++) rmax = std::max(rmax, pl.radix[s]);
+    const int bf = pl.m / std::min(rmax, 8);  // plain passes have m / R butterflies, fused ones m / (R1 R2)
+    return std::min(512, std::max(128, (bf + 63) / 64 * 64));  // 512: the fused radix-25 pass holds 25 points per thread (128 registers)
+}
+
 int make_plan(gb200_acq* h, int max_smem)
 {
     const int N = h->cfg.fft_size;
@@ -160,17 +195,30 @@ int make_plan(gb200_acq* h, int max_smem)
     if (!g) return set_error(GB200_EINVAL, "fft_size %d: no split into <= 8 shared-memory blocks", N);
     pl.g_radix = g;
     pl.m = N / g;
-    int n_s = pl.m;
-    for (int s = 0; s < pl.n_stages; s++)
-        {
-            const unsigned ms = (unsigned)(n_s / radix[s]);
-            pl.inv_ms[s] = ms == 1 ? 0u : (unsigned)((0x100000000ull + ms - 1) / ms);
-            n_s /= radix[s];
-        }
-    pl.perm_rl = pl.radix[pl.n_stages - 1];
+    finish_plan(pl);
     h->tw_stage.clear();
     build_stage_tables(pl, &h->tw_stage);
-    h->threads = std::min(512, std::max(128, ((pl.m / 8) + 63) / 64 * 64));  // 512: the fused radix-25 pass holds 25 points per thread (128 registers)
+    h->threads = plan_threads(pl);
+    // forward split: peel the first plain factor of the first stage off into the global stage
+    h->split_fwd = false;
+    if (g == 1 && N >= 8192 && getenv("GB200_ACQ_SPLIT_FWD") != nullptr)  // opt-in: measured 3 % slower than one CTA per bin on the C3 sweep
+        {
+            FftPlan& pf = h->plan_f;
+            pf = pl;
+            int f1, f2;
+            stage_factors(pl.radix[0], &f1, &f2);
+            pf.g_radix = f1;
+            pf.m = N / f1;
+            pf.n_stages = 0;
+            if (f2 > 1) pf.radix[pf.n_stages++] = f2;
+            for (int s = 1; s < pl.n_stages; s++) pf.radix[pf.n_stages++] = pl.radix[s];
+            finish_plan(pf);
+            h->tw_stage_f.clear();
+            build_stage_tables(pf, &h->tw_stage_f);
+            h->smem_f = ((size_t)pf.m + pf.n_tw) * sizeof(float2);
+            h->threads_f = std::min(256, plan_threads(pf));  // 128 registers per thread: two CTAs per SM
+            h->split_fwd = true;
+        }
     // natural index -> position after the DIF stages (global stage first)
     h->pos_of_k.resize(N);
     for (int k = 0; k < N; k++)
@@ -213,20 +261,24 @@ cudaError_t opt_in_smem(K kernel, size_t smem)
 template <int IQ>
 cudaError_t forward_iq(gb200_acq* h, int batch, float2* dst)
 {
-    const FftPlan& pl = h->plan;
+    const bool split = h->split_fwd;
+    const FftPlan& pl = split ? h->plan_f : h->plan;
+    const float2* twT = split ? h->d_twT_f : h->d_twT;
+    const int threads = split ? h->threads_f : h->threads;
+    const size_t smem = split ? h->smem_f : h->smem;
     cudaError_t e;
     if (pl.g_radix == 1)
         {
-            if ((e = opt_in_smem(acq_fwd_kernel<IQ, true>, h->smem)) != cudaSuccess) return e;
-            acq_fwd_kernel<IQ, true><<<dim3(1, batch), h->threads, h->smem, h->stream>>>(pl, h->d_iq, h->cfg.consumed_samples, h->d_dphi, h->exact_wipeoff ? nullptr : h->d_phase, h->d_twT, dst, 0);
+            if ((e = opt_in_smem(acq_fwd_kernel<IQ, true>, smem)) != cudaSuccess) return e;
+            acq_fwd_kernel<IQ, true><<<dim3(1, batch), threads, smem, h->stream>>>(pl, h->d_iq, h->cfg.consumed_samples, h->d_dphi, h->exact_wipeoff ? nullptr : h->d_phase, twT, dst, 0);
             count_launch();
             return cudaGetLastError();
         }
     acq_gstage_fwd_kernel<IQ, true><<<dim3((pl.m + 255) / 256, batch), 256, 0, h->stream>>>(pl, h->d_iq, h->cfg.consumed_samples, h->d_dphi, h->exact_wipeoff ? nullptr : h->d_phase, h->d_twA, h->d_twB, h->d_stage);
     count_launch();
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    if ((e = opt_in_smem(acq_fwd_kernel<0, false>, h->smem)) != cudaSuccess) return e;
-    acq_fwd_kernel<0, false><<<dim3(pl.g_radix, batch), h->threads, h->smem, h->stream>>>(pl, h->d_stage, 0, nullptr, nullptr, h->d_twT, dst, 0);
+    if ((e = opt_in_smem(acq_fwd_kernel<0, false>, smem)) != cudaSuccess) return e;
+    acq_fwd_kernel<0, false><<<dim3(pl.g_radix, batch), threads, smem, h->stream>>>(pl, h->d_stage, 0, nullptr, nullptr, twT, dst, 0);
     count_launch();
     return cudaGetLastError();
 }

@@ -33,6 +33,10 @@ struct FftPlan
     // conflicts) and one or two hi entries (broadcast)
     int tw_off[FFT_MAX_STAGES];
     int tw_nh[FFT_MAX_STAGES];
+    // butterfly -> thread mapping: bit s set = consecutive threads take the same position j in consecutive sub-blocks (stride n_s,
+    // odd: conflict-free, twiddles broadcast) instead of consecutive j; used when a sub-block has fewer than 16 positions
+    unsigned map_blk;
+    unsigned inv_nblk[FFT_MAX_STAGES];  // ceil(2^32 / (m / n_s)) for that mapping
     int n_tw;      // entries of the stage-table block
     int perm_rl;   // full radix of the last DIF stage: code spectra are stored [q][butterfly] within a block (see acq_inv_kernel)
 };
@@ -223,15 +227,25 @@ struct FftNoPost
 // One in-place stage over a shared-memory block x[0..m_blk): sub-blocks of n_s points, radix R; T = the stage's table.
 // Forward (DIF): butterfly, then twiddle W_{n_s}^{j2*k}.  Inverse (DIT): conj twiddle, then inverse butterfly.
 template <int R, bool INV, class Pre, class Post>
-__device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, unsigned inv_ms, const float2* T, const Pre& pre, Post& post)
+__device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, unsigned inv_ms, unsigned inv_nblk, const float2* T, const Pre& pre, Post& post)
 {
     const int ms = n_s / R;
     const int nb = m_blk / R;
+    const int nblk = m_blk / n_s;
 #pragma unroll(Pre::on ? 2 : 1)
     for (int id = threadIdx.x; id < nb; id += blockDim.x)
         {
-            const int blk = ms == 1 ? id : (int)__umulhi((unsigned)id, inv_ms);  // id / ms (exact for id * ms < 2^32)
-            const int j2 = id - blk * ms;
+            int blk, j2;
+            if (inv_nblk)
+                {
+                    j2 = (int)__umulhi((unsigned)id, inv_nblk);  // id / nblk
+                    blk = id - j2 * nblk;
+                }
+            else
+                {
+                    blk = ms == 1 ? id : (int)__umulhi((unsigned)id, inv_ms);  // id / ms (exact for id * ms < 2^32)
+                    j2 = id - blk * ms;
+                }
             float2* p = x + blk * n_s + j2;
             float2 v[R];
 #pragma unroll
@@ -277,15 +291,25 @@ __device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, un
 // points  base + k * ms1 + k2 * ms2  (k < R1, k2 < R2).  First-stage twiddles of column k2 are
 // W_{n_s}^{(k2*ms2 + j) k} = (W_{n_s}^j * W_{R1 R2}^{k2})^k : one table look-up and R2 - 1 literal rotations per butterfly.
 template <int R1, int R2, bool INV, class Pre, class Post>
-__device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, const float2* T, int nh, const Pre& pre, Post& post)
+__device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, unsigned inv_ms, unsigned inv_nblk, const float2* T, int nh, const Pre& pre, Post& post)
 {
     const int ms1 = n_s / R1, ms2 = ms1 / R2;
     const int nb = m_blk / (R1 * R2);
+    const int nblk = m_blk / n_s;
     const float2* T2 = T + FFT_TW_STAGE_LO + nh;
     for (int id = threadIdx.x; id < nb; id += blockDim.x)
         {
-            const int blk = id / ms2;
-            const int j = id - blk * ms2;
+            int blk, j;
+            if (inv_nblk)
+                {
+                    j = (int)__umulhi((unsigned)id, inv_nblk);  // id / nblk
+                    blk = id - j * nblk;
+                }
+            else
+                {
+                    blk = ms2 == 1 ? id : (int)__umulhi((unsigned)id, inv_ms);  // id / ms2
+                    j = id - blk * ms2;
+                }
             float2* p = x + blk * n_s + j;
             float2 v[R1][R2];
 #pragma unroll
@@ -293,27 +317,28 @@ __device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, c
 #pragma unroll
                 for (int k2 = 0; k2 < R2; k2++) v[k][k2] = Pre::on ? cmul(p[k * ms1 + k2 * ms2], pre(k * R2 + k2, id)) : p[k * ms1 + k2 * ms2];
             // second-stage twiddles W_{ms1}^{j * k2} (shared by all k)
-            float2 wb[R2];
+            float2 wb1 = make_float2(1.0f, 0.0f);
             float2 w10 = make_float2(1.0f, 0.0f);
             if (ms2 > 1)
                 {
                     w10 = fft_stage_twiddle(T, j);
-                    wb[1] = fft_stage_twiddle(T2, j);
-#pragma unroll
-                    for (int k2 = 2; k2 < R2; k2++) wb[k2] = cmul(wb[k2 - 1], wb[1]);
+                    wb1 = fft_stage_twiddle(T2, j);
                 }
             if (INV)
                 {
-#pragma unroll
-                    for (int k = 0; k < R1; k++)
+                    if (ms2 > 1)
                         {
-                            float2 t[R2];
+                            float2 w = wb1;
 #pragma unroll
-                            for (int k2 = 0; k2 < R2; k2++) t[k2] = (ms2 > 1 && k2 > 0) ? cmulc(v[k][k2], wb[k2]) : v[k][k2];
-                            Dft<R2, true>::run(t);
+                            for (int k2 = 1; k2 < R2; k2++)
+                                {
 #pragma unroll
-                            for (int k2 = 0; k2 < R2; k2++) v[k][k2] = t[k2];
+                                    for (int k = 0; k < R1; k++) v[k][k2] = cmulc(v[k][k2], w);
+                                    if (k2 + 1 < R2) w = cmul(w, wb1);
+                                }
                         }
+#pragma unroll
+                    for (int k = 0; k < R1; k++) Dft<R2, true>::run(v[k]);
                 }
 #pragma unroll
             for (int k2 = 0; k2 < R2; k2++)
@@ -350,14 +375,17 @@ __device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, c
             if (!INV)
                 {
 #pragma unroll
-                    for (int k = 0; k < R1; k++)
+                    for (int k = 0; k < R1; k++) Dft<R2, false>::run(v[k]);
+                    if (ms2 > 1)
                         {
-                            float2 t[R2];
+                            float2 w = wb1;
 #pragma unroll
-                            for (int k2 = 0; k2 < R2; k2++) t[k2] = v[k][k2];
-                            Dft<R2, false>::run(t);
+                            for (int k2 = 1; k2 < R2; k2++)
+                                {
 #pragma unroll
-                            for (int k2 = 0; k2 < R2; k2++) v[k][k2] = (ms2 > 1 && k2 > 0) ? cmul(t[k2], wb[k2]) : t[k2];
+                                    for (int k = 0; k < R1; k++) v[k][k2] = cmul(v[k][k2], w);
+                                    if (k2 + 1 < R2) w = cmul(w, wb1);
+                                }
                         }
                 }
 #pragma unroll
@@ -375,19 +403,22 @@ __device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, c
 }
 
 template <bool INV, class Pre, class Post>
-__device__ __forceinline__ void fft_smem_stage_any(int R, float2* x, int m_blk, int n_s, unsigned inv_ms, const float2* T, int nh, const Pre& pre, Post& post)
+__device__ __forceinline__ void fft_smem_stage_any(const FftPlan& pl, int s, float2* x, int n_s, const float2* sT, const Pre& pre, Post& post)
 {
-    switch (R)
+    const unsigned inv_ms = pl.inv_ms[s], inv_nblk = ((pl.map_blk >> s) & 1u) ? pl.inv_nblk[s] : 0u;
+    const float2* T = sT + pl.tw_off[s];
+    const int nh = pl.tw_nh[s], m_blk = pl.m;
+    switch (pl.radix[s])
         {
-        case 2: fft_smem_stage<2, INV>(x, m_blk, n_s, inv_ms, T, pre, post); break;
-        case 3: fft_smem_stage<3, INV>(x, m_blk, n_s, inv_ms, T, pre, post); break;
-        case 4: fft_smem_stage<4, INV>(x, m_blk, n_s, inv_ms, T, pre, post); break;
-        case 5: fft_smem_stage<5, INV>(x, m_blk, n_s, inv_ms, T, pre, post); break;
-        case 8: fft_smem_stage2<4, 2, INV>(x, m_blk, n_s, T, nh, pre, post); break;    // fused pairs: same layout as the two plain stages
-        case 9: fft_smem_stage2<3, 3, INV>(x, m_blk, n_s, T, nh, pre, post); break;
-        case 16: fft_smem_stage2<4, 4, INV>(x, m_blk, n_s, T, nh, pre, post); break;
-        case 25: fft_smem_stage2<5, 5, INV>(x, m_blk, n_s, T, nh, pre, post); break;
-        default: fft_smem_stage<7, INV>(x, m_blk, n_s, inv_ms, T, pre, post); break;
+        case 2: fft_smem_stage<2, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, pre, post); break;
+        case 3: fft_smem_stage<3, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, pre, post); break;
+        case 4: fft_smem_stage<4, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, pre, post); break;
+        case 5: fft_smem_stage<5, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, pre, post); break;
+        case 8: fft_smem_stage2<4, 2, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;  // fused pairs: same layout as the two plain stages
+        case 9: fft_smem_stage2<3, 3, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
+        case 16: fft_smem_stage2<4, 4, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
+        case 25: fft_smem_stage2<5, 5, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
+        default: fft_smem_stage<7, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, pre, post); break;
         }
 }
 
@@ -399,7 +430,7 @@ __device__ __forceinline__ void fft_smem_forward(const FftPlan& pl, float2* x, c
     FftNoPost post;
     for (int s = 0; s < pl.n_stages; s++)
         {
-            fft_smem_stage_any<false>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], sT + pl.tw_off[s], pl.tw_nh[s], pre, post);
+            fft_smem_stage_any<false>(pl, s, x, n_s, sT, pre, post);
             n_s /= pl.radix[s];
         }
 }
@@ -418,13 +449,12 @@ __device__ __forceinline__ void fft_smem_inverse(const FftPlan& pl, float2* x, c
     for (int s = pl.n_stages - 1; s >= 0; s--)
         {
             n_s *= pl.radix[s];
-            const float2* T = sT + pl.tw_off[s];
             if (Pre::on && s == pl.n_stages - 1)
-                fft_smem_stage_any<true>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], T, pl.tw_nh[s], pre, no_post);
+                fft_smem_stage_any<true>(pl, s, x, n_s, sT, pre, no_post);
             else if (Post::on && s == 0)
-                fft_smem_stage_any<true>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], T, pl.tw_nh[s], no_pre, post);
+                fft_smem_stage_any<true>(pl, s, x, n_s, sT, no_pre, post);
             else
-                fft_smem_stage_any<true>(pl.radix[s], x, pl.m, n_s, pl.inv_ms[s], T, pl.tw_nh[s], no_pre, no_post);
+                fft_smem_stage_any<true>(pl, s, x, n_s, sT, no_pre, no_post);
         }
 }
 

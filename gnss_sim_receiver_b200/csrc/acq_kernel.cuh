@@ -234,20 +234,23 @@ struct AcqSink
     int besti;
     __device__ __forceinline__ void operator()(float2 y, int n)
     {
+        // branch-free: samples outside [out_offset, out_offset + neff) add nothing and can never win
         const int i = n - out_offset;
-        if (i < 0 || i >= neff) return;
+        const bool ok = (unsigned)i < (unsigned)neff;
         float g = y.x * y.x + y.y * y.y;
-        if (grid_row)
+        if (grid_row)  // uniform
             {
-                if (accumulate) g = grid_row[i] + g;
-                grid_row[i] = g;
+                if (ok)
+                    {
+                        if (accumulate) g = grid_row[i] + g;
+                        grid_row[i] = g;
+                    }
             }
-        sum += g;
-        if (g > best || (g == best && i < besti))
-            {
-                best = g;
-                besti = i;
-            }
+        sum += ok ? g : 0.0f;
+        const float gm = ok ? g : -2.0f;
+        const bool better = gm > best || (gm == best && i < besti);
+        best = better ? gm : best;
+        besti = better ? i : besti;
     }
 };
 }  // namespace gb200
