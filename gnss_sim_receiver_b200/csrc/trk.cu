@@ -1,5 +1,6 @@
 // Tracking multicorrelator engine: C ABI (include/gnss_b200.h) over trk_kernel.cuh.
 #include "trk_kernel2.cuh"
+#include "trk_kernel3.cuh"
 #include "host_pool.h"
 #include <chrono>
 #include <mutex>
@@ -37,7 +38,7 @@ struct gb200_trk
     TrkGroup* h_groups{nullptr};  // pinned
     TrkGroup* d_groups{nullptr};
     std::vector<std::pair<long long, int>> order;  // scratch of plan_run_kernel
-    int last_path{0}, last_groups{0}, last_R{16}, last_G{4};  // path 0: chunked kernel, 1: run-based kernel
+    int last_path{0}, last_groups{0}, last_R{16}, last_G{4};  // path 0: chunked kernel, 1: run-based kernel, 2: high-dynamics kernel
     // last enqueued launch (for collect / replay)
     int last_n{0}, last_T{0}, last_chunks{0}, last_cplx{0};
     size_t last_smem{0};
@@ -158,6 +159,17 @@ cudaError_t launch_run(gb200_trk* h)
 cudaError_t launch(gb200_trk* h)
 {
     if (h->last_path == 1) return launch_run(h);
+    if (h->last_path == 2)
+        {
+            switch (h->cfg.iq_dtype)
+                {
+                case GB200_IQ_CF32: trk_high_dyn_kernel<GB200_IQ_CF32><<<h->last_n, TRK3_THREADS, 0, h->stream>>>(h->d_cmds, h->d_out); break;
+                case GB200_IQ_CS16: trk_high_dyn_kernel<GB200_IQ_CS16><<<h->last_n, TRK3_THREADS, 0, h->stream>>>(h->d_cmds, h->d_out); break;
+                default: trk_high_dyn_kernel<GB200_IQ_CS8><<<h->last_n, TRK3_THREADS, 0, h->stream>>>(h->d_cmds, h->d_out); break;
+                }
+            count_launch();
+            return cudaGetLastError();
+        }
     const int T = h->last_T, n = h->last_n, ch = h->last_chunks;
     const size_t sm = h->last_smem;
     if (h->last_cplx)

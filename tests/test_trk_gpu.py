@@ -202,3 +202,40 @@ def test_run_based_kernel_many_channels(fs, L, chip_rate, nt, spacing, iq_dtype,
     again = eng.collect()[:, :nt]
     assert np.array_equal(again.view(np.uint32), got.view(np.uint32))
     eng.close()
+
+
+@pytest.mark.parametrize("n,fs,nt,spacing,phase_rate,code_rate", [
+    (4000, 4e6, 3, 0.5, 1e-7, 1e-9), (16000, 16e6, 5, 0.25, -3e-8, 2e-10), (25000, 25e6, 11, 0.1, 5e-9, -1e-11), (4000, 4e6, 1, 0.5, 2e-7, 0.0),
+])
+def test_high_dynamics_variant(n, fs, nt, spacing, phase_rate, code_rate):
+    """a4: Tracking_XX.high_dyn=true — quadratic code phase on tap 0, the other taps as whole-sample rotations of it, carrier
+    with a phase-rate term (volk_gnsssdr_32f_xn_high_dynamics_resampler_32f_xn + ..._high_dynamic_rotator_dot_prod_32fc_xn).
+    A plain command shares the call: the kernel serves both laws."""
+    from gnss_sim_receiver_b200 import _capi
+    rng = np.random.default_rng(n + nt)
+    L = 1023
+    sig = (rng.uniform(-0.5, 0.5, n) + 1j * rng.uniform(-0.5, 0.5, n)).astype(np.complex64)
+    code = rng.choice([-1.0, 1.0], L).astype(np.float32)
+    shifts = _taps(nt, spacing)
+    code_step = 1.023e6 / fs
+    eng = _engine(max_channels=2, max_code_len=L, ring_samples=4 * 32768, max_block=32768)
+    eng.set_code(0, code)
+    eng.push_iq(np.zeros(11, np.complex64))
+    first = eng.push_iq(sig)
+    for rem_carr, phase_step, rem_code in [(0.25, 0.1, 0.4), (-1.3, -0.02137, 0.7)]:
+        cmds = eng.make_cmds([0, 0], [first, first], [n, n], np.stack([shifts, shifts]), [rem_carr] * 2, [phase_step] * 2, [rem_code] * 2, [code_step] * 2,
+                             phase_rate=[phase_rate, 0.0], code_rate=[code_rate, 0.0], flags=[_capi.TRK_HIGH_DYN, 0])
+        got = eng.correlate(cmds)
+        assert eng.last_kernel == "trk_high_dyn_kernel"
+        ref_hd = O.mc_real_codes(sig, code, shifts, rem_carr, phase_step, rem_code, code_step, high_dyn=True, phase_rate=phase_rate, code_rate=code_rate)
+        ref_plain = O.mc_real_codes(sig, code, shifts, rem_carr, phase_step, rem_code, code_step)
+        assert rel_err(got[0], ref_hd) < TOL, (got[0], ref_hd)
+        assert rel_err(got[1], ref_plain) < TOL
+        if O.ref_available():  # the reference's own generic protokernels
+            ref_ref = O.mc_real_codes(sig, code, shifts, rem_carr, phase_step, rem_code, code_step, high_dyn=True, phase_rate=phase_rate, code_rate=code_rate, impl="ref")
+            assert rel_err(got[0], ref_ref) < TOL
+    # the rotation law is only defined for ascending taps inside the window
+    with pytest.raises(_capi.GB200Error):
+        eng.correlate(eng.make_cmds([0], [first], [n], shifts[None, ::-1] if nt > 1 else np.array([[0.0, -1.0]], np.float32), [0.0], [0.0], [0.0], [code_step],
+                                    phase_rate=[0.0], code_rate=[0.0], flags=[_capi.TRK_HIGH_DYN]))
+    eng.close()
