@@ -52,6 +52,7 @@ SYMBOLS = {
     "gb200_trk_push_iq": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_uint64)]),
     "gb200_trk_push_iq_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_uint64)]),
     "gb200_trk_skip": (C.c_int, [_vp, C.c_int64]),
+    "gb200_trk_write_iq": (C.c_int, [_vp, C.c_uint64, _vp, C.c_int64]),
     "gb200_trk_head": (C.c_uint64, [_vp]),
     "gb200_trk_correlate": (C.c_int, [_vp, _vp, C.c_int, _vp]),
     "gb200_trk_enqueue": (C.c_int, [_vp, _vp, C.c_int]),

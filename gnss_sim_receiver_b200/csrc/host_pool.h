@@ -3,6 +3,7 @@
 #pragma once
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cstdlib>
 #include <functional>
@@ -39,6 +40,7 @@ public:
             slices_ = slices;
             pending_.store(slices - 1, std::memory_order_relaxed);
             generation_++;
+            gen_hint_.store(generation_, std::memory_order_release);
         }
         cv_.notify_all();
         run_slice(slices - 1);  // the caller takes the last slice
@@ -55,6 +57,7 @@ private:
         int want = (int)std::thread::hardware_concurrency() / 2 - 1;
         if (const char* e = std::getenv("GB200_HOST_THREADS")) want = std::atoi(e) - 1;
         want = std::max(0, std::min(want, 7));
+        if (const char* e = std::getenv("GB200_HOST_SPIN_US")) spin_us_ = std::max(0, std::atoi(e));
         for (int i = 0; i < want; i++) threads_.emplace_back([this, i] { loop(i); });
     }
     ~HostPool()
@@ -77,6 +80,12 @@ private:
         unsigned long seen = 0;
         for (;;)
             {
+                // calls come in bursts (preprocess, then plan, every code period): poll for a short while before sleeping, a
+                // condition-variable wake-up costs 50-100 us per worker
+                const auto t0 = std::chrono::steady_clock::now();
+                while (gen_hint_.load(std::memory_order_acquire) == seen && std::chrono::steady_clock::now() - t0 < std::chrono::microseconds(spin_us_))
+                    {
+                    }
                 std::unique_lock<std::mutex> lk(mu_);
                 cv_.wait(lk, [&] { return stop_ || generation_ != seen; });
                 if (stop_) return;
@@ -97,6 +106,8 @@ private:
     int n_{0}, slices_{1};
     std::atomic<int> pending_{0};
     unsigned long generation_{0};
+    std::atomic<unsigned long> gen_hint_{0};
+    int spin_us_{200};
     bool stop_{false};
 };
 }  // namespace gb200

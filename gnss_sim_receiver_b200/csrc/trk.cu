@@ -38,6 +38,8 @@ struct gb200_trk
     TrkGroup* h_groups{nullptr};  // pinned
     TrkGroup* d_groups{nullptr};
     std::vector<std::pair<long long, int>> order;  // scratch of plan_run_kernel
+    bool scan_ok{false};                            // all commands of the call pass run_applicable (set with the preprocessing)
+    float scan_min_step{0}, scan_max_step{0};
     int last_path{0}, last_groups{0}, last_R{16}, last_G{4};  // path 0: chunked kernel, 1: run-based kernel, 2: high-dynamics kernel
     // last enqueued launch (for collect / replay)
     int last_n{0}, last_T{0}, last_chunks{0}, last_cplx{0};
@@ -275,18 +277,15 @@ static int set_code_impl(gb200_trk* h, int ch, const void* code, int code_len, b
 int gb200_trk_set_code(gb200_trk* h, int ch, const float* code, int code_len) { return set_code_impl(h, ch, code, code_len, false); }
 int gb200_trk_set_code_complex(gb200_trk* h, int ch, const gb200_cf32* code, int code_len) { return set_code_impl(h, ch, code, code_len, true); }
 
-static int push_impl(gb200_trk* h, const void* src, int64_t n, uint64_t* first_index, cudaMemcpyKind kind)
+// copy n samples to the ring positions of absolute indices [abs_start, abs_start + n), with the mirror of [0, max_block)
+static int write_at(gb200_trk* h, uint64_t abs_start, const void* src, int64_t n, cudaMemcpyKind kind)
 {
-    if (!h || (!src && n > 0)) return set_error(GB200_EINVAL, "null argument");
-    if (n < 0 || n > h->cfg.ring_samples) return set_error(GB200_EINVAL, "push of %lld samples exceeds the ring (%lld)", (long long)n, (long long)h->cfg.ring_samples);
-    GB_CUDA(cudaSetDevice(h->cfg.device));
     const int64_t cap = h->cfg.ring_samples, mb = h->cfg.max_block;
     const int eb = h->elem_bytes;
-    if (first_index) *first_index = h->head;
     int64_t done = 0;
     while (done < n)
         {
-            const int64_t pos = (int64_t)((h->head + (uint64_t)done) % (uint64_t)cap);
+            const int64_t pos = (int64_t)((abs_start + (uint64_t)done) % (uint64_t)cap);
             const int64_t run = std::min<int64_t>(n - done, cap - pos);
             const char* s = static_cast<const char*>(src) + done * eb;
             GB_CUDA(cudaMemcpyAsync(h->d_ring + pos * eb, s, (size_t)run * eb, kind, h->stream));
@@ -297,6 +296,17 @@ static int push_impl(gb200_trk* h, const void* src, int64_t n, uint64_t* first_i
                 }
             done += run;
         }
+    return GB200_OK;
+}
+
+static int push_impl(gb200_trk* h, const void* src, int64_t n, uint64_t* first_index, cudaMemcpyKind kind)
+{
+    if (!h || (!src && n > 0)) return set_error(GB200_EINVAL, "null argument");
+    if (n < 0 || n > h->cfg.ring_samples) return set_error(GB200_EINVAL, "push of %lld samples exceeds the ring (%lld)", (long long)n, (long long)h->cfg.ring_samples);
+    GB_CUDA(cudaSetDevice(h->cfg.device));
+    if (first_index) *first_index = h->head;
+    const int rc = write_at(h, h->head, src, n, kind);
+    if (rc) return rc;
     h->head += (uint64_t)n;
     return GB200_OK;
 }
@@ -318,6 +328,19 @@ int gb200_trk_skip(gb200_trk* h, int64_t n_samples)
 {
     if (!h || n_samples < 0) return set_error(GB200_EINVAL, "bad argument");
     h->head += (uint64_t)n_samples;
+    return GB200_OK;
+}
+
+int gb200_trk_write_iq(gb200_trk* h, uint64_t abs_index, const void* iq_host, int64_t n_samples)
+{
+    if (!h || (!iq_host && n_samples > 0) || n_samples < 0) return set_error(GB200_EINVAL, "bad argument");
+    const uint64_t cap = (uint64_t)h->cfg.ring_samples;
+    if (abs_index + (uint64_t)n_samples > h->head) return set_error(GB200_ERANGE, "write [%llu,+%lld) beyond the newest sample %llu", (unsigned long long)abs_index, (long long)n_samples, (unsigned long long)h->head);
+    if (h->head > cap && abs_index < h->head - cap) return set_error(GB200_ERANGE, "write start %llu already overwritten (ring holds the last %llu samples)", (unsigned long long)abs_index, (unsigned long long)cap);
+    GB_CUDA(cudaSetDevice(h->cfg.device));
+    const int rc = write_at(h, abs_index, iq_host, n_samples, cudaMemcpyHostToDevice);
+    if (rc) return rc;
+    GB_CUDA(cudaStreamSynchronize(h->stream));
     return GB200_OK;
 }
 

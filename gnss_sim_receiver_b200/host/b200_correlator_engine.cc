@@ -106,16 +106,44 @@ bool B200CorrelatorEngine::ensure(uint64_t abs_index, const void* iq, int64_t n)
     std::lock_guard<std::mutex> lk(mu_);
     const uint64_t head = gb200_trk_head(h_);
     const uint64_t end = abs_index + static_cast<uint64_t>(n);
-    if (end <= head)  // already resident, unless the ring has wrapped past it
-        return head - abs_index <= static_cast<uint64_t>(cfg_.ring_samples);
-    uint64_t from = head;
-    if (abs_index > head)  // nobody asked for [head, abs_index): skip it (see gb200_trk_skip)
+    const size_t eb = elem_bytes(cfg_.iq_dtype);
+    if (end > head)
         {
-            if (gb200_trk_skip(h_, static_cast<int64_t>(abs_index - head)) != GB200_OK) fail("gb200_trk_skip");
-            from = abs_index;
+            uint64_t from = head;
+            if (abs_index > head)  // nobody has asked for [head, abs_index) yet: skip it, remember it (see gb200_trk_skip)
+                {
+                    if (gb200_trk_skip(h_, static_cast<int64_t>(abs_index - head)) != GB200_OK) fail("gb200_trk_skip");
+                    gaps_.emplace_back(head, abs_index);
+                    from = abs_index;
+                }
+            const char* src = static_cast<const char*>(iq) + (from - abs_index) * eb;
+            if (gb200_trk_push_iq(h_, src, static_cast<int64_t>(end - from), nullptr) != GB200_OK) fail("gb200_trk_push_iq");
         }
-    const char* src = static_cast<const char*>(iq) + (from - abs_index) * elem_bytes(cfg_.iq_dtype);
-    if (gb200_trk_push_iq(h_, src, static_cast<int64_t>(end - from), nullptr) != GB200_OK) fail("gb200_trk_push_iq");
+    const uint64_t new_head = gb200_trk_head(h_);
+    const uint64_t oldest = new_head > static_cast<uint64_t>(cfg_.ring_samples) ? new_head - static_cast<uint64_t>(cfg_.ring_samples) : 0;
+    if (abs_index < oldest) return false;  // the ring has wrapped past the start of this stretch
+    // a channel that runs behind the one that skipped may need part of a skipped stretch: back-fill the overlap
+    for (size_t g = 0; g < gaps_.size();)
+        {
+            const uint64_t a = gaps_[g].first, b = gaps_[g].second;
+            if (b <= oldest)
+                {
+                    gaps_.erase(gaps_.begin() + static_cast<std::ptrdiff_t>(g));
+                    continue;
+                }
+            const uint64_t lo = std::max(a, abs_index), hi = std::min(b, end);
+            if (lo < hi)
+                {
+                    const char* src = static_cast<const char*>(iq) + (lo - abs_index) * eb;
+                    if (gb200_trk_write_iq(h_, lo, src, static_cast<int64_t>(hi - lo)) != GB200_OK) fail("gb200_trk_write_iq");
+                    gaps_.erase(gaps_.begin() + static_cast<std::ptrdiff_t>(g));
+                    if (a < lo) gaps_.emplace_back(a, lo);
+                    if (hi < b) gaps_.emplace_back(hi, b);
+                    g = 0;  // the list changed; it holds a handful of entries at most
+                    continue;
+                }
+            g++;
+        }
     return true;
 }
 

@@ -17,6 +17,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 
 namespace gb200h
@@ -71,6 +72,7 @@ private:
     EngineConfig cfg_;
     gb200_trk* h_{nullptr};
     mutable std::mutex mu_;       // engine state (ring, codes, launches)
+    std::vector<std::pair<uint64_t, uint64_t>> gaps_;  // stretches [a, b) behind the head that were skipped, not uploaded
     std::vector<char> used_;
     // batching of per-channel requests: the first request opens a batch and leads it
     struct Batch;

@@ -119,6 +119,9 @@ int gb200_trk_push_iq_device(gb200_trk* h, const void* iq_dev, int64_t n_samples
  * channel needs a stretch of the stream, e.g. all channels idle (state 0 of dll_pll_veml_tracking.cc:1746-1752 just
  * consumes its input). */
 int gb200_trk_skip(gb200_trk* h, int64_t n_samples);
+/* Back-fill a stretch that is already behind the head (e.g. one that gb200_trk_skip jumped over and a slower channel turns
+ * out to need): samples of absolute indices [abs_index, abs_index + n_samples), which must still be inside the ring. */
+int gb200_trk_write_iq(gb200_trk* h, uint64_t abs_index, const void* iq_host, int64_t n_samples);
 /* absolute index one past the newest sample */
 uint64_t gb200_trk_head(const gb200_trk* h);
 

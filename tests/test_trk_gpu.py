@@ -239,3 +239,32 @@ def test_high_dynamics_variant(n, fs, nt, spacing, phase_rate, code_rate):
         eng.correlate(eng.make_cmds([0], [first], [n], shifts[None, ::-1] if nt > 1 else np.array([[0.0, -1.0]], np.float32), [0.0], [0.0], [0.0], [code_step],
                                     phase_rate=[0.0], code_rate=[0.0], flags=[_capi.TRK_HIGH_DYN]))
     eng.close()
+
+
+def test_skip_then_backfill():
+    """gb200_trk_skip jumps over a stretch nobody has asked for; gb200_trk_write_iq back-fills it when a slower channel needs it
+    after all (the per-GPU engine does this for channel threads that run behind the one that skipped)."""
+    from gnss_sim_receiver_b200 import _capi
+    import ctypes as C
+    rng = np.random.default_rng(8)
+    n, L = 4000, 1023
+    eng = _engine(max_channels=1, max_code_len=L, ring_samples=8 * n, max_block=n + 8)
+    code = rng.choice([-1.0, 1.0], L).astype(np.float32)
+    eng.set_code(0, code)
+    x = (rng.standard_normal(4 * n) + 1j * rng.standard_normal(4 * n)).astype(np.complex64)
+    shifts = _taps(3)
+    lib = _capi.lib()
+    eng.push_iq(x[:n])
+    assert lib.gb200_trk_skip(eng._h, n) == 0            # [n, 2n) not uploaded
+    eng.push_iq(x[2 * n:])
+    assert eng.head == 4 * n
+    args = ([0.3], [0.01], [0.1], [0.25575])
+    ref = O.mc_real_codes_f64(x[n + 500:2 * n + 500], code, shifts, 0.3, 0.01, 0.1, 0.25575, mimic_inc=True)
+    stale = eng.correlate(eng.make_cmds([0], [n + 500], [n], shifts[None, :], *args))[0]
+    assert rel_err(stale, ref) > 1e-2                    # the skipped part of the window holds whatever was there
+    seg = np.ascontiguousarray(x[n:2 * n])
+    assert lib.gb200_trk_write_iq(eng._h, n, seg.ctypes.data_as(C.c_void_p), n) == 0
+    got = eng.correlate(eng.make_cmds([0], [n + 500], [n], shifts[None, :], *args))[0]
+    assert rel_err(got, ref) < TOL
+    assert lib.gb200_trk_write_iq(eng._h, 4 * n - 10, seg.ctypes.data_as(C.c_void_p), n) != 0  # beyond the head
+    eng.close()
