@@ -31,6 +31,10 @@ N_TAPS = 11
 CHANNELS_PER_GPU = 10240
 FLOP_PER_CH_SAMPLE = 12 + 4 * N_TAPS  # wipe-off 6 + phasor advance 6 + 2 FMA per tap
 METRIC = "tracked channel-Msps/s (11 taps)"
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernels at this workload, from the ncu --set full
+# captures committed under profiles/ (r01_trk_v3_details / r01_acq_v3_details); a profiler figure, not measured by this script
+TRK_NCU_DRAM_BYTES = 45648128 + 60416   # trk_run_kernel<11,CF32,9,1>, 10240 commands: code tables + IQ ring + commands
+ACQ_NCU_DRAM_BYTES = 23111680 + 18688   # acq_inv_kernel<0>, 2560 cells: X and the code spectra stay in L2
 
 
 def peaks():
@@ -235,8 +239,9 @@ def run_acq(args, rank, world, local, dist, flush):
         "config": {"workload": f"C3 acquisition sweep: GPS L1 C/A {FS / 1e6:g} MS/s gr_complex, fft {n}, {ACQ_PRNS} PRN x {bins} Doppler bins (+-{ACQ_DMAX} Hz / {ACQ_DSTEP} Hz), CFAR, 1 dwell, one sweep per GPU"},
         "e2e": {"value": cells * K / e2e_t, "unit": "cells/s", "h2d_bytes_per_step": n * 8, "d2h_bytes_per_step": ACQ_PRNS * C.sizeof(_capi.AcqResult)},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
-                     "note": f"algorithmic bytes per cell = 16*N = {bytes_per_cell} (SURVEY 8d); peak = {which} HBM copy bandwidth"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": ACQ_NCU_DRAM_BYTES,
+                     "note": f"algorithmic bytes per cell = 16*N = {bytes_per_cell} (SURVEY 8d), x {ACQ_PRNS * bins} cells per launch; peak = {which} HBM copy bandwidth; "
+                             "traffic = dram bytes of one acq_inv_kernel launch from the ncu --set full capture under profiles/ (spectra are L2-resident)"},
         "cpu_baseline": cpu_reference_acq(8.0),
     }
 
@@ -347,7 +352,7 @@ def run_ours(args):
                    "channels_per_gpu": nch, "l2": "256 MiB flush write between timed steps", "parallelism": f"channels sharded x{world}, no collective"},
         "e2e": {"value": e2e_value, "unit": "channel-Msps/s", "h2d_bytes_per_step": N_BLK * 8 + nch * C.sizeof(_capi.TrkCmd), "d2h_bytes_per_step": out_bytes},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak, "traffic": None,
+        "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak, "traffic": TRK_NCU_DRAM_BYTES,
                      "note": f"FP32-FMA pipe roofline (SURVEY 8d): {FLOP_PER_CH_SAMPLE} flop per channel-sample; peak = 148 SM x 128 lanes x 2 x sm_max_mhz ({which}); kernel moves ~0 HBM bytes per unit",
                      "sustained_ms_per_step": sustained_ms},
         "cpu_baseline": cpu, "clocks": clocks, "acq": acq,
@@ -387,7 +392,12 @@ def main():
     if args.impl == "reference":
         run_reference(args)
     else:
-        run_ours(args)
+        try:
+            run_ours(args)
+        finally:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                dist.destroy_process_group()
 
 
 if __name__ == "__main__":
