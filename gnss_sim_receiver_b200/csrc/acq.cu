@@ -161,8 +161,8 @@ int plan_threads(const FftPlan& pl)
     int rmax = 2;
     for (int s = 0; s < pl.n_stages; s++) rmax = std::max(rmax, pl.radix[s]);
     const int bf = pl.m / std::min(rmax, 8);  // plain passes have m / R butterflies, fused ones m / (R1 R2)
-    if (const char* e = getenv("GB200_ACQ_THREADS")) return std::min(512, std::max(64, atoi(e) / 32 * 32));  // tuning knob
-    return std::min(512, std::max(128, (bf + 63) / 64 * 64));  // 512: the fused radix-25 pass holds 25 points per thread (128 registers)
+    if (const char* e = getenv("GB200_ACQ_THREADS")) return std::min(ACQ_MAX_THREADS, std::max(64, atoi(e) / 32 * 32));  // tuning knob
+    return std::min(ACQ_MAX_THREADS, std::max(128, (bf + 63) / 64 * 64));  // 512: the fused radix-25 pass holds 25 points per thread (128 registers)
 }
 
 int make_plan(gb200_acq* h, int max_smem)
@@ -207,7 +207,7 @@ int make_plan(gb200_acq* h, int max_smem)
         const size_t per_sm = 228 * 1024;
         const int fit = (int)(per_sm / (h->smem + 1024));
         const int k = fit >= 4 ? 4 : fit >= 2 ? 2 : 1;
-        if (getenv("GB200_ACQ_THREADS") == nullptr) h->threads = std::max(128, std::min(h->threads, 512 / k));
+        if (getenv("GB200_ACQ_THREADS") == nullptr) h->threads = k == 1 ? h->threads : std::max(128, std::min(h->threads, 512 / k));
     }
     // forward split: peel the first plain factor of the first stage off into the global stage
     h->split_fwd = false;

@@ -14,6 +14,9 @@
 
 namespace gb200
 {
+#ifndef ACQ_MAX_THREADS
+#define ACQ_MAX_THREADS 512  // threads per CTA of the shared-memory FFT kernels: 128 registers each fill the register file
+#endif
 constexpr int FFT_MAX_STAGES = 20;
 constexpr int FFT_TW_SHIFT = 8;  // W_N^e = A[e >> 8] * B[e & 255]
 constexpr int FFT_TW_LO = 1 << FFT_TW_SHIFT;

@@ -102,7 +102,7 @@ __global__ void acq_phase_table_kernel(const float* __restrict__ inc, int n_bins
 // block as [q][butterfly] of the first inverse stage (position id * RL + q -> q * (m / RL) + id), the order in which
 // acq_inv_kernel's first stage reads it with coalesced loads.
 template <int IQ, bool SRC_IQ>
-__global__ void __launch_bounds__(512) acq_fwd_kernel(FftPlan pl, const void* __restrict__ src, int consumed, const unsigned long long* __restrict__ dphi, const float* __restrict__ phase_tab,
+__global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_fwd_kernel(FftPlan pl, const void* __restrict__ src, int consumed, const unsigned long long* __restrict__ dphi, const float* __restrict__ phase_tab,
     const float2* __restrict__ gT, float2* __restrict__ dst, int code_out)
 {
     extern __shared__ __align__(16) float2 sm[];

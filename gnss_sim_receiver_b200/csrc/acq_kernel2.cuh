@@ -11,7 +11,7 @@ namespace gb200
 //   MODE 1: (g_radix  > 1) store the block to scratch[(slot_i * n_bins + bin)][N] for the global inverse stage
 //   MODE 2: test hook — no code product, store the natural-order complex output to scratch
 template <int MODE>
-__global__ void __launch_bounds__(512) acq_inv_kernel(AcqParams p, const float2* __restrict__ X, const float2* __restrict__ Cs, const int* __restrict__ slots,
+__global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_inv_kernel(AcqParams p, const float2* __restrict__ X, const float2* __restrict__ Cs, const int* __restrict__ slots,
     const float2* __restrict__ gT, float2* __restrict__ scratch, float* __restrict__ grid, AcqCell* __restrict__ cells)
 {
     extern __shared__ __align__(16) float2 sm[];
