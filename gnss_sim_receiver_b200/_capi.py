@@ -63,6 +63,7 @@ SYMBOLS = {
     "gb200_acq_destroy": (C.c_int, [_vp]),
     "gb200_acq_set_local_code": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),
     "gb200_acq_set_doppler_grid": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
+    "gb200_acq_set_doppler_bins": (C.c_int, [_vp, C.POINTER(C.c_float), C.c_int]),
     "gb200_acq_set_wipeoff_mode": (C.c_int, [_vp, C.c_int]),
     "gb200_acq_num_doppler_bins": (C.c_int, [_vp]),
     "gb200_acq_neff": (C.c_int, [_vp]),

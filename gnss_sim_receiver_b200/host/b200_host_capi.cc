@@ -466,12 +466,12 @@ int64_t gb200h_acq_work(gb200h_acq* a, const void* items, int64_t n_items, int c
             const size_t isz = a->adapter->item_size();
             int64_t done = 0;
             int idle_calls = 0;
-            while (done < n_items && idle_calls < 4)
+            while (done < n_items && idle_calls < 8)  // a two-step search makes 4 calls in a row that consume nothing
                 {
                     const int n = static_cast<int>(std::min<int64_t>(chunk, n_items - done));
                     const int c = blk.general_work(static_cast<const char*>(items) + done * isz, n);
                     done += c;
-                    if (!blk.active()) break;
+                    if (!blk.active() && !blk.step_two()) break;  // a two-step search re-activates itself for the fine grid
                     idle_calls = (c == 0) ? idle_calls + 1 : 0;
                 }
             return done;

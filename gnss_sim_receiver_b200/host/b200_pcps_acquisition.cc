@@ -42,13 +42,36 @@ b200_pcps_acquisition::b200_pcps_acquisition(const Acq_Conf& conf)
     sizes(conf, &d_consumed_samples, &d_fft_size);
     iq_dtype_ = item_type_iq(conf.item_type);
     if (iq_dtype_ < 0) throw std::invalid_argument("Unknown item type: " + conf.item_type);
-    if (conf.make_2_steps) std::cerr << "WARNING: make_two_steps is not implemented by the B200 acquisition block; running the single-step search\n";
     const gb200_acq_config g = engine_config(conf, d_fft_size, d_consumed_samples, iq_dtype_, 1);
     if (gb200_acq_create(&g, &h_) != GB200_OK) fail("gb200_acq_create");
+    if (conf.make_2_steps)
+        {
+            if (conf.num_doppler_bins_step2 == 0U) throw std::invalid_argument("make_two_steps needs second_nbins > 0");
+            if (gb200_acq_create(&g, &h2_) != GB200_OK) fail("gb200_acq_create (second step)");
+            d_doppler_center_step_two = 0.0F;
+            update_grid_doppler_wipeoffs_step2();  // sizes the fine grid; re-centred after every positive first step
+        }
     d_data_buffer.assign(static_cast<size_t>(d_consumed_samples) * conf.it_size, 0);
 }
 
-b200_pcps_acquisition::~b200_pcps_acquisition() { gb200_acq_destroy(h_); }
+b200_pcps_acquisition::~b200_pcps_acquisition()
+{
+    gb200_acq_destroy(h_);
+    gb200_acq_destroy(h2_);
+}
+
+// :304-312: fine bins at  centre + (k - floor(n2 / 2)) * second_doppler_step,  float arithmetic
+void b200_pcps_acquisition::update_grid_doppler_wipeoffs_step2()
+{
+    const uint32_t n2 = d_acq_parameters.num_doppler_bins_step2;
+    std::vector<float> f(n2);
+    for (uint32_t k = 0; k < n2; k++)
+        {
+            const float doppler = (static_cast<float>(k) - static_cast<float>(std::floor(n2 / 2.0))) * d_acq_parameters.doppler_step2;
+            f[k] = d_doppler_center_step_two + doppler;
+        }
+    if (gb200_acq_set_doppler_bins(h2_, f.data(), static_cast<int>(n2)) != GB200_OK) fail("gb200_acq_set_doppler_bins");
+}
 
 void b200_pcps_acquisition::apply_grid()
 {
@@ -90,6 +113,7 @@ void b200_pcps_acquisition::set_local_code(std::complex<float>* code)
     std::lock_guard<std::mutex> lk(d_setlock);
     const int n = d_acq_parameters.bit_transition_flag ? static_cast<int>(d_fft_size / 2) : static_cast<int>(d_consumed_samples);
     if (gb200_acq_set_local_code(h_, 0, reinterpret_cast<const gb200_cf32*>(code), n) != GB200_OK) fail("gb200_acq_set_local_code");
+    if (h2_ && gb200_acq_set_local_code(h2_, 0, reinterpret_cast<const gb200_cf32*>(code), n) != GB200_OK) fail("gb200_acq_set_local_code");
 }
 
 // :315-336
@@ -135,12 +159,13 @@ bool b200_pcps_acquisition::start()
 // :884-899 (gb200_acq_threshold evaluates 2 * gamma_p_inv(2 * dwells, (1 - pfa)^(1 / (N_eff * bins))))
 void b200_pcps_acquisition::calculate_threshold()
 {
-    if (d_acq_parameters.pfa <= 0.0F) return;
+    const float pfa = d_step_two ? d_acq_parameters.pfa2 : d_acq_parameters.pfa;  // :886
+    if (pfa <= 0.0F) return;
     if (grid_dirty_) apply_grid();
-    d_threshold = gb200_acq_threshold(h_, d_acq_parameters.pfa);
+    d_threshold = gb200_acq_threshold(d_step_two ? h2_ : h_, pfa);  // :894: the step's own number of Doppler bins
 }
 
-// :600-871 without the two-step branch
+// :600-871
 void b200_pcps_acquisition::acquisition_core(uint64_t samp_count)
 {
     std::unique_lock<std::mutex> lk(d_setlock);
@@ -148,7 +173,14 @@ void b200_pcps_acquisition::acquisition_core(uint64_t samp_count)
     d_num_noncoherent_integrations_counter++;
     if (grid_dirty_) apply_grid();
     const int32_t slot = 0;
-    if (gb200_acq_run(h_, d_data_buffer.data(), static_cast<int>(d_num_noncoherent_integrations_counter) - 1, &slot, 1, &last_) != GB200_OK) fail("gb200_acq_run");
+    if (gb200_acq_run(d_step_two ? h2_ : h_, d_data_buffer.data(), static_cast<int>(d_num_noncoherent_integrations_counter) - 1, &slot, 1, &last_) != GB200_OK) fail("gb200_acq_run");
+    if (d_step_two)
+        {
+            // :524 / :561: the fine bin's frequency, float arithmetic then truncated to int32
+            const float n2 = static_cast<float>(d_acq_parameters.num_doppler_bins_step2);
+            last_.doppler_hz = static_cast<int32_t>(d_doppler_center_step_two + (static_cast<float>(last_.doppler_index) - static_cast<float>(std::floor(n2 / 2.0))) * d_acq_parameters.doppler_step2);
+            last_.acq_doppler_hz = static_cast<float>(last_.doppler_hz);
+        }
     d_mag = last_.peak;
     d_input_power = last_.input_power;
     d_test_statistics = last_.test_statistics;
@@ -166,15 +198,46 @@ void b200_pcps_acquisition::acquisition_core(uint64_t samp_count)
             d_gnss_synchro->Acq_doppler_hz = static_cast<double>(last_.doppler_hz);
             d_gnss_synchro->Acq_samplestamp_samples = samp_count;
         }
-    d_gnss_synchro->Acq_doppler_step = d_doppler_step;
+    d_gnss_synchro->Acq_doppler_step = d_step_two ? static_cast<uint32_t>(d_acq_parameters.doppler_step2) : d_doppler_step;  // :749,:756
 
+    // a positive search: declare it, or (make_two_steps, first step) arm the fine Doppler grid around it (:770-787, :818-838)
+    const auto positive = [&](bool reset_counters) {
+        if (p.make_2_steps)
+            {
+                if (d_step_two)
+                    {
+                        send_positive_acquisition();
+                        d_step_two = false;
+                        d_state = 0;
+                    }
+                else
+                    {
+                        d_step_two = true;  // next: a fresh buffer searched on the small grid
+                        d_doppler_center_step_two = static_cast<float>(d_gnss_synchro->Acq_doppler_hz);
+                        update_grid_doppler_wipeoffs_step2();
+                        d_num_noncoherent_integrations_counter = 0U;
+                        if (reset_counters) d_positive_acq = 0;
+                        d_state = 0;
+                    }
+                calculate_threshold();
+            }
+        else
+            {
+                send_positive_acquisition();
+                d_state = 0;
+            }
+    };
+    const auto leave_step_two = [&] {
+        const bool was_step_two = d_step_two;
+        d_step_two = false;
+        if (was_step_two) calculate_threshold();
+    };
     if (!p.bit_transition_flag)
         {
             if (d_test_statistics > d_threshold)
                 {
                     d_active = false;
-                    send_positive_acquisition();
-                    d_state = 0;
+                    positive(true);
                 }
             else
                 {
@@ -186,16 +249,20 @@ void b200_pcps_acquisition::acquisition_core(uint64_t samp_count)
                     if (d_state != 0) send_negative_acquisition();
                     d_state = 0;
                     d_active = false;
+                    leave_step_two();
                 }
         }
     else
         {
             d_active = false;
-            d_state = 0;
             if (d_test_statistics > d_threshold)
-                send_positive_acquisition();
+                positive(false);
             else
-                send_negative_acquisition();
+                {
+                    d_state = 0;
+                    leave_step_two();
+                    send_negative_acquisition();
+                }
         }
     d_worker_active = false;
     if (d_num_noncoherent_integrations_counter == p.max_dwells || d_positive_acq == 1 || p.bit_transition_flag)
@@ -218,6 +285,11 @@ int b200_pcps_acquisition::general_work(const void* input_items, int ninput_item
                 {
                     d_sample_counter += static_cast<uint64_t>(ninput_items);
                     consumed = ninput_items;
+                }
+            if (d_step_two)  // :927-931: the fine search starts on its own
+                {
+                    d_state = 0;
+                    d_active = true;
                 }
             return consumed;
         }

@@ -54,6 +54,7 @@ public:
     // observers
     int state() const { return d_state; }
     bool active() const { return d_active; }
+    bool step_two() const { return d_step_two; }  // armed for (or running) the fine-Doppler step of make_two_steps
     float threshold() const { return d_threshold; }
     float test_statistics() const { return d_test_statistics; }
     float input_power() const { return d_input_power; }
@@ -73,6 +74,10 @@ private:
 
     Acq_Conf d_acq_parameters;
     gb200_acq* h_{nullptr};
+    gb200_acq* h2_{nullptr};  // second (fine Doppler) step of make_two_steps: its own grid of second_nbins bins
+    bool d_step_two{false};
+    float d_doppler_center_step_two{0.0F};
+    void update_grid_doppler_wipeoffs_step2();
     Gnss_Synchro* d_gnss_synchro{nullptr};
     std::weak_ptr<ChannelFsm> d_channel_fsm;
     std::function<void(int)> event_sink_;

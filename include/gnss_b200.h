@@ -186,6 +186,10 @@ int gb200_acq_destroy(gb200_acq* h);
 int gb200_acq_set_local_code(gb200_acq* h, int slot, const gb200_cf32* code, int n_code);
 /* set_doppler_max/step/center + update_grid_doppler_wipeoffs — pcps_acquisition.cc:248-302 */
 int gb200_acq_set_doppler_grid(gb200_acq* h, int doppler_max, int doppler_step, int doppler_center);
+/* Explicit list of wipe-off frequencies, one per Doppler bin, as update_grid_doppler_wipeoffs_step2 forms them for the
+ * second (fine) step of a two-step acquisition (pcps_acquisition.cc:304-312): floats, not necessarily on an integer grid.
+ * Results then carry doppler_index only (doppler_hz and acq_doppler_hz are 0: the caller maps the index). */
+int gb200_acq_set_doppler_bins(gb200_acq* h, const float* doppler_hz, int n_bins);
 /* Doppler wipe-off law.  0 (default): the reference's — (cosf, sinf) of an fp32 phase accumulated by repeated addition
  * (update_local_carrier :232-245 -> volk_gnsssdr_s32f_sincos_32fc_generic), so the magnitude grid matches the reference's
  * to ~1e-6; 1: exact phase exp(-j*2*pi*f*n/fs) (about 1e-4 of the peak away from the reference's own table, and closer

@@ -129,3 +129,35 @@ def test_acquisition_to_tracking_handover():
     assert len(r) > 50 and np.all(r["valid"] == 1) and np.all(r["prn"] == prn)
     bank.close()
     a.close()
+
+
+def test_two_step_acquisition_refines_doppler():
+    """make_two_steps (pcps_acquisition.cc:698-757,770-787): a positive coarse search arms a fine grid of second_nbins bins,
+    second_doppler_step apart, centred on the coarse Doppler; it runs on the NEXT buffer with the second step's own threshold
+    (pfa_second_step, second_nbins) and only then declares the acquisition."""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    prn, doppler, delay = 7, 835.0, 311.0
+    x = _stream(4 * 4000, prn, doppler, delay, 48.0, seed=13)
+    conf_text = CONF.format(item="gr_complex", pfa=0.01, dwells=1) + "Acquisition_1C.make_two_steps=true\nAcquisition_1C.second_nbins=4\nAcquisition_1C.second_doppler_step=125\n"
+    a = H.AcquisitionBlock(conf_text, "Acquisition_1C", prn)
+    a.arm()
+    consumed = a.work(x, chunk=1000)
+    s = a.status()
+    # oracle: coarse search on the first buffer, fine search on the second (the equivalent integer grid: -250 + c + 125 k)
+    conf1, r1 = _oracle(dict(prn=prn, dwells=[x[:4000]]))
+    assert r1.acq_doppler_hz == 750.0
+    conf2 = O.acq_conf(FS, 4000, 4000, 250, 125, float(np.float32(4e6) * np.float32(0.001)), 4, doppler_center=int(r1.acq_doppler_hz))
+    assert conf2.num_doppler_bins == 4
+    fc = O.acq_set_local_code(conf2, O.gps_l1_ca_code_sampled(prn, int(FS), 4000))
+    r2 = O.acq_statistic(conf2, O.acq_dwell(conf2, x[4000:8000], fc))
+    assert s.last_event == 1 and s.active == 0 and s.state == 0
+    assert consumed == 8000 and s.acq_samplestamp_samples == 8000
+    assert (s.indext, s.doppler_index) == (r2.indext, r2.doppler_index)
+    assert s.acq_doppler_hz == r2.acq_doppler_hz == 875.0          # nearest fine bin to 835 Hz
+    assert s.acq_delay_samples == r2.acq_delay_samples
+    assert abs(s.test_statistics - r2.test_statistics) <= 1e-3 * r2.test_statistics
+    # the fine step was judged against its own threshold (4 bins, pfa_second_step); once it has declared the acquisition the block
+    # is back on the coarse step's threshold (calculate_threshold after d_step_two = false, :775-786)
+    assert s.test_statistics > O.acq_threshold(conf2, 0.01)
+    assert abs(s.threshold - O.acq_threshold(conf1, 0.01)) <= 1e-5 * s.threshold
+    a.close()
