@@ -68,6 +68,12 @@ SYMBOLS = {
     "gb200h_acq_arm": (_i, [_vp, _f]),
     "gb200h_acq_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
     "gb200h_acq_get_status": (_i, [_vp, C.POINTER(AcqStatus)]),
+    "gb200h_rx_create": (_i, [_s, _s, _s, _i, C.POINTER(C.c_uint), _i, C.POINTER(_vp)]),
+    "gb200h_rx_destroy": (None, [_vp]),
+    "gb200h_rx_push": (_i, [_vp, _vp, C.c_int64, _vp, _i]),
+    "gb200h_rx_channel_info": (_i, [_vp, _i, _vp]),
+    "gb200h_rx_sweeps": (C.c_uint64, [_vp]),
+    "gb200h_rx_threshold": (_f, [_vp]),
 }
 
 _LIB = None
@@ -189,3 +195,46 @@ class AcquisitionBlock:
         s = AcqStatus()
         check(self._lib.gb200h_acq_get_status(self._h, C.byref(s)))
         return s
+
+
+class ChannelManager:
+    """B200ChannelManager (host/b200_channel_manager.h): batched all-PRN acquisition sweep feeding a lock-step tracking bank."""
+
+    def __init__(self, conf_text, acq_role, trk_role, n_channels, prns):
+        self._lib = lib()
+        self._h = _vp()
+        self.n = n_channels
+        p = (C.c_uint * len(prns))(*[int(x) for x in prns])
+        check(self._lib.gb200h_rx_create(conf_text.encode(), acq_role.encode(), trk_role.encode(), n_channels, p, len(prns), C.byref(self._h)))
+        self._rec = np.zeros(1 << 16, dtype=REC_DTYPE)
+
+    def close(self):
+        if self._h:
+            self._lib.gb200h_rx_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def push(self, iq):
+        iq = np.ascontiguousarray(iq)
+        n = iq.size if np.iscomplexobj(iq) else iq.size // 2
+        k = check(self._lib.gb200h_rx_push(self._h, iq.ctypes.data, n, self._rec.ctypes.data, len(self._rec)))
+        return self._rec[:k].copy()
+
+    def channel_info(self, ch):
+        v = np.zeros(10)
+        check(self._lib.gb200h_rx_channel_info(self._h, ch, v.ctypes.data))
+        keys = ["state", "prn", "acquisitions", "losses", "acq_doppler_hz", "acq_delay_samples", "acq_samplestamp_samples", "test_statistics", "trk_state", "cn0_db_hz"]
+        return dict(zip(keys, v))
+
+    @property
+    def sweeps(self):
+        return self._lib.gb200h_rx_sweeps(self._h)
+
+    @property
+    def threshold(self):
+        return self._lib.gb200h_rx_threshold(self._h)

@@ -1,5 +1,6 @@
 #include "b200_host_capi.h"
 #include "b200_adapters.h"
+#include "b200_channel_manager.h"
 #include "b200_configuration.h"
 #include "b200_gnss_codes.h"
 #include "b200_tracking_bank.h"
@@ -499,5 +500,66 @@ int gb200h_acq_get_status(gb200h_acq* a, gb200h_acq_status* s)
     s->doppler_index = blk.last_result().doppler_index;
     return 0;
 }
+
+struct gb200h_rx
+{
+    B200Configuration cfg;
+    std::unique_ptr<B200ChannelManager> mgr;
+    std::vector<B200TrackingBank::Output> outs;
+};
+
+int gb200h_rx_create(const char* conf_text, const char* acq_role, const char* trk_role, int n_channels, const unsigned* prns, int n_prns, gb200h_rx** out)
+{
+    try
+        {
+            auto r = std::make_unique<gb200h_rx>();
+            r->cfg.load_string(conf_text);
+            r->mgr = std::make_unique<B200ChannelManager>(&r->cfg, acq_role, trk_role, n_channels, std::vector<unsigned>(prns, prns + n_prns));
+            *out = r.release();
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+void gb200h_rx_destroy(gb200h_rx* r) { delete r; }
+
+int gb200h_rx_push(gb200h_rx* r, const void* iq, int64_t n_samples, gb200h_trk_record* records, int max_records)
+{
+    try
+        {
+            r->outs.clear();
+            r->mgr->push(iq, n_samples, &r->outs);
+            const int n = std::min<int>(static_cast<int>(r->outs.size()), max_records);
+            for (int i = 0; i < n; i++) to_record(r->outs[i].channel, r->outs[i].synchro, &records[i]);
+            return n;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int gb200h_rx_channel_info(gb200h_rx* r, int ch, double* v)
+{
+    if (!r || ch < 0 || ch >= r->mgr->size()) return -1;
+    const auto c = r->mgr->info(ch);
+    v[0] = c.state;
+    v[1] = c.prn;
+    v[2] = c.acquisitions;
+    v[3] = c.losses;
+    v[4] = c.acq_doppler_hz;
+    v[5] = c.acq_delay_samples;
+    v[6] = static_cast<double>(c.acq_samplestamp_samples);
+    v[7] = c.test_statistics;
+    v[8] = r->mgr->bank().block(ch).state();
+    v[9] = r->mgr->bank().block(ch).cn0_db_hz();
+    return 0;
+}
+
+uint64_t gb200h_rx_sweeps(gb200h_rx* r) { return r->mgr->sweeps(); }
+float gb200h_rx_threshold(gb200h_rx* r) { return r->mgr->threshold(); }
 
 }  // extern "C"

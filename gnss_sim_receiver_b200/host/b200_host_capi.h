@@ -81,6 +81,18 @@ int gb200h_acq_arm(gb200h_acq* a, float threshold_if_no_pfa);
 int64_t gb200h_acq_work(gb200h_acq* a, const void* items, int64_t n_items, int chunk);
 int gb200h_acq_get_status(gb200h_acq* a, gb200h_acq_status* s);
 
+/* ---- channel manager (B200ChannelManager): batched acquisition sweep feeding a lock-step tracking bank */
+typedef struct gb200h_rx gb200h_rx;
+int gb200h_rx_create(const char* conf_text, const char* acq_role, const char* trk_role, int n_channels, const unsigned* prns, int n_prns, gb200h_rx** out);
+void gb200h_rx_destroy(gb200h_rx* r);
+/* feed host samples of the configured item type; returns the number of tracking records written (<= max_records) */
+int gb200h_rx_push(gb200h_rx* r, const void* iq, int64_t n_samples, gb200h_trk_record* records, int max_records);
+/* v[0..9] = state (0 standby, 1 acquisition, 2 tracking), prn, acquisitions, losses, acq_doppler_hz, acq_delay_samples,
+ * acq_samplestamp_samples, test_statistics, tracking block state, tracking CN0 (dB-Hz) */
+int gb200h_rx_channel_info(gb200h_rx* r, int ch, double* v);
+uint64_t gb200h_rx_sweeps(gb200h_rx* r);
+float gb200h_rx_threshold(gb200h_rx* r);
+
 #ifdef __cplusplus
 }
 #endif

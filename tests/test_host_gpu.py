@@ -161,3 +161,57 @@ def test_two_step_acquisition_refines_doppler():
     assert s.test_statistics > O.acq_threshold(conf2, 0.01)
     assert abs(s.threshold - O.acq_threshold(conf1, 0.01)) <= 1e-5 * s.threshold
     a.close()
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built")
+def test_channel_manager_acquires_tracks_loses_and_reacquires():
+    """the callers around the two engines.  Three satellites in the air, three channels, all 32 PRNs searched in
+    one sweep per buffered block.  One satellite is switched off for 2.4 s: its channel loses lock (ChannelFsm state 2 -> 0),
+    the sweeps resume for the idle channel, and the satellite is re-acquired when it comes back."""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    prns = [4, 13, 22]
+    dop = [1300.0, -2650.0, 420.0]
+    dly = [100.7, 640.2, 901.5]
+    cn0 = [47.0, 45.0, 46.0]
+    codes = np.stack([O.gps_l1_ca_code(p) for p in prns])
+    bits = np.random.default_rng(2).choice(np.array([-1, 1], dtype=np.int8), (3, 3000))
+    pre = np.array([1, -1, -1, -1, 1, -1, 1, 1], dtype=np.int8)
+    for b in range(0, 3000, 50):
+        bits[:, b:b + 8] = pre
+    # pfa: thousands of sweeps x 32 satellites must not raise a false alarm.  Lock test every 20 symbols x 20 ms = 0.4 s on a CN0
+    # smoothed with the default alpha = 0.002 would coast through the outage: a fast smoother and no tolerance make the loss prompt
+    conf_text = (CONF.format(item="gr_complex", pfa=1e-7, dwells=1).replace("max_lock_fail=50", "max_lock_fail=0").replace("cn0_min=25", "cn0_min=30")
+                 + "Tracking_1C.cn0_smoother_alpha=0.5\n")
+    rx = H.ChannelManager(conf_text, "Acquisition_1C", "Tracking_1C", 3, list(range(1, 33)))
+    chunk = 400000
+    off_from, off_to, total = int(4.0 * FS), int(6.4 * FS), int(10.4 * FS)  # pull-in 2 s + bit sync <= 1.2 s before and after
+    recs = []
+    history = []
+    for first in range(0, total, chunk):
+        gone = off_from <= first < off_to  # PRN 22 off the air for these chunks (same seed: the noise is unchanged)
+        k = 2 if gone else 3
+        x = O.gen_if(chunk, first, FS, codes[:k], dop[:k], dly[:k], [0.3, 1.1, 2.0][:k], cn0[:k], nav_bits=bits[:k], seed=31)
+        recs.append(rx.push(x))
+        history.append([rx.channel_info(c) for c in range(3)] + [rx.sweeps])
+    r = np.concatenate(recs)
+    info = [rx.channel_info(c) for c in range(3)]
+    by_prn = {int(i["prn"]): i for i in info if i["state"] == 2}
+    # all three satellites end up tracked, each on one channel, nothing else was declared
+    assert sorted(by_prn) == prns, info
+    assert sum(i["acquisitions"] for i in info) == 4 and sum(i["losses"] for i in info) == 1, info
+    for p, f in zip(prns, dop):
+        assert abs(by_prn[p]["acq_doppler_hz"] - f) <= 125.0 and by_prn[p]["trk_state"] >= 2
+        assert abs(by_prn[p]["cn0_db_hz"] - cn0[prns.index(p)]) < 3.0
+    # the two satellites that never went away were acquired by the first sweep and never lost
+    first_sweep = history[0]
+    assert sorted(int(i["prn"]) for i in first_sweep[:3] if i["state"] == 2) == prns and first_sweep[3] <= 3
+    assert by_prn[22]["acquisitions"] == 2 and by_prn[22]["losses"] == 1 and by_prn[4]["losses"] == 0 and by_prn[13]["losses"] == 0
+    assert by_prn[22]["acq_samplestamp_samples"] >= off_to
+    # no idle channel, no sweep: the count stands still until the loss of lock, then one sweep per buffered millisecond
+    assert history[int(3.9 * FS) // chunk][3] == first_sweep[3]
+    # PRN 22's records stop while it is off the air and resume after the re-acquisition
+    t22 = r["tracking_sample_counter"][(r["prn"] == 22) & (r["valid"] == 1)].astype(np.int64)
+    assert np.any(t22 < off_from) and np.any(t22 > off_to + int(2.0 * FS))
+    assert np.max(np.diff(t22)) > int(2.0 * FS)  # lost inside the outage, re-acquired after it, 2 s of pull-in
+    assert 100 < rx.sweeps < 2500
+    rx.close()
