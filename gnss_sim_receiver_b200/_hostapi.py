@@ -68,6 +68,7 @@ SYMBOLS = {
     "gb200h_acq_arm": (_i, [_vp, _f]),
     "gb200h_acq_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
     "gb200h_acq_get_status": (_i, [_vp, C.POINTER(AcqStatus)]),
+    "gb200h_mat_write_sample": (_i, [_s, _vp, _i, _i, C.c_int32, C.c_uint32, C.c_uint64, _f]),
     "gb200h_rx_create": (_i, [_s, _s, _s, _i, C.POINTER(C.c_uint), _i, C.POINTER(_vp)]),
     "gb200h_rx_destroy": (None, [_vp]),
     "gb200h_rx_push": (_i, [_vp, _vp, C.c_int64, _vp, _i]),

@@ -1,6 +1,7 @@
 #include "b200_host_capi.h"
 #include "b200_adapters.h"
 #include "b200_channel_manager.h"
+#include "b200_mat_writer.h"
 #include "b200_configuration.h"
 #include "b200_gnss_codes.h"
 #include "b200_tracking_bank.h"
@@ -498,6 +499,18 @@ int gb200h_acq_get_status(gb200h_acq* a, gb200h_acq_status* s)
     s->last_event = a->last_event;
     s->indext = blk.last_result().indext;
     s->doppler_index = blk.last_result().doppler_index;
+    return 0;
+}
+
+int gb200h_mat_write_sample(const char* filename, const float* grid, int rows, int cols, int32_t i32, uint32_t u32, uint64_t u64, float f32)
+{
+    MatFile5 m(filename);
+    if (!m.ok()) return -1;
+    m.write("acq_grid", MatFile5::SINGLE, static_cast<uint32_t>(rows), static_cast<uint32_t>(cols), grid);
+    m.scalar("doppler_max", MatFile5::INT32, i32);
+    m.scalar("PRN", MatFile5::UINT32, u32);
+    m.scalar("sample_counter", MatFile5::UINT64, u64);
+    m.scalar("threshold", MatFile5::SINGLE, f32);
     return 0;
 }
 

@@ -81,6 +81,9 @@ int gb200h_acq_arm(gb200h_acq* a, float threshold_if_no_pfa);
 int64_t gb200h_acq_work(gb200h_acq* a, const void* items, int64_t n_items, int chunk);
 int gb200h_acq_get_status(gb200h_acq* a, gb200h_acq_status* s);
 
+/* MAT level-5 writer used by the acquisition dump (b200_mat_writer.h): one file with a single matrix and one scalar of each class */
+int gb200h_mat_write_sample(const char* filename, const float* grid, int rows, int cols, int32_t i32, uint32_t u32, uint64_t u64, float f32);
+
 /* ---- channel manager (B200ChannelManager): batched acquisition sweep feeding a lock-step tracking bank */
 typedef struct gb200h_rx gb200h_rx;
 int gb200h_rx_create(const char* conf_text, const char* acq_role, const char* trk_role, int n_channels, const unsigned* prns, int n_prns, gb200h_rx** out);

@@ -1,4 +1,5 @@
 #include "b200_pcps_acquisition.h"
+#include "b200_mat_writer.h"
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -44,10 +45,21 @@ b200_pcps_acquisition::b200_pcps_acquisition(const Acq_Conf& conf)
     if (iq_dtype_ < 0) throw std::invalid_argument("Unknown item type: " + conf.item_type);
     const gb200_acq_config g = engine_config(conf, d_fft_size, d_consumed_samples, iq_dtype_, 1);
     if (gb200_acq_create(&g, &h_) != GB200_OK) fail("gb200_acq_create");
+    d_dump = conf.dump;
+    if (d_dump)
+        {
+            // :134-165: the dump name without its extension; the grid must stay on the device after a sweep
+            d_dump_filename = conf.dump_filename.empty() ? std::string("./acquisition") : conf.dump_filename;
+            const size_t slash = d_dump_filename.find_last_of('/');
+            const size_t dot = d_dump_filename.find_last_of('.');
+            if (dot != std::string::npos && dot != 0 && (slash == std::string::npos || dot > slash + 1)) d_dump_filename.erase(dot);
+            if (gb200_acq_keep_grid(h_, 1) != GB200_OK) fail("gb200_acq_keep_grid");
+        }
     if (conf.make_2_steps)
         {
             if (conf.num_doppler_bins_step2 == 0U) throw std::invalid_argument("make_two_steps needs second_nbins > 0");
             if (gb200_acq_create(&g, &h2_) != GB200_OK) fail("gb200_acq_create (second step)");
+            if (d_dump && gb200_acq_keep_grid(h2_, 1) != GB200_OK) fail("gb200_acq_keep_grid");
             d_doppler_center_step_two = 0.0F;
             update_grid_doppler_wipeoffs_step2();  // sizes the fine grid; re-centred after every positive first step
         }
@@ -267,6 +279,7 @@ void b200_pcps_acquisition::acquisition_core(uint64_t samp_count)
     d_worker_active = false;
     if (d_num_noncoherent_integrations_counter == p.max_dwells || d_positive_acq == 1 || p.bit_transition_flag)
         {
+            if (d_dump && d_positive_acq) dump_results(static_cast<int32_t>(p.bit_transition_flag ? d_fft_size / 2 : d_fft_size));  // :862-866
             d_num_noncoherent_integrations_counter = 0U;
             d_positive_acq = 0;
         }
@@ -335,6 +348,56 @@ int b200_pcps_acquisition::general_work(const void* input_items, int ninput_item
             break;
         }
     return consumed;
+}
+
+// :393-493 — same file name scheme, variable names, classes and shapes; MAT level 5 instead of v7.3 (b200_mat_writer.h)
+void b200_pcps_acquisition::dump_results(int32_t effective_fft_size)
+{
+    d_dump_number++;
+    std::string filename = d_dump_filename;
+    filename.append("_");
+    filename.append(1, d_gnss_synchro->System);
+    filename.append("_");
+    filename.append(1, d_gnss_synchro->Signal[0]);
+    filename.append(1, d_gnss_synchro->Signal[1]);
+    filename.append("_ch_");
+    filename.append(std::to_string(d_channel));
+    filename.append("_");
+    filename.append(std::to_string(d_dump_number));
+    filename.append("_sat_");
+    filename.append(std::to_string(d_gnss_synchro->PRN));
+    filename.append(".mat");
+    MatFile5 mat(filename);
+    if (!mat.ok())
+        {
+            std::cout << "Unable to create or open Acquisition dump file\n";
+            return;
+        }
+    const auto neff = static_cast<uint32_t>(effective_fft_size);
+    // d_grid: effective_fft_size x num_doppler_bins, column-major = one Doppler bin after the other
+    std::vector<float> grid(static_cast<size_t>(d_num_doppler_bins) * neff);
+    if (gb200_acq_read_grid(h_, 0, grid.data()) != GB200_OK) fail("gb200_acq_read_grid");
+    mat.write("acq_grid", MatFile5::SINGLE, neff, d_num_doppler_bins, grid.data());
+    mat.scalar("doppler_max", MatFile5::INT32, static_cast<int32_t>(d_acq_parameters.doppler_max));
+    mat.scalar("doppler_step", MatFile5::INT32, static_cast<int32_t>(d_doppler_step));
+    mat.scalar("d_positive_acq", MatFile5::INT32, static_cast<int32_t>(d_positive_acq));
+    mat.scalar("acq_doppler_hz", MatFile5::SINGLE, static_cast<float>(d_gnss_synchro->Acq_doppler_hz));
+    mat.scalar("acq_delay_samples", MatFile5::SINGLE, static_cast<float>(d_gnss_synchro->Acq_delay_samples));
+    mat.scalar("test_statistic", MatFile5::SINGLE, d_test_statistics);
+    mat.scalar("threshold", MatFile5::SINGLE, d_threshold);
+    mat.scalar("input_power", MatFile5::SINGLE, d_input_power);
+    mat.scalar("sample_counter", MatFile5::UINT64, static_cast<uint64_t>(d_sample_counter));
+    mat.scalar("PRN", MatFile5::UINT32, static_cast<uint32_t>(d_gnss_synchro->PRN));
+    mat.scalar("num_dwells", MatFile5::INT32, static_cast<int32_t>(d_num_noncoherent_integrations_counter));
+    if (d_acq_parameters.make_2_steps)
+        {
+            const uint32_t n2 = d_acq_parameters.num_doppler_bins_step2;
+            std::vector<float> narrow(static_cast<size_t>(n2) * neff);
+            if (gb200_acq_read_grid(h2_, 0, narrow.data()) != GB200_OK) fail("gb200_acq_read_grid");
+            mat.write("acq_grid_narrow", MatFile5::SINGLE, neff, n2, narrow.data());
+            mat.scalar("doppler_step_narrow", MatFile5::SINGLE, d_acq_parameters.doppler_step2);
+            mat.scalar("doppler_grid_narrow_min", MatFile5::SINGLE, d_doppler_center_step_two - static_cast<float>(std::floor(n2 / 2.0)) * d_acq_parameters.doppler_step2);
+        }
 }
 
 std::vector<float> b200_pcps_acquisition::magnitude_grid()

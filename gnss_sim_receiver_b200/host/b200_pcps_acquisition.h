@@ -18,6 +18,7 @@
 #include <functional>
 #include <memory>
 #include <mutex>
+#include <string>
 #include <vector>
 
 namespace gb200h
@@ -78,6 +79,10 @@ private:
     bool d_step_two{false};
     float d_doppler_center_step_two{0.0F};
     void update_grid_doppler_wipeoffs_step2();
+    void dump_results(int32_t effective_fft_size);  // :393-493
+    bool d_dump{false};
+    long long d_dump_number{0};
+    std::string d_dump_filename;
     Gnss_Synchro* d_gnss_synchro{nullptr};
     std::weak_ptr<ChannelFsm> d_channel_fsm;
     std::function<void(int)> event_sink_;

@@ -235,3 +235,22 @@ def test_gpu_entry_points_fail_loudly_without_a_device():
         H.TrackingBank(CONF_C1, "Tracking_1C", 2)
     with pytest.raises(H.HostError, match="no CUDA device|CPU fallback"):
         H.AcquisitionBlock(CONF_C1, "Acquisition_1C", 1)
+
+
+def test_mat_writer_is_readable_by_scipy(tmp_path):
+    """The acquisition dump writer (MAT level 5): classes, shapes and column-major data survive a round trip through
+    scipy.io.loadmat, the reader the reference's python utilities use."""
+    import ctypes as C
+    from scipy.io import loadmat
+    from gnss_sim_receiver_b200 import _hostapi as H
+    rng = np.random.default_rng(1)
+    grid = rng.random((5, 37)).astype(np.float32)  # 5 Doppler bins of 37 code phases, one bin after the other
+    f = str(tmp_path / "acq_G_1C_ch_0_1_sat_7.mat")
+    assert H.lib().gb200h_mat_write_sample(f.encode(), grid.ctypes.data, 37, 5, -5000, 7, 2**40 + 3, np.float32(2.5)) == 0
+    m = loadmat(f)
+    assert m["acq_grid"].dtype == np.float32 and m["acq_grid"].shape == (37, 5)
+    assert np.array_equal(m["acq_grid"], grid.T)
+    assert m["doppler_max"].dtype == np.int32 and int(m["doppler_max"][0, 0]) == -5000
+    assert m["PRN"].dtype == np.uint32 and int(m["PRN"][0, 0]) == 7
+    assert m["sample_counter"].dtype == np.uint64 and int(m["sample_counter"][0, 0]) == 2**40 + 3
+    assert m["threshold"].dtype == np.float32 and float(m["threshold"][0, 0]) == 2.5

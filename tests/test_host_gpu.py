@@ -215,3 +215,36 @@ def test_channel_manager_acquires_tracks_loses_and_reacquires():
     assert np.max(np.diff(t22)) > int(2.0 * FS)  # lost inside the outage, re-acquired after it, 2 s of pull-in
     assert 100 < rx.sweeps < 2500
     rx.close()
+
+
+def test_acquisition_dump_file(tmp_path):
+    """Acquisition_XX.dump=true: the .mat written after a positive acquisition (pcps_acquisition.cc:393-493) carries the search
+    grid and the scalars under the reference's variable names; here for a two-step search (coarse + narrow grid)."""
+    from scipy.io import loadmat
+    from gnss_sim_receiver_b200 import _hostapi as H
+    prn, doppler, delay = 7, 835.0, 311.0
+    x = _stream(4 * 4000, prn, doppler, delay, 48.0, seed=13)
+    conf_text = (CONF.format(item="gr_complex", pfa=0.01, dwells=1) + "Acquisition_1C.make_two_steps=true\nAcquisition_1C.second_nbins=4\n"
+                 "Acquisition_1C.second_doppler_step=125\nAcquisition_1C.dump=true\nAcquisition_1C.dump_filename=" + str(tmp_path / "acq_dump.mat") + "\n")
+    a = H.AcquisitionBlock(conf_text, "Acquisition_1C", prn)
+    a.arm()
+    a.work(x, chunk=1000)
+    s = a.status()
+    assert s.last_event == 1
+    files = sorted(os.listdir(tmp_path))
+    assert files == ["acq_dump_G_1C_ch_0_1_sat_7.mat"], files
+    m = loadmat(str(tmp_path / files[0]))
+    conf1 = O.acq_conf(FS, 4000, 4000, 10000, 250, float(np.float32(4e6) * np.float32(0.001)), 4)
+    fc = O.acq_set_local_code(conf1, O.gps_l1_ca_code_sampled(prn, int(FS), 4000))
+    g1 = O.acq_dwell(conf1, x[:4000], fc)
+    conf2 = O.acq_conf(FS, 4000, 4000, 250, 125, float(np.float32(4e6) * np.float32(0.001)), 4, doppler_center=750)
+    g2 = O.acq_dwell(conf2, x[4000:8000], fc)
+    assert m["acq_grid"].shape == (4000, 80) and m["acq_grid_narrow"].shape == (4000, 4)
+    assert np.max(np.abs(m["acq_grid"].T - g1)) <= 2e-5 * g1.max()
+    assert np.max(np.abs(m["acq_grid_narrow"].T - g2)) <= 2e-5 * g2.max()
+    assert int(m["doppler_max"][0, 0]) == 10000 and int(m["doppler_step"][0, 0]) == 250 and int(m["d_positive_acq"][0, 0]) == 1
+    assert int(m["PRN"][0, 0]) == prn and int(m["sample_counter"][0, 0]) == 8000 and int(m["num_dwells"][0, 0]) == 1
+    assert float(m["acq_doppler_hz"][0, 0]) == 875.0 and float(m["acq_delay_samples"][0, 0]) == s.acq_delay_samples
+    assert float(m["doppler_step_narrow"][0, 0]) == 125.0 and float(m["doppler_grid_narrow_min"][0, 0]) == 500.0
+    assert abs(float(m["test_statistic"][0, 0]) - s.test_statistics) <= 1e-6 * s.test_statistics
+    a.close()
