@@ -329,7 +329,7 @@ def run_ours(args):
     launches = lib.gb200_launch_count() - l0
     barrier(dist)
     # sustained (no flush, back to back) for the clock record: keeps the GPU under load long enough for nvidia-smi to see it
-    sustained_ms = eng.replay(max(K, 50))
+    sustained_ms = eng.replay(max(K, 50, int(1500.0 * K / max(dev_ms, 1e-3))))  # ~1.5 s: several nvidia-smi samples
     dev_ms = reduce_max(dist, local, dev_ms)
     sustained_ms = reduce_max(dist, local, sustained_ms)
     clocks = sampler.summary() if rank == 0 else None

@@ -62,6 +62,8 @@ constexpr double TWO_PI = 6.283185307179586476925286766559;
 // Stage radices in DIF order, even factors first (the late, short-stride stages are the odd ones).  Pairs of equal small
 // factors are fused into one register-resident pass (16 = 4x4, 8 = 4x2, 9 = 3x3, 25 = 5x5; acq_fft.cuh: fft_smem_stage2):
 // 25000 = 8 * 25 * 25 * 5 takes 4 passes over shared memory instead of 7.  GB200_ACQ_PLAIN_RADIX=1 keeps the plain stages.
+bool is_small_radix(int r) { return r == 2 || r == 3 || r == 4 || r == 5 || r == 7 || r == 8 || r == 9 || r == 16 || r == 25; }
+
 bool factor_235(int n, std::vector<int>& radix, bool fuse)
 {
     radix.clear();
@@ -70,6 +72,10 @@ bool factor_235(int n, std::vector<int>& radix, bool fuse)
     while (n % 3 == 0) { c3++; n /= 3; }
     while (n % 5 == 0) { c5++; n /= 5; }
     while (n % 7 == 0) { c7++; n /= 7; }
+    // what is left must split into primes 11 ... 61 (generic O(P) per point stage, acq_fft.cuh: fft_smem_stage_prime)
+    std::vector<int> primes;
+    for (int p = 11; p <= 61 && n > 1; p += 2)
+        while (n % p == 0) { primes.push_back(p); n /= p; }
     if (n != 1) return false;
     if (fuse)
         {
@@ -85,6 +91,12 @@ bool factor_235(int n, std::vector<int>& radix, bool fuse)
         while (c5 >= 2) { radix.push_back(25); c5 -= 2; }
     while (c5--) radix.push_back(5);
     while (c7--) radix.push_back(7);
+    if (!primes.empty())
+        {
+            // the first and the last stage carry the hooks of the inverse kernel: the prime stages go in between
+            if (radix.size() < 2) return false;
+            radix.insert(radix.begin() + 1, primes.begin(), primes.end());
+        }
     return (int)radix.size() <= FFT_MAX_STAGES;
 }
 
@@ -110,10 +122,36 @@ int build_stage_tables(FftPlan& pl, std::vector<float2>* tab)
             int f1, f2;
             stage_factors(pl.radix[s], &f1, &f2);
             const int ms1 = n_s / f1;
-            const int jmax = f2 > 1 ? ms1 / f2 : ms1;  // butterfly positions j < jmax
+            const bool prime = !is_small_radix(pl.radix[s]);
+            const int jmax = prime ? n_s : (f2 > 1 ? ms1 / f2 : ms1);  // butterfly positions j < jmax (prime stage: exponents j2 * k < n_s)
             const int nh = (jmax + FFT_TW_STAGE_LO - 1) / FFT_TW_STAGE_LO;
             pl.tw_off[s] = off;
             pl.tw_nh[s] = nh;
+            if (prime)
+                {
+                    // W_{n_s}^t two-level, then W_P^t for t < P
+                    if (tab)
+                        {
+                            for (int l = 0; l < FFT_TW_STAGE_LO; l++)
+                                {
+                                    const double a = -TWO_PI * (double)l / (double)n_s;
+                                    tab->push_back(make_float2((float)std::cos(a), (float)std::sin(a)));
+                                }
+                            for (int q = 0; q < nh; q++)
+                                {
+                                    const double a = -TWO_PI * (double)(q * FFT_TW_STAGE_LO) / (double)n_s;
+                                    tab->push_back(make_float2((float)std::cos(a), (float)std::sin(a)));
+                                }
+                            for (int t = 0; t < pl.radix[s]; t++)
+                                {
+                                    const double a = -TWO_PI * (double)t / (double)pl.radix[s];
+                                    tab->push_back(make_float2((float)std::cos(a), (float)std::sin(a)));
+                                }
+                        }
+                    off += FFT_TW_STAGE_LO + nh + pl.radix[s];
+                    n_s /= pl.radix[s];
+                    continue;
+                }
             const int n_tab = f2 > 1 ? 2 : 1;
             if (tab)
                 for (int t = 0; t < n_tab; t++)
@@ -179,14 +217,17 @@ int make_plan(gb200_acq* h, int max_smem)
         {
             if (N % r) continue;
             pl.m = N / r;
-            if (!factor_235(pl.m, radix, fuse)) return set_error(GB200_EINVAL, "fft_size %d has a prime factor other than 2, 3, 5, 7", N);
+            if (!factor_235(pl.m, radix, fuse)) return set_error(GB200_EINVAL, "fft_size %d: prime factors above 61 (or a single small factor next to them) are not supported", N);
             // the inverse kernel fuses the code product into its first stage and the search into its last: two stages at least
             if (radix.size() < 2) factor_235(pl.m, radix, false);
             if (radix.size() == 1 && radix[0] == 4) radix = {2, 2};
             if (radix.size() < 2) continue;
             pl.n_stages = (int)radix.size();
             for (int s = 0; s < pl.n_stages; s++) pl.radix[s] = radix[s];
-            const size_t bytes = ((size_t)pl.m + build_stage_tables(pl, nullptr)) * sizeof(float2);
+            pl.y_len = 0;
+            for (int s = 0; s < pl.n_stages; s++)
+                if (!is_small_radix(pl.radix[s])) pl.y_len = pl.m;
+            const size_t bytes = ((size_t)pl.m + pl.y_len + build_stage_tables(pl, nullptr)) * sizeof(float2);
             if (bytes <= (size_t)max_smem)
                 {
                     g = r;
@@ -225,7 +266,8 @@ int make_plan(gb200_acq* h, int max_smem)
             finish_plan(pf);
             h->tw_stage_f.clear();
             build_stage_tables(pf, &h->tw_stage_f);
-            h->smem_f = ((size_t)pf.m + pf.n_tw) * sizeof(float2);
+            pf.y_len = pl.y_len ? pf.m : 0;
+            h->smem_f = ((size_t)pf.m + pf.y_len + pf.n_tw) * sizeof(float2);
             h->threads_f = std::min(256, plan_threads(pf));  // 128 registers per thread: two CTAs per SM
             h->split_fwd = true;
         }

@@ -42,6 +42,7 @@ struct FftPlan
     unsigned inv_nblk[FFT_MAX_STAGES];  // ceil(2^32 / (m / n_s)) for that mapping
     int n_tw;      // entries of the stage-table block
     int perm_rl;   // full radix of the last DIF stage: code spectra are stored [q][butterfly] within a block (see acq_inv_kernel)
+    int y_len;     // m when the plan has a prime-radix stage (11 <= P <= 61: out-of-place, needs a second block in shared memory), else 0
 };
 
 constexpr int FFT_TW_STAGE_LO = 32;
@@ -405,6 +406,55 @@ __device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, u
     if (!Post::on) __syncthreads();
 }
 
+// Stage of prime radix P (11 ... 61), for transform lengths such as 6625 = 5^3 * 53 (6.625 MS/s front-ends) or
+// 5456 = 2^4 * 11 * 31: the DFT by definition, one thread per OUTPUT point, out of place through y (the second block in
+// shared memory), O(P) per point.  T: two-level table of W_{n_s}^t for t < n_s, followed by W_P^t, t < P.  Never the first
+// or the last stage of a plan (the hooks live in the small-radix stages), so it takes none.
+template <bool INV>
+__device__ __noinline__ void fft_smem_stage_prime(float2* x, float2* y, int m_blk, int n_s, int P, const float2* T, int nh)
+{
+    const int ms = n_s / P;
+    const float2* Cf = T + FFT_TW_STAGE_LO + nh;  // W_P^t
+    if (INV)
+        {
+            // DIT: conj twiddle W_{n_s}^{j2 k} on the inputs first
+            for (int id = threadIdx.x; id < m_blk; id += blockDim.x)
+                {
+                    const int r = id % n_s, k = r / ms, j2 = r - k * ms;
+                    if (k > 0 && j2 > 0) x[id] = cmulc(x[id], fft_stage_twiddle(T, j2 * k));
+                }
+            __syncthreads();
+        }
+    for (int id = threadIdx.x; id < m_blk; id += blockDim.x)
+        {
+            const int blk = id / n_s, r = id - blk * n_s, q = r / ms, j2 = r - q * ms;
+            const float2* p = x + blk * n_s + j2;
+            float2 acc = p[0];
+            int e = 0;  // (q * k) mod P
+            for (int k = 1; k < P; k++)
+                {
+                    e += q;
+                    if (e >= P) e -= P;
+                    const float2 c = Cf[e];
+                    const float2 v = p[k * ms];
+                    acc = cadd(acc, INV ? cmulc(v, c) : cmul(v, c));
+                }
+            y[id] = acc;
+        }
+    __syncthreads();
+    for (int id = threadIdx.x; id < m_blk; id += blockDim.x)
+        {
+            float2 v = y[id];
+            if (!INV)
+                {
+                    const int r = id % n_s, q = r / ms, j2 = r - q * ms;
+                    if (q > 0 && j2 > 0) v = cmul(v, fft_stage_twiddle(T, j2 * q));  // DIF: twiddle W_{n_s}^{j2 q} on the outputs
+                }
+            x[id] = v;
+        }
+    __syncthreads();
+}
+
 template <bool INV, class Pre, class Post>
 __device__ __forceinline__ void fft_smem_stage_any(const FftPlan& pl, int s, float2* x, int n_s, const float2* sT, const Pre& pre, Post& post)
 {
@@ -421,7 +471,8 @@ __device__ __forceinline__ void fft_smem_stage_any(const FftPlan& pl, int s, flo
         case 9: fft_smem_stage2<3, 3, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
         case 16: fft_smem_stage2<4, 4, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
         case 25: fft_smem_stage2<5, 5, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
-        default: fft_smem_stage<7, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, pre, post); break;
+        case 7: fft_smem_stage<7, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, pre, post); break;
+        default: fft_smem_stage_prime<INV>(x, x + pl.m, m_blk, n_s, pl.radix[s], T, nh); break;  // prime radix 11 ... 61 (never with hooks)
         }
 }
 

@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_fwd_kernel(FftPlan pl, co
 {
     extern __shared__ __align__(16) float2 sm[];
     float2* x = sm;
-    float2* sT = sm + pl.m;
+    float2* sT = sm + pl.m + pl.y_len;
     fft_load_tables(pl, gT, sT);
     const size_t base = (size_t)blockIdx.y * pl.n + (size_t)blockIdx.x * pl.m;
     if (SRC_IQ)

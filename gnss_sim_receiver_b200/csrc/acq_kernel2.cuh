@@ -17,7 +17,7 @@ __global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_inv_kernel(AcqParams p, c
     extern __shared__ __align__(16) float2 sm[];
     const FftPlan& pl = p.plan;
     float2* x = sm;
-    float2* sT = sm + pl.m;
+    float2* sT = sm + pl.m + pl.y_len;
     const int bin = blockIdx.y, si = blockIdx.z;
     const size_t blk_off = (size_t)blockIdx.x * pl.m;
     const float2* xs = X + (size_t)bin * pl.n + blk_off;

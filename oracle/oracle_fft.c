@@ -1,7 +1,7 @@
 /* TEST INFRASTRUCTURE — NOT PRODUCT CODE.  See oracle.h.
- * Unnormalised complex DFT, any length whose prime factors are in {2,3,5,7}
- * (every d_fft_size the reference's configurations produce: 4000, 16000,
- * 20000, 25000, 32000, 100000 ...).  Stand-in for FFTW3f reached through
+ * Unnormalised complex DFT, any length whose prime factors are <= 61
+ * (the d_fft_size of the reference's configurations: 4000, 16000, 20000,
+ * 25000, 32000, 100000 ... and 6625 = 5^3 * 53, 5456 = 2^4 * 11 * 31 ...).  Stand-in for FFTW3f reached through
  * gr::fft::fft_complex_fwd/rev (src/algorithms/libs/gnss_sdr_fft.h:27-61;
  * call sites pcps_acquisition.cc:113-114,206,647,653) which is not part of
  * the reference tree.  Stockham autosort, twiddles from a float64 table. */
@@ -20,6 +20,8 @@ static int factorize(int n, int* radix)
     while (n % 3 == 0) { radix[nf++] = 3; n /= 3; }
     while (n % 5 == 0) { radix[nf++] = 5; n /= 5; }
     while (n % 7 == 0) { radix[nf++] = 7; n /= 7; }
+    for (int p = 11; p <= 61; p += 2)
+        while (n % p == 0) { radix[nf++] = p; n /= p; }
     return n == 1 ? nf : -1;
 }
 
@@ -76,7 +78,7 @@ static const void* twiddles(int n, int inverse, int is_double)
                 for (int j = 0; j < m; j++)                                                        \
                     {                                                                              \
                         const int k = j % ns;                                                      \
-                        T vr[7], vi[7];                                                            \
+                        T vr[64], vi[64];                                                            \
                         for (int r = 0; r < R; r++)                                                \
                             {                                                                      \
                                 const T xr = a[2 * (j + r * m)], xi = a[2 * (j + r * m) + 1];      \

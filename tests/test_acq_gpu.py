@@ -24,7 +24,8 @@ def _engine(**kw):
     return AcquisitionEngine(**kw)
 
 
-@pytest.mark.parametrize("n", [8, 20, 60, 1400, 4000, 16000, 20000, 25000, 32000, 50000, 100000, 200000])
+@pytest.mark.parametrize("n", [8, 20, 60, 1400, 4000, 16000, 20000, 25000, 32000, 50000, 100000, 200000,
+                               6625, 5456, 2600, 4092, 13250, 3312, 2650])  # second row: prime factors 11 ... 53 (generic prime-radix stage)
 def test_fft_hook_vs_numpy(n):
     rng = np.random.default_rng(n)
     x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
@@ -75,7 +76,7 @@ def _check(r, ro, present, thr=None, stat_tol=1e-3):
         assert (r.test_statistics > thr) == (ro.test_statistics > thr)
 
 
-@pytest.mark.parametrize("fs,dmax,dstep", [(4e6, 10000, 250), (25e6, 5000, 250)])
+@pytest.mark.parametrize("fs,dmax,dstep", [(4e6, 10000, 250), (25e6, 5000, 250), (6.625e6, 5000, 250)])  # 6625 = 5^3 * 53
 def test_gps_l1_cfar_vs_oracle(fs, dmax, dstep):
     """C1 / C3 shape: GPS L1 C/A, one code period, +-dmax in dstep bins, CFAR statistic (pfa threshold)."""
     prns = list(range(1, 9))
