@@ -67,6 +67,7 @@ bool is_small_radix(int r) { return r == 2 || r == 3 || r == 4 || r == 5 || r ==
 bool factor_235(int n, std::vector<int>& radix, bool fuse)
 {
     radix.clear();
+    const int n_in = n;
     int c2 = 0, c3 = 0, c5 = 0, c7 = 0;
     while (n % 2 == 0) { c2++; n /= 2; }
     while (n % 3 == 0) { c3++; n /= 3; }
@@ -94,7 +95,7 @@ bool factor_235(int n, std::vector<int>& radix, bool fuse)
     if (!primes.empty())
         {
             // the first and the last stage carry the hooks of the inverse kernel: the prime stages go in between
-            if (radix.size() < 2) return false;
+            if (radix.size() < 2) return fuse ? factor_235(n_in, radix, false) : false;  // 16 -> 4 * 4 makes room
             radix.insert(radix.begin() + 1, primes.begin(), primes.end());
         }
     return (int)radix.size() <= FFT_MAX_STAGES;
