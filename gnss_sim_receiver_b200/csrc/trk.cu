@@ -112,7 +112,7 @@ cudaError_t launch_run_one(gb200_trk* h)
     const size_t smem = (size_t)TRK2_THREADS * R * EB + (size_t)(R + 2) * TRK2_THREADS * sizeof(float2) + (size_t)G * TRK2_TAB * sizeof(float2);
     cudaError_t e = cudaFuncSetAttribute(trk_run_kernel<T, IQ, CH, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    trk_run_kernel<T, IQ, CH, G><<<h->last_groups, TRK2_THREADS, smem, h->stream>>>(h->d_cmds, h->d_groups, reinterpret_cast<const unsigned char*>(h->d_ring), h->d_out);
+    trk_run_kernel<T, IQ, CH, G><<<h->last_groups, TRK2_THREADS, smem, h->stream>>>(h->d_cmds, h->last_G == 1 ? nullptr : h->d_groups, reinterpret_cast<const unsigned char*>(h->d_ring), h->d_out);
     count_launch();
     return cudaGetLastError();
 }

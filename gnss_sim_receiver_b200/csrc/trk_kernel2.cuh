@@ -113,8 +113,27 @@ __global__ void __launch_bounds__(TRK2_THREADS) trk_run_kernel(const TrkDevCmd* 
     __shared__ Trk2Cmd<T> s_cmd[G];
     __shared__ float s_red[TRK2_THREADS / 32][2 * T];
 
-    const TrkGroup& grp = groups[blockIdx.x];
+    // groups == nullptr: one command per CTA (the default plan) — the group is derived here instead of being built on the
+    // host and copied (64 bytes per command)
+    __shared__ TrkGroup s_grp;
     const int tid = threadIdx.x;
+    if (tid == 0)
+        {
+            if (groups)
+                s_grp = groups[blockIdx.x];
+            else
+                {
+                    const TrkDevCmd& c = cmds[blockIdx.x];
+                    const long long ws = (long long)((static_cast<const unsigned char*>(c.iq) - ring) / EB);
+                    s_grp.tile0 = ws & ~7LL;
+                    s_grp.n_tiles = (int)((ws + c.n - s_grp.tile0 + TILE - 1) / TILE);
+                    s_grp.n_cmds = 1;
+                    s_grp.cmd[0] = (int)blockIdx.x;
+                    s_grp.ws[0] = ws;
+                }
+        }
+    __syncthreads();
+    const TrkGroup& grp = s_grp;
     const int n_tiles = grp.n_tiles;
     const int n_g = grp.n_cmds;
 
