@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(TRK2_THREADS) trk_run_kernel(const TrkDevCmd* 
     extern __shared__ __align__(128) unsigned char smem[];
     const uint4* s_rows = reinterpret_cast<const uint4*>(smem);
     float2* s_prefix = reinterpret_cast<float2*>(smem + TILE_BYTES);  // [R + 2][128]
-    float2* s_tab = s_prefix + (R + 2) * TRK2_THREADS;               // [G][TRK2_TAB] (c[j], c[j+1])
+    float2* s_tab = s_prefix + (R + 2) * TRK2_THREADS;               // [G][TRK2_TAB] (c[j] - c[j+1], c[j+1])
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ Trk2Cmd<T> s_cmd[G];
     __shared__ float s_red[TRK2_THREADS / 32][2 * T];
@@ -199,7 +199,8 @@ __global__ void __launch_bounds__(TRK2_THREADS) trk_run_kernel(const TrkDevCmd* 
                                     for (int j = tid; j < TRK2_TAB; j += TRK2_THREADS)
                                         {
                                             const int k1 = (k + 1 == L) ? 0 : k + 1;
-                                            s_tab[g * TRK2_TAB + j] = make_float2(__ldg(c.code + k), __ldg(c.code + k1));
+                                            const float ck = __ldg(c.code + k), ck1 = __ldg(c.code + k1);
+                                            s_tab[g * TRK2_TAB + j] = make_float2(ck - ck1, ck1);  // (c[j] - c[j+1], c[j+1]): the tap loop needs exactly these
                                             k += adv;
                                             if (k >= L) k -= L;
                                         }
@@ -234,8 +235,8 @@ __global__ void __launch_bounds__(TRK2_THREADS) trk_run_kernel(const TrkDevCmd* 
                                     {
                                         const int i = ch * SPC + j;
                                         if (!FULL && (nr + i < 0 || nr + i >= n)) x[j] = make_float2(0.0f, 0.0f);
-                                        P.x += x[j].x * ph.x - x[j].y * ph.y;
-                                        P.y += x[j].x * ph.y + x[j].y * ph.x;
+                                        P.x = fmaf(x[j].x, ph.x, fmaf(-x[j].y, ph.y, P.x));  // 4 FFMA: the product is never formed on its own
+                                        P.y = fmaf(x[j].x, ph.y, fmaf(x[j].y, ph.x, P.y));
                                         const float pr = ph.x * inc.x - ph.y * inc.y;
                                         ph.y = ph.x * inc.y + ph.y * inc.x;
                                         ph.x = pr;
@@ -270,9 +271,8 @@ __global__ void __launch_bounds__(TRK2_THREADS) trk_run_kernel(const TrkDevCmd* 
                             const int kb = __float_as_int(kqm) + (__float_as_int(mq) > __float_as_int(m0) ? 0 : 1);
                             const float2 cc = tab[__float_as_int(m0) - tab_bias];
                             const float2 Pk = s_prefix[(kb - MAGICBITS) * TRK2_THREADS + tid];
-                            const float d = cc.x - cc.y;
-                            acc_re[g][t] += cc.y * P.x + d * Pk.x;
-                            acc_im[g][t] += cc.y * P.y + d * Pk.y;
+                            acc_re[g][t] = fmaf(cc.y, P.x, fmaf(cc.x, Pk.x, acc_re[g][t]));  // c[j+1] * S + (c[j] - c[j+1]) * P[k]
+                            acc_im[g][t] = fmaf(cc.y, P.y, fmaf(cc.x, Pk.y, acc_im[g][t]));
                         }
                 }
             __syncthreads();  // the tile and the code windows are free again
