@@ -118,7 +118,7 @@ class TrackingBank:
         self._h = _vp()
         check(self._lib.gb200h_bank_create(conf_text.encode(), role.encode(), n_channels, max_engine_channels, C.byref(self._h)))
         self.n = n_channels
-        self._rec = np.zeros(max(4 * n_channels, 64), dtype=REC_DTYPE)
+        self._rec = np.zeros(1 << 15, dtype=REC_DTYPE)
 
     def close(self):
         if self._h:

@@ -303,7 +303,8 @@ int gb200h_bank_step(gb200h_bank* b, gb200h_trk_record* records, int max_records
         {
             b->outs.clear();
             b->bank->step(&b->outs);
-            const int n = std::min<int>(static_cast<int>(b->outs.size()), max_records);
+            if (static_cast<int>(b->outs.size()) > max_records) throw std::runtime_error("gb200h_bank_step: " + std::to_string(b->outs.size()) + " records do not fit the caller's buffer");
+            const int n = static_cast<int>(b->outs.size());
             for (int i = 0; i < n; i++) to_record(b->outs[i].channel, b->outs[i].synchro, &records[i]);
             return n;
         }
@@ -545,7 +546,8 @@ int gb200h_rx_push(gb200h_rx* r, const void* iq, int64_t n_samples, gb200h_trk_r
         {
             r->outs.clear();
             r->mgr->push(iq, n_samples, &r->outs);
-            const int n = std::min<int>(static_cast<int>(r->outs.size()), max_records);
+            if (static_cast<int>(r->outs.size()) > max_records) throw std::runtime_error("gb200h_rx_push: " + std::to_string(r->outs.size()) + " records do not fit the caller's buffer");
+            const int n = static_cast<int>(r->outs.size());
             for (int i = 0; i < n; i++) to_record(r->outs[i].channel, r->outs[i].synchro, &records[i]);
             return n;
         }

@@ -113,7 +113,12 @@ void* ref_loop_new(const RefLoopParams* params, const float* tracking_code, cons
     k->dll = Tracking_loop_filter(static_cast<float>(p.code_period), p.dll_bw, p.dll_order, false);
     k->pll.set_params(p.fll_bw, p.pll_bw, p.pll_order);
     k->mc.init(2 * p.vector_length, k->n_taps);
-    if (p.track_pilot) k->mc_data.init(2 * p.vector_length, 1);
+    k->mc.set_high_dynamics_resampler(false);  // :536 with Tracking_XX.high_dyn=false (the class default is true)
+    if (p.track_pilot)
+        {
+            k->mc_data.init(2 * p.vector_length, 1);
+            k->mc_data.set_high_dynamics_resampler(false);  // :530
+        }
     k->cn0_s.set_alpha(p.cn0_smoother_alpha);
     k->cn0_s.set_samples_for_initialization(p.cn0_smoother_samples / static_cast<int>(p.code_period * 1000.0));
     k->lock_s.set_alpha(p.lock_smoother_alpha);

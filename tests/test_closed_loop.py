@@ -191,3 +191,116 @@ def test_thread_per_block_form_matches_the_lock_step_bank():
     assert b.launches < a.launches * 4  # requests of concurrent channels share launches
     a.close()
     b.close()
+
+
+# ------------------------------------------------------------------------------------------------ Galileo E1, pilot + data
+E1_SECONDS = float(os.environ.get("GB200_LOOP_SECONDS_E1", "12"))
+E1_CS25 = "0011100000001010110110010"  # E1-C secondary code
+
+CONF_E1 = """
+GNSS-SDR.internal_fs_sps=4000000
+Tracking_1B.implementation=Galileo_E1_DLL_PLL_VEML_Tracking_B200
+Tracking_1B.item_type=gr_complex
+Tracking_1B.track_pilot=true
+Tracking_1B.pll_bw_hz=15.0
+Tracking_1B.dll_bw_hz=0.75
+Tracking_1B.pll_bw_narrow_hz=5.0
+Tracking_1B.dll_bw_narrow_hz=0.2
+Tracking_1B.early_late_space_chips=0.25
+Tracking_1B.very_early_late_space_chips=0.5
+Tracking_1B.early_late_space_narrow_chips=0.15
+Tracking_1B.very_early_late_space_narrow_chips=0.5
+Tracking_1B.extend_correlation_symbols=1
+Tracking_1B.pull_in_time_s=1
+Tracking_1B.cn0_samples=20
+Tracking_1B.cn0_min=25
+Tracking_1B.max_lock_fail=50
+Tracking_1B.max_carrier_lock_fail=5000
+Tracking_1B.carrier_lock_th=0.5
+"""
+
+
+def e1_code(sig, prn):
+    buf = np.zeros(8184, dtype=np.float32)
+    O.ref().ref_galileo_e1_code_gen_sinboc11_float(buf.ctypes.data_as(O.C.c_void_p), 8184, sig, int(prn))
+    return buf
+
+
+def e1_scenario(nsat, seed=21):
+    """E1 open service: data component E1-B (250 symbols/s) minus pilot E1-C with its 25-chip secondary code, equal power."""
+    rng = np.random.default_rng(seed)
+    prns = rng.choice(np.arange(1, 31), nsat, replace=False)
+    sc = dict(prn=prns, doppler=rng.uniform(-3000, 3000, nsat), delay=rng.uniform(0, 8184, nsat), phase=rng.uniform(0, 2 * np.pi, nsat),
+              cn0=rng.uniform(42, 48, nsat), acq_err=rng.uniform(-10, 10, nsat))
+    sc["data_code"] = np.stack([e1_code(b"1B", p) for p in prns])
+    sc["pilot_code"] = np.stack([e1_code(b"1C", p) for p in prns])
+    sec = np.array([1 if c == "0" else -1 for c in E1_CS25], dtype=np.int8)
+    bits = rng.choice(np.array([-1, 1], dtype=np.int8), (nsat, 3000))
+    # the generator sums independent components: rows 0..nsat-1 = data, nsat..2nsat-1 = pilot (sign folded into the table)
+    sc["gen_codes"] = np.concatenate([sc["data_code"], -sc["pilot_code"]])
+    sc["gen_bits"] = np.concatenate([bits, np.tile(sec, (nsat, 120))])
+    f_entry = 2.046e6 * (1 + sc["doppler"] / 1575.42e6)  # table entries per second (2 per chip)
+    sc["acq_delay"] = np.mod(sc["delay"] / f_entry * FS, FS * 0.004)
+    return sc
+
+
+def e1_chunks(sc, seconds):
+    two = lambda a: np.concatenate([a, a])
+    n_total = int(seconds * FS)
+    for first in range(0, n_total, CHUNK):
+        n = min(CHUNK, n_total - first)
+        yield first, O.gen_if(n, first, FS, sc["gen_codes"], two(sc["doppler"]), two(sc["delay"]), two(sc["phase"]), two(sc["cn0"]) - 3.0103,
+                              nav_bits=sc["gen_bits"], periods_per_bit=1, f_chip=2.046e6, seed=78)
+
+
+def e1_ref_params():
+    p = ref_params(0)
+    p.code_period, p.chip_rate = 0.004, 1.023e6
+    p.pll_bw, p.dll_bw, p.fll_bw, p.pll_bw_narrow, p.dll_bw_narrow = 15.0, 0.75, 35.0, 5.0, 0.2
+    p.el, p.vel, p.el_narrow, p.vel_narrow = 0.25, 0.5, 0.15, 0.5
+    p.vector_length, p.veml, p.secondary, p.track_pilot, p.symbols_per_bit, p.samples_per_chip, p.code_length_chips = 16000, 1, 1, 1, 1, 2, 4092
+    p.correlation_length_ms = 4
+    p.secondary_code_length, p.data_secondary_code_length = 25, 0
+    p.secondary_code = E1_CS25.encode()
+    return p
+
+
+@pytest.mark.gpu
+@needs_ref
+def test_closed_loop_galileo_e1_pilot_vs_reference_objects():
+    """C2 shape: Galileo E1, VEML (5 taps) on the pilot with secondary-code lock, one-tap data correlator for the symbols —
+    the product's bank against loops made of the reference's own objects, on the same stream."""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    nsat = 4
+    sc = e1_scenario(nsat)
+    bank = H.TrackingBank(CONF_E1, "Tracking_1B", nsat)
+    loops = []
+    for k in range(nsat):
+        bank.set_codes(k, sc["pilot_code"][k], sc["data_code"][k])
+        bank.start(k, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+        loops.append(O.RefLoop(e1_ref_params(), sc["pilot_code"][k], sc["data_code"][k], int(sc["prn"][k]), float(sc["acq_delay"][k]),
+                               float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0))
+    got, ref = [[] for _ in range(nsat)], [[] for _ in range(nsat)]
+    for _, x in e1_chunks(sc, E1_SECONDS):
+        bank.push(x)
+        r = bank.step()
+        for k in range(nsat):
+            got[k].append(r[r["channel"] == k])
+            ref[k].append(loops[k].feed(x))
+    for k in range(nsat):
+        g, r = np.concatenate(got[k]), np.concatenate(ref[k])
+        gs, rs = bank.channel_state(k), loops[k].state()
+        assert rs["state"] == 4, (k, rs)
+        assert gs["state"] == 4, (k, gs)
+        assert len(g) == len(r) and len(g) > 500, (k, len(g), len(r))
+        d_cnt = np.abs(g["tracking_sample_counter"].astype(np.int64) - r["tracking_sample_counter"].astype(np.int64))
+        assert d_cnt.max() <= 1, (k, d_cnt.max())
+        # telemetry symbols come from the DATA component's prompt: identical signs
+        assert np.array_equal(np.sign(g["prompt_i"]), np.sign(r["prompt_i"])), k
+        half = len(g) // 2
+        assert np.max(np.abs(g["cn0_db_hz"][half:] - r["cn0_db_hz"][half:])) < 0.1, k
+        assert np.sqrt(np.mean((g["carrier_doppler_hz"][half:] - r["carrier_doppler_hz"][half:]) ** 2)) < 0.5, k
+        assert abs(np.mean(g["carrier_doppler_hz"][half:]) - sc["doppler"][k]) < 2.0
+    for lp in loops:
+        lp.close()
+    bank.close()
