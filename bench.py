@@ -33,8 +33,8 @@ FLOP_PER_CH_SAMPLE = 12 + 4 * N_TAPS  # wipe-off 6 + phasor advan
 METRIC = "tracked channel-Msps/s (11 taps)"
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernels at this workload, from the ncu --set full
 # captures committed under profiles/ (r01_trk_v3_details / r01_acq_v3_details); a profiler figure, not measured by this script
-TRK_NCU_DRAM_BYTES = 45648128 + 60416   # trk_run_kernel<11,CF32,9,1>, 10240 commands: code tables + IQ ring + commands
-ACQ_NCU_DRAM_BYTES = 23111680 + 18688   # acq_inv_kernel<0>, 2560 cells: X and the code spectra stay in L2
+TRK_NCU_DRAM_BYTES = 44993024 + 61952   # trk_run_kernel<11,CF32,9,1>, 10240 commands: code tables + IQ ring + commands
+ACQ_NCU_DRAM_BYTES = 22503168 + 0       # acq_inv_kernel<0>, 2560 cells: X and the code spectra stay in L2
 
 
 def peaks():
