@@ -19,6 +19,12 @@ class TrkConfig(C.Structure):
                 ("ring_samples", C.c_int64), ("max_block", C.c_int32), ("max_cmds", C.c_int32)]
 
 
+class IngestFormat(C.Structure):
+    """gb200_ingest_format (include/gnss_b200.h)"""
+    _fields_ = [("kind", C.c_int32), ("sample_type", C.c_int32), ("item_size", C.c_int32), ("big_endian_items", C.c_int32),
+                ("big_endian_bytes", C.c_int32)]
+
+
 class TrkCmd(C.Structure):
     _fields_ = [("ch", C.c_int32), ("n_samples", C.c_int32), ("n_taps", C.c_int32), ("flags", C.c_int32),
                 ("sample_offset", C.c_uint64),
@@ -53,6 +59,8 @@ SYMBOLS = {
     "gb200_trk_push_iq_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_uint64)]),
     "gb200_trk_skip": (C.c_int, [_vp, C.c_int64]),
     "gb200_trk_write_iq": (C.c_int, [_vp, C.c_uint64, _vp, C.c_int64]),
+    "gb200_trk_push_raw": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.POINTER(C.c_uint64), C.POINTER(C.c_int64)]),
+    "gb200_trk_read_iq": (C.c_int, [_vp, C.c_uint64, _vp, C.c_int64]),
     "gb200_trk_head": (C.c_uint64, [_vp]),
     "gb200_trk_correlate": (C.c_int, [_vp, _vp, C.c_int, _vp]),
     "gb200_trk_enqueue": (C.c_int, [_vp, _vp, C.c_int]),

@@ -59,6 +59,7 @@ SYMBOLS = {
     "gb200h_bank_set_codes": (_i, [_vp, _i, _vp, _vp, _i]),
     "gb200h_bank_start": (_i, [_vp, _i, C.c_uint, _d, _d, C.c_uint64, C.c_uint64]),
     "gb200h_bank_push": (_i, [_vp, _vp, C.c_int64]),
+    "gb200h_bank_push_raw": (C.c_int64, [_vp, _vp, C.c_int64, _i, _i, _i, _i, _i]),
     "gb200h_bank_step": (_i, [_vp, _vp, _i]),
     "gb200h_bank_channel_state": (_i, [_vp, _i, _vp]),
     "gb200h_bank_launches": (C.c_uint64, [_vp]),
@@ -143,6 +144,10 @@ class TrackingBank:
         iq = np.ascontiguousarray(iq)
         n = iq.size if np.iscomplexobj(iq) else iq.size // 2
         check(self._lib.gb200h_bank_push(self._h, iq.ctypes.data, n))
+
+    def push_raw(self, raw, kind, sample_type=0, item_size=1, big_endian_items=False, big_endian_bytes=False):
+        raw = np.ascontiguousarray(raw)
+        return check(self._lib.gb200h_bank_push_raw(self._h, raw.ctypes.data, raw.nbytes, kind, sample_type, item_size, int(big_endian_items), int(big_endian_bytes)))
 
     def step(self):
         n = check(self._lib.gb200h_bank_step(self._h, self._rec.ctypes.data, len(self._rec)))

@@ -1,6 +1,7 @@
 // Tracking multicorrelator engine: C ABI (include/gnss_b200.h) over trk_kernel.cuh.
 #include "trk_kernel2.cuh"
 #include "trk_kernel3.cuh"
+#include "ingest_kernel.cuh"
 #include "host_pool.h"
 #include <chrono>
 #include <mutex>
@@ -46,6 +47,8 @@ struct gb200_trk
     size_t last_smem{0};
     int sm_count{148};
     int max_smem{0};
+    unsigned char* d_raw{nullptr};  // staging of raw ingest bytes (gb200_trk_push_raw)
+    size_t raw_bytes{0};
 };
 
 namespace
@@ -244,6 +247,7 @@ int gb200_trk_destroy(gb200_trk* h)
     cudaSetDevice(h->cfg.device);
     cudaStreamSynchronize(h->stream);
     cudaFree(h->d_ring);
+    cudaFree(h->d_raw);
     cudaFree(h->d_codes);
     cudaFreeHost(h->h_cmds);
     cudaFree(h->d_cmds);
@@ -346,6 +350,8 @@ int gb200_trk_write_iq(gb200_trk* h, uint64_t abs_index, const void* iq_host, in
 
 uint64_t gb200_trk_head(const gb200_trk* h) { return h ? h->head : 0; }
 
+
 }  // extern "C"
 
+#include "ingest.inc"
 #include "trk_submit.inc"

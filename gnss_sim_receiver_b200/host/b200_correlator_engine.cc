@@ -95,6 +95,14 @@ uint64_t B200CorrelatorEngine::push(const void* iq, int64_t n)
     return first;
 }
 
+uint64_t B200CorrelatorEngine::push_raw(const void* raw, int64_t n_bytes, const gb200_ingest_format& fmt, int64_t* n_samples)
+{
+    std::lock_guard<std::mutex> lk(mu_);
+    uint64_t first = 0;
+    if (gb200_trk_push_raw(h_, raw, n_bytes, &fmt, &first, n_samples) != GB200_OK) fail("gb200_trk_push_raw");
+    return first;
+}
+
 uint64_t B200CorrelatorEngine::head() const
 {
     std::lock_guard<std::mutex> lk(mu_);

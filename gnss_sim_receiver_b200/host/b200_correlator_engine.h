@@ -54,6 +54,9 @@ public:
 
     // Append samples to the ring; returns the absolute index of the first one.
     uint64_t push(const void* iq, int64_t n_samples);
+    // raw file items (File_Signal_Source item types, 2-bit packed): converted to the ring type on the device (gb200_trk_push_raw);
+    // *n_samples receives how many samples the bytes held
+    uint64_t push_raw(const void* raw, int64_t n_bytes, const gb200_ingest_format& fmt, int64_t* n_samples);
     // Make sure the ring holds stream samples [abs_index, abs_index + n): uploads only the part beyond the ring's head.
     // `iq` points at the sample with absolute index abs_index.  Returns false when abs_index is older than the ring.
     bool ensure(uint64_t abs_index, const void* iq, int64_t n_samples);

@@ -297,6 +297,19 @@ int gb200h_bank_push(gb200h_bank* b, const void* iq, int64_t n_samples)
         }
 }
 
+int64_t gb200h_bank_push_raw(gb200h_bank* b, const void* raw, int64_t n_bytes, int kind, int sample_type, int item_size, int big_endian_items, int big_endian_bytes)
+{
+    try
+        {
+            const gb200_ingest_format fmt{kind, sample_type, item_size, big_endian_items, big_endian_bytes};
+            return b->bank->push_raw(raw, n_bytes, fmt);
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
 int gb200h_bank_step(gb200h_bank* b, gb200h_trk_record* records, int max_records)
 {
     try

@@ -53,6 +53,8 @@ void gb200h_bank_destroy(gb200h_bank* b);
 int gb200h_bank_set_codes(gb200h_bank* b, int ch, const float* tracking_code, const float* data_code, int n_entries);
 int gb200h_bank_start(gb200h_bank* b, int ch, unsigned prn, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t nitems_read);
 int gb200h_bank_push(gb200h_bank* b, const void* iq, int64_t n_samples);
+/* raw file items (gb200_ingest_format fields), converted on the device; returns the number of samples appended or < 0 */
+int64_t gb200h_bank_push_raw(gb200h_bank* b, const void* raw, int64_t n_bytes, int kind, int sample_type, int item_size, int big_endian_items, int big_endian_bytes);
 /* runs rounds until no channel can advance; returns the number of records written (at most max_records) */
 int gb200h_bank_step(gb200h_bank* b, gb200h_trk_record* records, int max_records);
 /* v[0..7] = state, carrier_doppler_hz, cn0_db_hz, carrier_lock_test, code_freq_chips, rem_code_phase_samples, nitems_read, current_prn_length */

@@ -24,6 +24,12 @@ public:
     void start_tracking(int i, uint64_t nitems_read);
     // append stream samples (engine's iq_dtype) to the device ring
     void push(const void* iq, int64_t n_samples) { engine_->push(iq, n_samples); }
+    int64_t push_raw(const void* raw, int64_t n_bytes, const gb200_ingest_format& fmt)
+    {
+        int64_t n = 0;
+        engine_->push_raw(raw, n_bytes, fmt, &n);
+        return n;
+    }
     // Run rounds until no channel can advance.  Every produced Gnss_Synchro is appended to `out` with its channel index.
     // Returns the number of kernel launches.
     struct Output

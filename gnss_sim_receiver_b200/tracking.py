@@ -9,7 +9,10 @@ import ctypes as C
 import numpy as np
 
 from . import _capi
-from ._capi import GB200_MAX_TAPS, IQ_CF32, IQ_CS16, IQ_CS8, TrkCmd, TrkConfig, check
+from ._capi import GB200_MAX_TAPS, IQ_CF32, IQ_CS16, IQ_CS8, IngestFormat, TrkCmd, TrkConfig, check
+
+SRC_CF32, SRC_CS16, SRC_CS8, SRC_S16, SRC_S8, SRC_2BIT = range(6)  # GB200_SRC_*
+TWOBIT_REAL, TWOBIT_IQ, TWOBIT_QI = range(3)  # GB200_2BIT_*
 
 _CMD_DTYPE = np.dtype([("ch", "<i4"), ("n_samples", "<i4"), ("n_taps", "<i4"), ("flags", "<i4"), ("sample_offset", "<u8"),
                        ("rem_carrier_phase_rad", "<f4"), ("phase_step_rad", "<f4"), ("phase_rate_step_rad", "<f4"),
@@ -65,6 +68,22 @@ class TrackingEngine:
         first = C.c_uint64()
         check(self._lib.gb200_trk_push_iq(self._h, iq.ctypes.data, n, C.byref(first)))
         return first.value
+
+    # File_Signal_Source item types / Two_Bit_Packed_File_Signal_Source: raw bytes cross PCIe, converted on the device
+    def push_raw(self, raw, kind, sample_type=0, item_size=1, big_endian_items=False, big_endian_bytes=False):
+        """Append the samples held in `raw` (any contiguous numpy array, taken as bytes).  Returns (first_index, n_samples)."""
+        raw = np.ascontiguousarray(raw)
+        fmt = IngestFormat(int(kind), int(sample_type), int(item_size), int(bool(big_endian_items)), int(bool(big_endian_bytes)))
+        first, n = C.c_uint64(), C.c_int64()
+        check(self._lib.gb200_trk_push_raw(self._h, raw.ctypes.data, raw.nbytes, C.byref(fmt), C.byref(first), C.byref(n)))
+        return first.value, n.value
+
+    def read_iq(self, abs_index, n_samples):
+        """Samples [abs_index, abs_index + n_samples) of the ring, in the ring's own item type (complex64 or (n, 2) integers)."""
+        np_t, eb = _IQ_NP[self.iq_dtype]
+        out = np.empty(n_samples, np.complex64) if self.iq_dtype == IQ_CF32 else np.empty((n_samples, 2), np_t)
+        check(self._lib.gb200_trk_read_iq(self._h, abs_index, out.ctypes.data, n_samples))
+        return out
 
     def push_iq_device(self, dev_ptr, n_samples):
         first = C.c_uint64()

@@ -125,6 +125,35 @@ int gb200_trk_write_iq(gb200_trk* h, uint64_t abs_index, const void* iq_host, in
 /* absolute index one past the newest sample */
 uint64_t gb200_trk_head(const gb200_trk* h);
 
+/* ---- raw-sample ingest: the item types of the reference's file sources, converted on the device ----
+ * File_Signal_Source item types (src/algorithms/signal_source/adapters/file_signal_source.cc, file_source_base.cc:
+ * "gr_complex", "ishort", "ibyte", "short", "byte") and the 2-bit packed stream of Two_Bit_Packed_File_Signal_Source
+ * (adapters/two_bit_packed_file_signal_source.cc:33-36,79-91; gnuradio_blocks/unpack_2bit_samples.cc:121-208). */
+#define GB200_SRC_CF32 0 /* gr_complex                                        */
+#define GB200_SRC_CS16 1 /* ishort: interleaved I,Q int16 (Ishort_To_Complex)  */
+#define GB200_SRC_CS8 2  /* ibyte: interleaved I,Q int8 (Ibyte_To_Complex)     */
+#define GB200_SRC_S16 3  /* short: real int16, Q = 0                           */
+#define GB200_SRC_S8 4   /* byte: real int8, Q = 0                             */
+#define GB200_SRC_2BIT 5 /* four 2-bit samples per byte, values -3,-1,+1,+3    */
+#define GB200_2BIT_REAL 0 /* sample_type=real: four real samples per byte      */
+#define GB200_2BIT_IQ 1   /* sample_type=iq: two complex samples per byte      */
+#define GB200_2BIT_QI 2   /* sample_type=qi: same with reverse_interleaving    */
+typedef struct gb200_ingest_format
+{
+    int32_t kind;             /* GB200_SRC_* */
+    int32_t sample_type;      /* GB200_SRC_2BIT only: GB200_2BIT_* (two_bit_packed_file_signal_source.cc:79-91) */
+    int32_t item_size;        /* GB200_SRC_2BIT only: bytes per file item, 1 2 4 or 8 (:55-77 byte/short/int/long) */
+    int32_t big_endian_items; /* GB200_SRC_2BIT only: the bytes of an item are stored most significant first (:34) */
+    int32_t big_endian_bytes; /* GB200_SRC_2BIT only: the first sample sits in the top bits of a byte (:35) */
+} gb200_ingest_format;
+/* Appends the samples held in n_bytes of raw host data to the ring, converting to cfg.iq_dtype in a kernel (the raw bytes
+ * are what crosses PCIe).  Integer sources convert without scaling like the reference's adapters; a source wider than the
+ * ring type is refused (GB200_EINVAL).  *first_index / *n_samples (may be NULL) receive the absolute index of the first
+ * appended sample and how many were appended. */
+int gb200_trk_push_raw(gb200_trk* h, const void* raw_host, int64_t n_bytes, const gb200_ingest_format* fmt, uint64_t* first_index, int64_t* n_samples);
+/* Read back samples [abs_index, abs_index + n_samples) of the ring in cfg.iq_dtype (diagnostics and tests). */
+int gb200_trk_read_iq(gb200_trk* h, uint64_t abs_index, void* iq_host, int64_t n_samples);
+
 /* Carrier_wipeoff_multicorrelator_resampler() for n_cmds commands:
  * out[i * GB200_MAX_TAPS + t] = correlator output of command i, tap t (d_corr_out).
  * Blocking: copies the commands in, launches, copies the results back. */

@@ -112,6 +112,12 @@ int orc_acq_statistic(const orc_acq_conf* c, const float* grid, int num_dwells, 
 float orc_acq_threshold(const orc_acq_conf* c, float pfa);
 int orc_acq_neff(const orc_acq_conf* c);
 
+/* ---- raw-sample conversions in front of the paths (oracle_ingest.c) ---- */
+/* unpack_2bit_samples::work — unpack_2bit_samples.cc:121-208; out receives 4 * nbytes values in {-3,-1,1,3} */
+void orc_unpack_2bit(const int8_t* in, int64_t nbytes, int item_size, int big_endian_items, int big_endian_bytes, int reverse_interleaving, int8_t* out);
+/* integer / float items -> interleaved (re, im) floats, no scaling; kind = GB200_SRC_* 0..4 */
+void orc_items_to_complex(const void* in, int64_t n_samples, int kind, float* out);
+
 #ifdef __cplusplus
 }
 #endif

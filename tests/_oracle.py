@@ -309,3 +309,27 @@ class RefLoop:
         if self._h:
             self._r.ref_loop_free(self._h)
             self._h = None
+
+
+def unpack_2bit(raw, item_size=1, big_endian_items=False, big_endian_bytes=False, reverse_interleaving=False):
+    """unpack_2bit_samples::work on a byte array -> int8 array of 4 values per byte."""
+    raw = np.ascontiguousarray(raw).view(np.int8).ravel()
+    out = np.empty(4 * raw.size, np.int8)
+    f = orc().orc_unpack_2bit
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    f(raw.ctypes.data, raw.size, item_size, int(big_endian_items), int(big_endian_bytes), int(reverse_interleaving), out.ctypes.data)
+    return out
+
+
+def items_to_complex(raw, kind):
+    """File item types -> complex64 (GB200_SRC_* 0..4: gr_complex, ishort, ibyte, short, byte), no scaling."""
+    raw = np.ascontiguousarray(raw)
+    per = {0: 8, 1: 4, 2: 2, 3: 2, 4: 1}[kind]
+    n = raw.nbytes // per
+    out = np.empty(n, np.complex64)
+    f = orc().orc_items_to_complex
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
+    f(raw.ctypes.data, n, kind, out.ctypes.data)
+    return out

@@ -248,3 +248,46 @@ def test_acquisition_dump_file(tmp_path):
     assert float(m["doppler_step_narrow"][0, 0]) == 125.0 and float(m["doppler_grid_narrow_min"][0, 0]) == 500.0
     assert abs(float(m["test_statistic"][0, 0]) - s.test_statistics) <= 1e-6 * s.test_statistics
     a.close()
+
+
+def test_two_bit_packed_stream_tracks_like_its_unpacked_bytes():
+    """Two_Bit_Packed_File_Signal_Source shape (sample_type=iq): the packed bytes are unpacked on the device into an ibyte ring;
+    the tracking records are identical to those of a bank fed the host-unpacked ibyte stream (same ring contents)."""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    from gnss_sim_receiver_b200 import tracking as T
+    prn, doppler, delay, cn0 = 9, 1480.0, 1203.7, 48.0
+    codes = np.stack([O.gps_l1_ca_code(prn)])
+    n = int(5 * FS)
+    bits = np.ones((1, 3000), dtype=np.int8)
+    bits[0, ::2] = -1
+    for b in range(0, 3000, 50):
+        bits[0, b:b + 8] = np.array([1, -1, -1, -1, 1, -1, 1, 1], dtype=np.int8)
+    x = O.gen_if(n, 0, FS, codes, [doppler], [delay], [0.4], [cn0], nav_bits=bits, seed=33)
+    # 2-bit quantiser: sign + magnitude against one sigma; field value s in {-2,-1,0,1} -> level 2 s + 1
+    sigma = np.std(x.real)
+    def field(v):
+        lvl = np.where(np.abs(v) > sigma, 3, 1) * np.where(v < 0, -1, 1)
+        return (((lvl - 1) // 2) & 3).astype(np.uint8)
+    fi, fq = field(x.real), field(x.imag)
+    packed = (fi[0::2] | (fq[0::2] << 2) | (fi[1::2] << 4) | (fq[1::2] << 6)).astype(np.uint8)
+    unpacked = O.unpack_2bit(packed)  # int8 I,Q,I,Q...
+    conf = CONF.format(item="gr_complex", pfa=0.01, dwells=1).replace("Tracking_1C.item_type=gr_complex", "Tracking_1C.item_type=ibyte")
+    delay_samples = delay / 1.023e6 * FS  # code start, like the acquisition tests above
+    outs = []
+    for packed_input in (False, True):
+        bank = H.TrackingBank(conf, "Tracking_1C", 1)
+        bank.start(0, prn, delay_samples, doppler + 30.0, 0, 0)
+        recs = []
+        for first in range(0, n, 400000):
+            m = min(400000, n - first)
+            if packed_input:
+                assert bank.push_raw(packed[first // 2:(first + m) // 2], T.SRC_2BIT, T.TWOBIT_IQ) == m
+            else:
+                bank.push(unpacked[2 * first:2 * (first + m)])
+            recs.append(bank.step())
+        outs.append((np.concatenate(recs), bank.channel_state(0)))
+        bank.close()
+    (ra, sa), (rb, sb) = outs
+    assert len(ra) > 50 and sa["state"] == 4 and abs(sa["carrier_doppler_hz"] - doppler) < 5.0, sa
+    assert ra.tobytes() == rb.tobytes()
+    assert sa == sb
