@@ -26,6 +26,18 @@ class AcqStatus(C.Structure):
                 ("state", C.c_int32), ("active", C.c_int32), ("last_event", C.c_int32), ("indext", C.c_uint32), ("doppler_index", C.c_int32)]
 
 
+class Synchro(C.Structure):
+    """gb200h_synchro: every field of the GnssSynchro message (docs/protobuf/gnss_synchro.proto of the reference)"""
+    _fields_ = [("system", C.c_char), ("signal", C.c_char * 3), ("prn", C.c_uint32), ("channel_id", C.c_int32),
+                ("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double), ("acq_samplestamp_samples", C.c_uint64),
+                ("acq_doppler_step", C.c_uint32), ("flag_valid_acquisition", C.c_int32), ("fs", C.c_int64),
+                ("prompt_i", C.c_double), ("prompt_q", C.c_double), ("cn0_db_hz", C.c_double), ("carrier_doppler_hz", C.c_double),
+                ("carrier_phase_rads", C.c_double), ("code_phase_samples", C.c_double), ("tracking_sample_counter", C.c_uint64),
+                ("flag_valid_symbol_output", C.c_int32), ("correlation_length_ms", C.c_int32), ("flag_valid_word", C.c_int32),
+                ("tow_at_current_symbol_ms", C.c_uint32), ("pseudorange_m", C.c_double), ("rx_time", C.c_double),
+                ("flag_valid_pseudorange", C.c_int32), ("flag_pll_180_deg_phase_locked", C.c_int32), ("interp_tow_ms", C.c_double)]
+
+
 REC_DTYPE = np.dtype([("channel", "<i4"), ("prn", "<u4"), ("valid", "<i4"), ("correlation_length_ms", "<i4"), ("prompt_i", "<f8"), ("prompt_q", "<f8"),
                       ("cn0_db_hz", "<f8"), ("carrier_doppler_hz", "<f8"), ("carrier_phase_rads", "<f8"), ("code_phase_samples", "<f8"),
                       ("tracking_sample_counter", "<u8")])
@@ -76,6 +88,12 @@ SYMBOLS = {
     "gb200h_rx_channel_info": (_i, [_vp, _i, _vp]),
     "gb200h_rx_sweeps": (C.c_uint64, [_vp]),
     "gb200h_rx_threshold": (_f, [_vp]),
+    "gb200h_synchro_serialize": (_i, [_vp, _i, _vp, _i]),
+    "gb200h_monitor_create": (_i, [_s, _s, _i, C.POINTER(_vp)]),
+    "gb200h_monitor_destroy": (None, [_vp]),
+    "gb200h_monitor_enabled": (_i, [_vp]),
+    "gb200h_monitor_write": (C.c_int64, [_vp, _i, _vp, _i]),
+    "gb200h_bank_monitor_datagrams": (C.c_int64, [_vp]),
 }
 
 _LIB = None
@@ -148,6 +166,10 @@ class TrackingBank:
     def push_raw(self, raw, kind, sample_type=0, item_size=1, big_endian_items=False, big_endian_bytes=False):
         raw = np.ascontiguousarray(raw)
         return check(self._lib.gb200h_bank_push_raw(self._h, raw.ctypes.data, raw.nbytes, kind, sample_type, item_size, int(big_endian_items), int(big_endian_bytes)))
+
+    @property
+    def monitor_datagrams(self):
+        return self._lib.gb200h_bank_monitor_datagrams(self._h)
 
     def step(self):
         n = check(self._lib.gb200h_bank_step(self._h, self._rec.ctypes.data, len(self._rec)))
@@ -244,3 +266,44 @@ class ChannelManager:
     @property
     def threshold(self):
         return self._lib.gb200h_rx_threshold(self._h)
+
+
+def _synchro_array(items):
+    arr = (Synchro * len(items))()
+    for a, d in zip(arr, items):
+        for k, v in d.items():
+            setattr(a, k, v.encode() if isinstance(v, str) else v)
+    return arr
+
+
+def serialize_synchros(items):
+    """Serdes_Gnss_Synchro::createProtobuffer on a list of dicts keyed by the proto field names -> bytes."""
+    arr = _synchro_array(items)
+    buf = C.create_string_buffer(512 * max(1, len(items)))
+    n = check(lib().gb200h_synchro_serialize(arr, len(items), buf, len(buf)))
+    return buf.raw[:n]
+
+
+class SynchroMonitor:
+    """gnss_synchro_monitor + Gnss_Synchro_Udp_Sink: decimated protobuf datagrams to the configured clients."""
+
+    def __init__(self, conf_text, role, n_channels):
+        self._lib = lib()
+        self._h = _vp()
+        check(self._lib.gb200h_monitor_create(conf_text.encode(), role.encode(), n_channels, C.byref(self._h)))
+
+    @property
+    def enabled(self):
+        return bool(self._lib.gb200h_monitor_enabled(self._h))
+
+    def write(self, channel, items):
+        arr = _synchro_array(items)
+        return check(self._lib.gb200h_monitor_write(self._h, channel, arr, len(items)))
+
+    def close(self):
+        if self._h:
+            self._lib.gb200h_monitor_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        self.close()

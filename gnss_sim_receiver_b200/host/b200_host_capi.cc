@@ -1,4 +1,5 @@
 #include "b200_host_capi.h"
+#include "b200_synchro_monitor.h"
 #include "b200_adapters.h"
 #include "b200_channel_manager.h"
 #include "b200_mat_writer.h"
@@ -183,6 +184,7 @@ struct gb200h_bank
     std::unique_ptr<B200TrackingBank> bank;
     std::vector<std::unique_ptr<Gnss_Synchro>> synchros;
     std::vector<B200TrackingBank::Output> outs;
+    std::unique_ptr<B200SynchroMonitor> monitor;  // TrackingMonitor.* of the bank's configuration
 };
 
 namespace
@@ -236,6 +238,7 @@ int gb200h_bank_create(const char* conf_text, const char* role, int n_channels, 
                     blk->set_channel(static_cast<uint32_t>(i));
                     b->bank->add_channel(std::move(blk));
                 }
+            b->monitor = std::make_unique<B200SynchroMonitor>(&b->cfg, "TrackingMonitor", n_channels);
             *out = b.release();
             return 0;
         }
@@ -319,6 +322,8 @@ int gb200h_bank_step(gb200h_bank* b, gb200h_trk_record* records, int max_records
             if (static_cast<int>(b->outs.size()) > max_records) throw std::runtime_error("gb200h_bank_step: " + std::to_string(b->outs.size()) + " records do not fit the caller's buffer");
             const int n = static_cast<int>(b->outs.size());
             for (int i = 0; i < n; i++) to_record(b->outs[i].channel, b->outs[i].synchro, &records[i]);
+            if (b->monitor->enabled())
+                for (int i = 0; i < n; i++) b->monitor->write(b->outs[i].channel, &b->outs[i].synchro, 1);
             return n;
         }
     catch (const std::exception& e)
@@ -589,5 +594,100 @@ int gb200h_rx_channel_info(gb200h_rx* r, int ch, double* v)
 
 uint64_t gb200h_rx_sweeps(gb200h_rx* r) { return r->mgr->sweeps(); }
 float gb200h_rx_threshold(gb200h_rx* r) { return r->mgr->threshold(); }
+
+// ---- Gnss_Synchro monitor stream
+struct gb200h_monitor
+{
+    B200Configuration cfg;
+    std::unique_ptr<B200SynchroMonitor> mon;
+};
+
+namespace
+{
+Gnss_Synchro from_c(const gb200h_synchro& v)
+{
+    Gnss_Synchro s;
+    s.System = v.system;
+    std::memcpy(s.Signal, v.signal, 3);
+    s.PRN = v.prn;
+    s.Channel_ID = v.channel_id;
+    s.Acq_delay_samples = v.acq_delay_samples;
+    s.Acq_doppler_hz = v.acq_doppler_hz;
+    s.Acq_samplestamp_samples = v.acq_samplestamp_samples;
+    s.Acq_doppler_step = v.acq_doppler_step;
+    s.Flag_valid_acquisition = v.flag_valid_acquisition != 0;
+    s.fs = v.fs;
+    s.Prompt_I = v.prompt_i;
+    s.Prompt_Q = v.prompt_q;
+    s.CN0_dB_hz = v.cn0_db_hz;
+    s.Carrier_Doppler_hz = v.carrier_doppler_hz;
+    s.Carrier_phase_rads = v.carrier_phase_rads;
+    s.Code_phase_samples = v.code_phase_samples;
+    s.Tracking_sample_counter = v.tracking_sample_counter;
+    s.Flag_valid_symbol_output = v.flag_valid_symbol_output != 0;
+    s.correlation_length_ms = v.correlation_length_ms;
+    s.Flag_valid_word = v.flag_valid_word != 0;
+    s.TOW_at_current_symbol_ms = v.tow_at_current_symbol_ms;
+    s.Pseudorange_m = v.pseudorange_m;
+    s.RX_time = v.rx_time;
+    s.Flag_valid_pseudorange = v.flag_valid_pseudorange != 0;
+    s.Flag_PLL_180_deg_phase_locked = v.flag_pll_180_deg_phase_locked != 0;
+    s.interp_TOW_ms = v.interp_tow_ms;
+    return s;
+}
+}  // namespace
+
+int gb200h_synchro_serialize(const gb200h_synchro* items, int n, char* buf, int cap)
+{
+    try
+        {
+            std::vector<Gnss_Synchro> v;
+            for (int i = 0; i < n; i++) v.push_back(from_c(items[i]));
+            const std::string data = create_protobuffer(v);
+            if (static_cast<int>(data.size()) > cap) throw std::runtime_error("gb200h_synchro_serialize: buffer too small");
+            std::memcpy(buf, data.data(), data.size());
+            return static_cast<int>(data.size());
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int gb200h_monitor_create(const char* conf_text, const char* role, int n_channels, gb200h_monitor** out)
+{
+    try
+        {
+            auto m = std::make_unique<gb200h_monitor>();
+            m->cfg.load_string(conf_text);
+            m->mon = std::make_unique<B200SynchroMonitor>(&m->cfg, role, n_channels);
+            *out = m.release();
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+void gb200h_monitor_destroy(gb200h_monitor* m) { delete m; }
+int gb200h_monitor_enabled(gb200h_monitor* m) { return m && m->mon->enabled() ? 1 : 0; }
+
+int64_t gb200h_monitor_write(gb200h_monitor* m, int channel, const gb200h_synchro* items, int n)
+{
+    try
+        {
+            std::vector<Gnss_Synchro> v;
+            for (int i = 0; i < n; i++) v.push_back(from_c(items[i]));
+            m->mon->write(channel, v.data(), n);
+            return static_cast<int64_t>(m->mon->datagrams());
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int64_t gb200h_bank_monitor_datagrams(gb200h_bank* b) { return b && b->monitor ? static_cast<int64_t>(b->monitor->datagrams()) : 0; }
 
 }  // extern "C"

@@ -98,6 +98,38 @@ int gb200h_rx_channel_info(gb200h_rx* r, int ch, double* v);
 uint64_t gb200h_rx_sweeps(gb200h_rx* r);
 float gb200h_rx_threshold(gb200h_rx* r);
 
+/* ---- Gnss_Synchro monitor stream (b200_synchro_monitor.h; serdes_gnss_synchro.h:72-119, gnss_synchro_udp_sink.cc:43-75) ---- */
+typedef struct gb200h_synchro
+{
+    char system;
+    char signal[3];
+    uint32_t prn;
+    int32_t channel_id;
+    double acq_delay_samples, acq_doppler_hz;
+    uint64_t acq_samplestamp_samples;
+    uint32_t acq_doppler_step;
+    int32_t flag_valid_acquisition;
+    int64_t fs;
+    double prompt_i, prompt_q, cn0_db_hz, carrier_doppler_hz, carrier_phase_rads, code_phase_samples;
+    uint64_t tracking_sample_counter;
+    int32_t flag_valid_symbol_output, correlation_length_ms, flag_valid_word;
+    uint32_t tow_at_current_symbol_ms;
+    double pseudorange_m, rx_time;
+    int32_t flag_valid_pseudorange, flag_pll_180_deg_phase_locked;
+    double interp_tow_ms;
+} gb200h_synchro;
+/* Serdes_Gnss_Synchro::createProtobuffer: the `Observables` message of n items; returns its length (<= cap) or < 0 */
+int gb200h_synchro_serialize(const gb200h_synchro* items, int n, char* buf, int cap);
+typedef struct gb200h_monitor gb200h_monitor;
+/* role: "Monitor", "TrackingMonitor", "AcquisitionMonitor" (gnss_flowgraph.cc:194-262) */
+int gb200h_monitor_create(const char* conf_text, const char* role, int n_channels, gb200h_monitor** out);
+void gb200h_monitor_destroy(gb200h_monitor* m);
+int gb200h_monitor_enabled(gb200h_monitor* m);
+/* one channel's new items; returns the datagrams sent so far or < 0 */
+int64_t gb200h_monitor_write(gb200h_monitor* m, int channel, const gb200h_synchro* items, int n);
+/* datagrams the bank's own TrackingMonitor (TrackingMonitor.enable_monitor=true in the bank's .conf) has sent */
+int64_t gb200h_bank_monitor_datagrams(gb200h_bank* b);
+
 #ifdef __cplusplus
 }
 #endif

@@ -272,6 +272,13 @@ def test_two_bit_packed_stream_tracks_like_its_unpacked_bytes():
     packed = (fi[0::2] | (fq[0::2] << 2) | (fi[1::2] << 4) | (fq[1::2] << 6)).astype(np.uint8)
     unpacked = O.unpack_2bit(packed)  # int8 I,Q,I,Q...
     conf = CONF.format(item="gr_complex", pfa=0.01, dwells=1).replace("Tracking_1C.item_type=gr_complex", "Tracking_1C.item_type=ibyte")
+    # the bank's TrackingMonitor (gnss_flowgraph.cc:241-262) streams every record as a protobuf datagram
+    import socket
+    from test_monitor_cpu import observables_class
+    listener = socket.socket(socket.AF_INET, socket.SOCK_DGRAM)
+    listener.bind(("127.0.0.1", 0))
+    listener.settimeout(2.0)
+    conf += f"TrackingMonitor.enable_monitor=true\nTrackingMonitor.udp_port={listener.getsockname()[1]}\n"
     delay_samples = delay / 1.023e6 * FS  # code start, like the acquisition tests above
     outs = []
     for packed_input in (False, True):
@@ -286,8 +293,15 @@ def test_two_bit_packed_stream_tracks_like_its_unpacked_bytes():
                 bank.push(unpacked[2 * first:2 * (first + m)])
             recs.append(bank.step())
         outs.append((np.concatenate(recs), bank.channel_state(0)))
+        assert bank.monitor_datagrams == len(outs[-1][0])
         bank.close()
     (ra, sa), (rb, sb) = outs
+    first = observables_class()()
+    first.ParseFromString(listener.recv(4096))
+    o = first.observable[0]
+    assert (o.system, o.signal, o.prn, o.tracking_sample_counter) == ("G", "1C", prn, int(ra["tracking_sample_counter"][0]))
+    assert o.prompt_i == ra["prompt_i"][0] and o.cn0_db_hz == ra["cn0_db_hz"][0] and o.fs == int(FS)
+    listener.close()
     assert len(ra) > 50 and sa["state"] == 4 and abs(sa["carrier_doppler_hz"] - doppler) < 5.0, sa
     assert ra.tobytes() == rb.tobytes()
     assert sa == sb
