@@ -66,6 +66,7 @@ SYMBOLS = {
     "gb200h_exponential_smoother_run": (None, [_f, _i, _f, _f, _vp, _vp, _i]),
     "gb200h_gps_l1_ca_code_gen_float": (_i, [_vp, C.c_uint, C.c_uint]),
     "gb200h_gps_l1_ca_code_gen_complex_sampled": (_i, [_vp, _i, C.c_uint, _i, C.c_uint]),
+    "gb200h_code_gen": (_i, [_i, _vp, _s, C.c_uint, _i, C.c_uint, _i, _i]),
     "gb200h_bank_create": (_i, [_s, _s, _i, _i, C.POINTER(_vp)]),
     "gb200h_bank_destroy": (None, [_vp]),
     "gb200h_bank_set_codes": (_i, [_vp, _i, _vp, _vp, _i]),

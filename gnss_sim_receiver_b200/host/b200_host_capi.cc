@@ -173,6 +173,32 @@ int gb200h_gps_l1_ca_code_gen_complex_sampled(float* dest_ri, int n, unsigned pr
         }
 }
 
+// one door for the other signals' generators (a17); what: 0 E1 sinboc11 float(8184), 1 E1 complex sampled, 2 L5I float, 3 L5Q float,
+// 4 L5I complex sampled, 5 L5Q complex sampled, 6 E5a complex primary, 7 E5a complex sampled.  Returns the samples written or < 0.
+int gb200h_code_gen(int what, float* dest, const char* signal_id, unsigned prn, int fs, unsigned chip_shift, int cboc, int secondary)
+{
+    try
+        {
+            auto* c = reinterpret_cast<std::complex<float>*>(dest);
+            switch (what)
+                {
+                case 0: galileo_e1_code_gen_sinboc11_float(dest, signal_id, prn); return 8184;
+                case 1: return galileo_e1_code_gen_complex_sampled(c, signal_id, cboc != 0, prn, fs, chip_shift, secondary != 0);
+                case 2: gps_l5i_code_gen_float(dest, prn); return 10230;
+                case 3: gps_l5q_code_gen_float(dest, prn); return 10230;
+                case 4: return gps_l5i_code_gen_complex_sampled(c, prn, fs);
+                case 5: return gps_l5q_code_gen_complex_sampled(c, prn, fs);
+                case 6: galileo_e5_a_code_gen_complex_primary(c, static_cast<int32_t>(prn), signal_id); return 10230;
+                case 7: return galileo_e5_a_code_gen_complex_sampled(c, prn, signal_id, fs, chip_shift);
+                default: throw std::invalid_argument("gb200h_code_gen: unknown generator");
+                }
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
 }  // extern "C"
 
 // ------------------------------------------------------------------ tracking bank

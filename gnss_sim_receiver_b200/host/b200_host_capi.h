@@ -34,6 +34,8 @@ void gb200h_fll_pll_filter_run(float fll_bw, float pll_bw, int order, float init
 void gb200h_exponential_smoother_run(float alpha, int init_samples, float min_value, float offset, const float* in, float* out, int n);
 int gb200h_gps_l1_ca_code_gen_float(float* dest, unsigned prn, unsigned chip_shift);
 int gb200h_gps_l1_ca_code_gen_complex_sampled(float* dest_ri, int n, unsigned prn, int fs, unsigned chip_shift);
+/* Galileo E1 / GPS L5 / Galileo E5a generators (b200_gnss_codes.h); `what` 0..7, see b200_host_capi.cc; returns samples written */
+int gb200h_code_gen(int what, float* dest, const char* signal_id, unsigned prn, int fs, unsigned chip_shift, int cboc, int secondary);
 
 /* ---- tracking bank: N dll_pll_veml tracking blocks of one signal over one GPU engine */
 typedef struct gb200h_bank gb200h_bank;

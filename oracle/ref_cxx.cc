@@ -129,6 +129,10 @@ void ref_gps_l5i_code_gen_complex_sampled(float* dest_ri, int n, unsigned prn, i
 {
     gps_l5i_code_gen_complex_sampled(own::span<cf>(reinterpret_cast<cf*>(dest_ri), n), prn, fs);
 }
+void ref_gps_l5q_code_gen_complex_sampled(float* dest_ri, int n, unsigned prn, int fs)
+{
+    gps_l5q_code_gen_complex_sampled(own::span<cf>(reinterpret_cast<cf*>(dest_ri), n), prn, fs);
+}
 void ref_galileo_e5_a_code_gen_complex_primary(float* dest_ri, int prn, const char* sig)
 {
     std::array<char, 3> id{{sig[0], sig[1], '\0'}};
