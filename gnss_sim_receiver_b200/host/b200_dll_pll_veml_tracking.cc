@@ -286,7 +286,55 @@ void b200_dll_pll_veml_tracking::start_tracking()
             d_tracking_code.assign(2 * d_code_length_chips, 0.0F);
             gps_l1_ca_code_gen_float(d_tracking_code.data(), d_acquisition_gnss_synchro->PRN, 0);
         }
-    // every other signal: the adapter supplied the tables through set_tracking_code / set_data_code
+    else if (!tracking_code_supplied_)
+        {
+            // dll_pll_veml_tracking.cc:670-722: the other signals' tables, same generators (b200_gnss_codes.h)
+            const uint32_t prn = d_acquisition_gnss_synchro->PRN;
+            const size_t entries = static_cast<size_t>(d_code_samples_per_chip) * d_code_length_chips;
+            if (d_systemName == "GPS" && d_signal_type == "L5")
+                {
+                    d_tracking_code.assign(2 * entries, 0.0F);
+                    if (p.track_pilot)
+                        {
+                            d_data_code.assign(2 * entries, 0.0F);
+                            gps_l5q_code_gen_float(d_tracking_code.data(), prn);
+                            gps_l5i_code_gen_float(d_data_code.data(), prn);
+                        }
+                    else
+                        gps_l5i_code_gen_float(d_tracking_code.data(), prn);
+                }
+            else if (d_systemName == "Galileo" && d_signal_type == "1B")
+                {
+                    d_tracking_code.assign(2 * entries, 0.0F);
+                    if (p.track_pilot)
+                        {
+                            d_data_code.assign(2 * entries, 0.0F);
+                            galileo_e1_code_gen_sinboc11_float(d_tracking_code.data(), "1C", prn);
+                            galileo_e1_code_gen_sinboc11_float(d_data_code.data(), "1B", prn);
+                        }
+                    else
+                        galileo_e1_code_gen_sinboc11_float(d_tracking_code.data(), "1B", prn);
+                }
+            else if (d_systemName == "Galileo" && d_signal_type == "5X")
+                {
+                    std::vector<std::complex<float>> aux(d_code_length_chips);
+                    galileo_e5_a_code_gen_complex_primary(aux.data(), static_cast<int32_t>(prn), "5X");
+                    d_tracking_code.assign(2 * entries, 0.0F);
+                    if (p.track_pilot)
+                        {
+                            d_secondary_code_string = galileo_e5a_q_secondary_code(prn);
+                            d_data_code.assign(2 * entries, 0.0F);
+                            for (size_t i = 0; i < entries; i++)
+                                {
+                                    d_tracking_code[i] = aux[i].imag();
+                                    d_data_code[i] = aux[i].real();
+                                }
+                        }
+                    else
+                        for (size_t i = 0; i < entries; i++) d_tracking_code[i] = aux[i].real();
+                }
+        }
+    // tables supplied through set_tracking_code / set_data_code take precedence (tests, other signals)
     if (p.track_pilot) d_Prompt_Data = gr_complex(0.0, 0.0);
     upload_codes();
     std::fill(d_correlator_outs.begin(), d_correlator_outs.end(), gr_complex(0.0, 0.0));

@@ -5,6 +5,7 @@
 #include <complex>
 #include <cstddef>
 #include <cstdint>
+#include <string>
 namespace gb200h
 {
 // 1023 entries of +-1; throws std::invalid_argument for a PRN outside 1..37
@@ -31,6 +32,9 @@ int gps_l5q_code_gen_complex_sampled(std::complex<float>* dest, uint32_t prn, in
 void galileo_e5_a_code_gen_complex_primary(std::complex<float>* dest, int32_t prn, const char* signal_id);
 // :96-121: resampled to sampling_freq and rotated by chip_shift; returns the number of samples written
 int galileo_e5_a_code_gen_complex_sampled(std::complex<float>* dest, uint32_t prn, const char* signal_id, int32_t sampling_freq, uint32_t chip_shift);
+// GALILEO_E5A_Q_SECONDARY_CODE[prn - 1] (Galileo_E5a.h:3585-3633): the 100-chip E5a-Q secondary code as a '0'/'1' string; the
+// reference's table initialises PRN 1..47 only (rows 48..50 are empty strings there): all '0' is returned for those
+std::string galileo_e5a_q_secondary_code(uint32_t prn);
 // gnss_signal_replica.cc:257-291: dest[i] = from[int(fl(t_out (i + 1)) fs_in + 1) - 1] in fp32, last entry forced to the last one
 void resampler(const float* from, size_t n_from, float* dest, size_t n_dest, float fs_in, float fs_out);
 void resampler(const std::complex<float>* from, size_t n_from, std::complex<float>* dest, size_t n_dest, float fs_in, float fs_out);

@@ -36,7 +36,8 @@ enum Table
     E1B = 0,
     E1C = 1,
     E5AI = 2,
-    E5AQ = 3
+    E5AQ = 3,
+    E5AQ_SECONDARY = 4
 };
 
 struct TableRef
@@ -52,7 +53,7 @@ TableRef table(int which)
     if (std::memcmp(p, "GB2C", 4) != 0) throw std::runtime_error("memory-code table: bad magic");
     std::memcpy(&version, p + 4, 4);
     std::memcpy(&n_tables, p + 8, 4);
-    if (version != 1 || n_tables < 4) throw std::runtime_error("memory-code table: unknown version");
+    if (version != 1 || n_tables < 5) throw std::runtime_error("memory-code table: unknown version");
     const unsigned char* data = p + 12 + 8 * n_tables;
     TableRef r{};
     for (int t = 0; t <= which; t++)
@@ -302,5 +303,14 @@ int galileo_e5_a_code_gen_complex_sampled(std::complex<float>* dest, uint32_t pr
         }
     for (uint32_t i = 0; i < samples_per_code; i++) dest[(i + delay) % samples_per_code] = code[i];
     return static_cast<int>(samples_per_code);
+}
+
+std::string galileo_e5a_q_secondary_code(uint32_t prn)
+{
+    const TableRef t = table(E5AQ_SECONDARY);
+    std::string out(100, '0');
+    if (prn < 1 || prn > t.n_prn) return out;
+    for (uint32_t i = 0; i < 100; i++) out[i] = chip(t, prn, i) < 0 ? '1' : '0';
+    return out;
 }
 }  // namespace gb200h

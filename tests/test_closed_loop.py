@@ -276,7 +276,8 @@ def test_closed_loop_galileo_e1_pilot_vs_reference_objects():
     bank = H.TrackingBank(CONF_E1, "Tracking_1B", nsat)
     loops = []
     for k in range(nsat):
-        bank.set_codes(k, sc["pilot_code"][k], sc["data_code"][k])
+        # no set_codes: start_tracking builds the E1-C / E1-B tables itself (dll_pll_veml_tracking.cc:684-699); the reference loop
+        # gets the reference generator's tables
         bank.start(k, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
         loops.append(O.RefLoop(e1_ref_params(), sc["pilot_code"][k], sc["data_code"][k], int(sc["prn"][k]), float(sc["acq_delay"][k]),
                                float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0))

@@ -32,10 +32,10 @@ def vp(a):
 def test_table_file_shape_and_digest():
     path = os.path.join(HERE, "..", "gnss_sim_receiver_b200", "data", "gnss_memory_codes.bin")
     raw = open(path, "rb").read()
-    assert raw[:4] == b"GB2C" and len(raw) == 12 + 32 + 2 * 50 * 512 + 2 * 50 * 1279
+    assert raw[:4] == b"GB2C" and len(raw) == 12 + 40 + 2 * 50 * 512 + 2 * 50 * 1279 + 47 * 13
     assert hashlib.sha256(raw).hexdigest() == open(os.path.join(HERE, "golden", "gnss_memory_codes.sha256")).read().strip()
     # balanced codes: a memory code has about as many +1 as -1 chips
-    e1b = np.unpackbits(np.frombuffer(raw[44:44 + 50 * 512], np.uint8).reshape(50, 512), axis=1, bitorder="little")[:, :4092]
+    e1b = np.unpackbits(np.frombuffer(raw[52:52 + 50 * 512], np.uint8).reshape(50, 512), axis=1, bitorder="little")[:, :4092]
     assert np.all(np.abs(e1b.mean(axis=1) - 0.5) < 0.03)
     # the library serves exactly these chips
     code, n = gen(0, 8184, b"1B", 11)

@@ -7,7 +7,9 @@ OUTPUT of the reference's own generators compiled under oracle/_ref (dev contain
 (bit = 1 for a chip of -1), PRN 1..50 each.  The file is embedded into libgnss_b200_host.so (b200_gnss_codes.cc, .incbin).
 
 Layout (little-endian): magic "GB2C", u32 version=1, u32 n_tables=4, then per table: u32 n_prn, u32 n_chips, followed
-by the tables in the same order, each PRN padded to whole bytes, chips LSB-first.  Order: E1B, E1C, E5aI, E5aQ.
+by the tables in the same order, each PRN padded to whole bytes, chips LSB-first.  Order: E1B, E1C, E5aI, E5aQ, then the
+E5a-Q secondary codes CS100 (100 chips per PRN, bit = the ICD's binary digit; OS SIS ICD table 20), which no generator
+function of the reference outputs: those strings (47: the reference's array leaves rows 48..50 empty) are read from Galileo_E5a.h:3585-3633 by this script.
 """
 import ctypes as C
 import os
@@ -38,6 +40,12 @@ def main():
         assert set(np.unique(buf)) == {-1.0, 1.0}
         ti[prn - 1], tq[prn - 1] = buf[0::2] < 0, buf[1::2] < 0
     tables += [ti, tq]
+    import re
+    hdr = open("/root/reference/src/core/system_parameters/Galileo_E5a.h").read()
+    body = hdr[hdr.index("GALILEO_E5A_Q_SECONDARY_CODE[GALILEO_E5A_NUMBER_OF_CODES]"):]
+    strings = re.findall(r'"([01]{100})"', body)
+    assert len(strings) == 47  # the reference's table initialises 47 of its 50 rows; the table here holds those 47
+    tables.append(np.array([[int(ch) for ch in st] for st in strings], np.uint8))
     out = os.path.join(os.path.dirname(__file__), "..", "gnss_sim_receiver_b200", "data", "gnss_memory_codes.bin")
     with open(out, "wb") as f:
         f.write(b"GB2C" + struct.pack("<II", 1, len(tables)))
