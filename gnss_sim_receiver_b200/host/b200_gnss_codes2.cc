@@ -4,7 +4,7 @@
 //   * Galileo memory codes (E1-B, E1-C, E5a-I, E5a-Q) are ICD tables, not LFSR outputs: they are read from
 //     data/gnss_memory_codes.bin (one bit per chip, written by tools/make_code_tables.py), embedded below with .incbin;
 //   * GPS L5 codes come from the two 13-stage registers of IS-GPS-705 (XA short-cycled at 8190, XB advanced per PRN).
-// tests/test_codes_cpu.py checks every generator bit-exactly against the reference's (oracle/_ref) for all PRNs.
+// tests/test_codes_cpu.py checks every generator bit-exactly against the reference's own compiled generators for all PRNs.
 #include "b200_gnss_codes.h"
 #include <cmath>
 #include <cstring>
