@@ -51,6 +51,8 @@ SYMBOLS = {
     "gb200_launch_count": (C.c_uint64, []),
     "gb200_device_count": (C.c_int, []),
     "gb200_version": (C.c_char_p, []),
+    "gb200_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
+    "gb200_host_free": (C.c_int, [C.c_void_p]),
     "gb200_trk_create": (C.c_int, [C.POINTER(TrkConfig), C.POINTER(_vp)]),
     "gb200_trk_destroy": (C.c_int, [_vp]),
     "gb200_trk_set_code": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),

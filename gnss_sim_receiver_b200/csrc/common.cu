@@ -47,4 +47,18 @@ int gb200_device_count(void)
     return n;
 }
 const char* gb200_version(void) { return "gnss_b200 0.1 (sm_100a)"; }
+int gb200_host_alloc(void** out, size_t bytes)
+{
+    if (!out || bytes == 0) return gb200::set_error(GB200_EINVAL, "gb200_host_alloc: null argument or zero size");
+    *out = nullptr;
+    if (gb200_device_count() == 0) return gb200::set_error(GB200_ENODEVICE, "no CUDA device (no CPU fallback)");
+    GB_CUDA(cudaHostAlloc(out, bytes, cudaHostAllocPortable));
+    return GB200_OK;
+}
+int gb200_host_free(void* p)
+{
+    if (!p) return GB200_OK;
+    GB_CUDA(cudaFreeHost(p));
+    return GB200_OK;
+}
 }

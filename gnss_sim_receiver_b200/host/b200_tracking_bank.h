@@ -7,6 +7,8 @@
 
 #include "b200_dll_pll_veml_tracking.h"
 #include <memory>
+#include <stdexcept>
+#include <string>
 #include <vector>
 
 namespace gb200h
@@ -49,7 +51,31 @@ private:
     std::shared_ptr<B200CorrelatorEngine> engine_;
     std::vector<Chan> ch_;
     std::vector<gb200_trk_cmd> cmds_;
-    std::vector<gb200_cf32> res_;
+    // correlator outputs of one round in page-locked memory (gb200_host_alloc): the engine DMAs results straight into it
+    struct PinnedTaps
+    {
+        gb200_cf32* p{nullptr};
+        size_t cap{0};
+        PinnedTaps() = default;
+        PinnedTaps(const PinnedTaps&) = delete;
+        PinnedTaps& operator=(const PinnedTaps&) = delete;
+        ~PinnedTaps() { gb200_host_free(p); }
+        void resize(size_t n)
+        {
+            if (n <= cap) return;
+            gb200_host_free(p);
+            p = nullptr;
+            cap = 0;
+            void* q = nullptr;
+            const size_t want = n + n / 2;
+            if (gb200_host_alloc(&q, want * sizeof(gb200_cf32)) != GB200_OK) throw std::runtime_error(std::string("gb200_host_alloc: ") + gb200_last_error());
+            p = static_cast<gb200_cf32*>(q);
+            cap = want;
+        }
+        gb200_cf32* data() { return p; }
+        const gb200_cf32& operator[](size_t i) const { return p[i]; }
+    };
+    PinnedTaps res_;
     std::vector<int> who_, data_idx_;
     std::vector<b200_dll_pll_veml_tracking::Step> steps_;
 };

@@ -29,6 +29,7 @@ class TrackingEngine:
         self._lib = _capi.lib()
         self.cfg = TrkConfig(device, max_channels, max_code_len, iq_dtype, ring_samples, max_block, max_cmds or max_channels)
         self._h = C.c_void_p()
+        self._host_bufs = []
         check(self._lib.gb200_trk_create(C.byref(self.cfg), C.byref(self._h)))
         self.iq_dtype = iq_dtype
         self._cmds = None
@@ -38,6 +39,10 @@ class TrackingEngine:
         if self._h:
             self._lib.gb200_trk_destroy(self._h)
             self._h = C.c_void_p()
+            # (arrays handed out by host_outputs() must not be used after close)
+            for p in self._host_bufs:
+                self._lib.gb200_host_free(p)
+            self._host_bufs = []
 
     def __del__(self):
         try:
@@ -114,9 +119,23 @@ class TrackingEngine:
         return arr
 
     # Carrier_wipeoff_multicorrelator_resampler for a batch of commands: (n_cmds, n_taps) complex64
-    def correlate(self, cmds):
+    def host_outputs(self, n_cmds):
+        """(n_cmds, GB200_MAX_TAPS) complex64 array in page-locked memory (gb200_host_alloc): the caller-owned `corr_out` of
+        Cpu_Multicorrelator_Real_Codes::set_input_output_vectors, kept across calls; results are DMA'd straight into it."""
+        p = C.c_void_p()
+        nbytes = n_cmds * GB200_MAX_TAPS * 8
+        check(self._lib.gb200_host_alloc(C.byref(p), nbytes))
+        buf = (C.c_char * nbytes).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=np.complex64).reshape(n_cmds, GB200_MAX_TAPS)
+        self._host_bufs.append(p)
+        return arr
+
+    def correlate(self, cmds, out=None):
         n = len(cmds)
-        out = np.empty((n, GB200_MAX_TAPS), dtype=np.complex64)
+        if out is None:
+            out = np.empty((n, GB200_MAX_TAPS), dtype=np.complex64)
+        else:
+            assert out.dtype == np.complex64 and out.shape == (n, GB200_MAX_TAPS) and out.flags.c_contiguous
         check(self._lib.gb200_trk_correlate(self._h, cmds, n, out.ctypes.data))
         nt = getattr(cmds, "_n_taps", None) or max(c.n_taps for c in cmds)
         return out[:, :nt]

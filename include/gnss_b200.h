@@ -54,6 +54,12 @@ uint64_t gb200_launch_count(void);
 /* number of visible CUDA devices (0 when there is none; never fails) */
 int gb200_device_count(void);
 const char* gb200_version(void);
+/* Page-locked host memory for buffers the caller keeps across calls (correlator outputs, IQ staging): the place of
+ * volk_gnsssdr_malloc in the reference (src/algorithms/tracking/libs/cpu_multicorrelator_real_codes.cc:44-49, d_correlator_outs in
+ * src/algorithms/tracking/gnuradio_blocks/dll_pll_veml_tracking.cc:520-522).  gb200_trk_correlate / gb200_trk_collect copy device
+ * results straight into an `out` that lives in such memory; any other pointer goes through the engine's own staging buffer. */
+int gb200_host_alloc(void** out, size_t bytes);
+int gb200_host_free(void* p);
 
 /* ======================================================================
  * Tracking multicorrelator engine

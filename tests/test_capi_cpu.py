@@ -51,6 +51,9 @@ def test_no_device_is_a_loud_error_not_a_fallback(capi):
     assert b"no CPU fallback" in lib.gb200_last_error()
     acfg = capi.AcqConfig(0, 0, 4000, 4000, 0, 1, 4, 1, 4, 4000.0, 4e6)
     assert lib.gb200_acq_create(C.byref(acfg), C.byref(h)) == -2
+    p = C.c_void_p()
+    assert lib.gb200_host_alloc(C.byref(p), 4096) == -2 and not p.value
+    assert lib.gb200_host_free(None) == 0
     with pytest.raises(capi.GB200Error):
         from gnss_sim_receiver_b200.tracking import TrackingEngine
         TrackingEngine()

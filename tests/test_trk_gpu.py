@@ -83,6 +83,13 @@ def test_signal_like_input_many_channels():
     eng.enqueue(cmds)
     again = eng.collect()[:, :nt]
     assert np.array_equal(again.view(np.uint32), got.view(np.uint32))
+    # caller-owned page-locked outputs (gb200_host_alloc): results are DMA'd straight into them, same bits
+    pinned = eng.host_outputs(nch)
+    pinned[:] = 0
+    direct = eng.correlate(cmds, out=pinned)
+    assert np.array_equal(np.ascontiguousarray(direct).view(np.uint32), got.view(np.uint32))
+    assert np.array_equal(pinned[:, :nt].view(np.uint32).reshape(nch, -1), np.ascontiguousarray(got).view(np.uint32).reshape(nch, -1))
+    del pinned, direct
     eng.close()
 
 
