@@ -94,6 +94,36 @@ __global__ void __launch_bounds__(256) ingest_2bit_kernel(IngestParams p)
         }
 }
 
+// LabSat 2/3 single-channel payload (labsat23_source.cc:364-433): little-endian int16 words, most significant bits first.
+// BITS = 2: sample k of a word has I = bit 15-2k, Q = bit 14-2k, value 2 b - 1.  BITS = 4: I = (bit 15-4k, bit 13-4k),
+// Q = (bit 14-4k, bit 12-4k) with (hi, lo) 00 -> +1, 01 -> +2, 10 -> -2, 11 -> -1.  One thread per OUTPUT sample: the
+// 8 (4) threads of a word read the same 2 bytes (one L1 line per warp), the ring writes are fully coalesced.
+__device__ __forceinline__ float labsat_level(unsigned hi, unsigned lo) { return hi ? (lo ? -1.0f : -2.0f) : (lo ? 2.0f : 1.0f); }
+
+template <int BITS, int DST>
+__global__ void __launch_bounds__(256) ingest_labsat_kernel(IngestParams p)
+{
+    constexpr int PER_WORD = 16 / (2 * (BITS / 2));  // 8 samples (BITS = 2) or 4 samples (BITS = 4)
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < p.n_units; i += stride)
+        {
+            const unsigned w = reinterpret_cast<const unsigned short*>(p.src)[i / PER_WORD];
+            const int k = (int)(i % PER_WORD);
+            float re, im;
+            if (BITS == 2)
+                {
+                    re = (float)(2 * (int)((w >> (15 - 2 * k)) & 1u) - 1);
+                    im = (float)(2 * (int)((w >> (14 - 2 * k)) & 1u) - 1);
+                }
+            else
+                {
+                    re = labsat_level((w >> (15 - 4 * k)) & 1u, (w >> (13 - 4 * k)) & 1u);
+                    im = labsat_level((w >> (14 - 4 * k)) & 1u, (w >> (12 - 4 * k)) & 1u);
+                }
+            ingest_store<DST>(p, p.abs_start + (unsigned long long)i, re, im);
+        }
+}
+
 // SRC: GB200_SRC_* of a whole-sample format (complex or real integer / float items)
 template <int SRC, int DST>
 __global__ void __launch_bounds__(256) ingest_convert_kernel(IngestParams p)

@@ -11,7 +11,7 @@ import numpy as np
 from . import _capi
 from ._capi import GB200_MAX_TAPS, IQ_CF32, IQ_CS16, IQ_CS8, IngestFormat, TrkCmd, TrkConfig, check
 
-SRC_CF32, SRC_CS16, SRC_CS8, SRC_S16, SRC_S8, SRC_2BIT = range(6)  # GB200_SRC_*
+SRC_CF32, SRC_CS16, SRC_CS8, SRC_S16, SRC_S8, SRC_2BIT, SRC_LABSAT2, SRC_LABSAT4 = range(8)  # GB200_SRC_*
 TWOBIT_REAL, TWOBIT_IQ, TWOBIT_QI = range(3)  # GB200_2BIT_*
 
 _CMD_DTYPE = np.dtype([("ch", "<i4"), ("n_samples", "<i4"), ("n_taps", "<i4"), ("flags", "<i4"), ("sample_offset", "<u8"),

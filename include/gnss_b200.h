@@ -141,6 +141,11 @@ uint64_t gb200_trk_head(const gb200_trk* h);
 #define GB200_SRC_S16 3  /* short: real int16, Q = 0                           */
 #define GB200_SRC_S8 4   /* byte: real int8, Q = 0                             */
 #define GB200_SRC_2BIT 5 /* four 2-bit samples per byte, values -3,-1,+1,+3    */
+#define GB200_SRC_LABSAT2 6 /* LabSat 2/3 single-channel payload, 1-bit I + 1-bit Q: 8 samples per int16 word, +-1  */
+#define GB200_SRC_LABSAT4 7 /* LabSat 2/3 single-channel payload, 2-bit I + 2-bit Q: 4 samples per int16 word, +-1,+-2 */
+/* (labsat23_source::decode_samples_one_channel, src/algorithms/signal_source/gnuradio_blocks/labsat23_source.cc:364-433, fed by
+ * general_work's native int16 reads :960-972,1016-1028; the file header (:141-361) is parsed by the caller, who pushes the
+ * payload bytes that follow it) */
 #define GB200_2BIT_REAL 0 /* sample_type=real: four real samples per byte      */
 #define GB200_2BIT_IQ 1   /* sample_type=iq: two complex samples per byte      */
 #define GB200_2BIT_QI 2   /* sample_type=qi: same with reverse_interleaving    */

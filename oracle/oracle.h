@@ -117,6 +117,8 @@ int orc_acq_neff(const orc_acq_conf* c);
 void orc_unpack_2bit(const int8_t* in, int64_t nbytes, int item_size, int big_endian_items, int big_endian_bytes, int reverse_interleaving, int8_t* out);
 /* integer / float items -> interleaved (re, im) floats, no scaling; kind = GB200_SRC_* 0..4 */
 void orc_items_to_complex(const void* in, int64_t n_samples, int kind, float* out);
+// labsat23_source::decode_samples_one_channel (labsat23_source.cc:364-433) over n_words int16 words, bits = 2 or 4
+void orc_labsat_one_channel(const int16_t* in, int64_t n_words, int bits, float* out);
 
 #ifdef __cplusplus
 }

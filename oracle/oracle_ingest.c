@@ -90,3 +90,40 @@ void orc_items_to_complex(const void* in, int64_t n_samples, int kind, float* ou
             out[2 * i + 1] = im;
         }
 }
+
+// labsat23_source::decode_samples_one_channel (labsat23_source.cc:364-433) over a payload of native int16 words
+// (general_work :960-972 for 2 bits per sample, :1016-1028 for 4): out receives 8 (bits = 2) or 4 (bits = 4) interleaved
+// (re, im) float pairs per word.  Bit k of a word is tested the way std::bitset<16>::operator[] does.
+static int word_bit(int16_t w, int k) { return (int)(((uint16_t)w >> k) & 1u); }
+
+void orc_labsat_one_channel(const int16_t* in, int64_t n_words, int bits, float* out)
+{
+    int64_t o = 0;
+    for (int64_t n = 0; n < n_words; n++)
+        {
+            const int16_t w = in[n];
+            if (bits == 2)
+                for (int i = 0; i < 8; i++)  // :370-376: (b, b') * 2 - (1, 1)
+                    {
+                        out[2 * o] = (float)word_bit(w, 15 - 2 * i) * 2.0f - 1.0f;
+                        out[2 * o + 1] = (float)word_bit(w, 14 - 2 * i) * 2.0f - 1.0f;
+                        o++;
+                    }
+            else
+                for (int i = 0; i < 4; i++)
+                    {
+                        float re, im;
+                        if (word_bit(w, 15 - 4 * i))  // :384-405
+                            re = word_bit(w, 13 - 4 * i) ? -1.0f : -2.0f;
+                        else
+                            re = word_bit(w, 13 - 4 * i) ? 2.0f : 1.0f;
+                        if (word_bit(w, 14 - 4 * i))  // :408-429
+                            im = word_bit(w, 12 - 4 * i) ? -1.0f : -2.0f;
+                        else
+                            im = word_bit(w, 12 - 4 * i) ? 2.0f : 1.0f;
+                        out[2 * o] = re;
+                        out[2 * o + 1] = im;
+                        o++;
+                    }
+        }
+}

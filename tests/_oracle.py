@@ -322,6 +322,17 @@ def unpack_2bit(raw, item_size=1, big_endian_items=False, big_endian_bytes=False
     return out
 
 
+def labsat_one_channel(raw, bits):
+    """labsat23_source::decode_samples_one_channel over a payload of native int16 words -> complex64 (8 or 4 per word)."""
+    w = np.ascontiguousarray(raw).view(np.int16).ravel()
+    out = np.empty(w.size * (8 if bits == 2 else 4), np.complex64)
+    f = orc().orc_labsat_one_channel
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
+    f(w.ctypes.data, w.size, bits, out.ctypes.data)
+    return out
+
+
 def items_to_complex(raw, kind):
     """File item types -> complex64 (GB200_SRC_* 0..4: gr_complex, ishort, ibyte, short, byte), no scaling."""
     raw = np.ascontiguousarray(raw)

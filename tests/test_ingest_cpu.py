@@ -50,3 +50,25 @@ def test_items_to_complex():
     assert np.array_equal(O.items_to_complex(s8, 4), s8.astype(np.complex64))
     c = (rng.standard_normal(16) + 1j * rng.standard_normal(16)).astype(np.complex64)
     assert np.array_equal(O.items_to_complex(c, 0), c)
+
+
+def test_labsat_known_answers():
+    """labsat23_source::decode_samples_one_channel (labsat23_source.cc:364-433), hand-worked words."""
+    # 2 bits per complex sample: 0xB400 = 10 11 01 00 | 00.. : (I,Q) pairs msb first -> (+1,-1) (+1,+1) (-1,+1) (-1,-1) then (-1,-1) x4
+    got = O.labsat_one_channel(np.array([0xB400], np.uint16), 2)
+    assert got.tolist() == [1 - 1j, 1 + 1j, -1 + 1j, -1 - 1j] + [-1 - 1j] * 4
+    # 4 bits per complex sample, nibble = (I_hi, Q_hi, I_lo, Q_lo): 0x0 -> (1,1); 0xF -> (-1,-1); 0xA = 1010 -> I=(1,1)=-1, Q=(0,0)=+1;
+    # 0x6 = 0110 -> I=(0,1)=+2, Q=(1,0)=-2
+    got = O.labsat_one_channel(np.array([0x0FA6], np.uint16), 4)
+    assert got.tolist() == [1 + 1j, -1 - 1j, -1 + 1j, 2 - 2j]
+    # every word, against an independent numpy formulation
+    w = np.arange(65536, dtype=np.uint16).astype(np.int64)
+    two = O.labsat_one_channel(w.astype(np.uint16), 2).reshape(65536, 8)
+    four = O.labsat_one_channel(w.astype(np.uint16), 4).reshape(65536, 4)
+    lvl = np.array([[1.0, 2.0], [-2.0, -1.0]])
+    for k in range(8):
+        assert np.array_equal(two[:, k], (2 * ((w >> (15 - 2 * k)) & 1) - 1) + 1j * (2 * ((w >> (14 - 2 * k)) & 1) - 1))
+    for k in range(4):
+        re = lvl[(w >> (15 - 4 * k)) & 1, (w >> (13 - 4 * k)) & 1]
+        im = lvl[(w >> (14 - 4 * k)) & 1, (w >> (12 - 4 * k)) & 1]
+        assert np.array_equal(four[:, k], (re + 1j * im).astype(np.complex64))

@@ -81,6 +81,29 @@ def test_item_types_bit_exact(ring_dtype):
     eng.close()
 
 
+@pytest.mark.parametrize("ring_dtype", [IQ_CF32, IQ_CS16, IQ_CS8])
+def test_labsat_single_channel_bit_exact(ring_dtype):
+    """LabSat 2/3 single-channel payload (1+1 and 2+2 bits per complex sample), every 16-bit word value, ragged pushes over the wrap."""
+    rng = np.random.default_rng(23 + ring_dtype)
+    eng = T.TrackingEngine(max_channels=2, max_code_len=1023, iq_dtype=ring_dtype, ring_samples=RING, max_block=BLOCK)
+    every = np.arange(65536, dtype=np.uint16)
+    for kind, bits, per in ((T.SRC_LABSAT2, 2, 8), (T.SRC_LABSAT4, 4, 4)):
+        for lo in range(0, 65536, 3000):  # all 65536 words in pushes that fit the ring
+            raw = every[lo:lo + 3000]
+            first, n = eng.push_raw(raw, kind)
+            want = O.labsat_one_channel(raw, bits)
+            assert n == want.size == per * raw.size
+            assert np.array_equal(ring_view(eng, first, n), want), (kind, lo)
+        for _ in range(6):
+            raw = rng.integers(0, 65536, int(rng.integers(1, 3500)), dtype=np.uint16)
+            first, n = eng.push_raw(raw, kind)
+            assert np.array_equal(ring_view(eng, first, n), O.labsat_one_channel(raw, bits)), kind
+    assert eng.head > 2 * RING
+    with pytest.raises(GB200Error):
+        eng.push_raw(np.zeros(3, np.uint8), T.SRC_LABSAT2)  # not whole int16 words
+    eng.close()
+
+
 def test_correlation_over_ingested_window_across_the_wrap():
     """2-bit "iq" stream -> byte ring -> multicorrelator, window straddling the end of the ring (mirror written by the kernel)."""
     rng = np.random.default_rng(8)
