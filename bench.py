@@ -301,13 +301,19 @@ def run_ours(args):
     # ---- e2e: public call with HOST buffers, H2D of the IQ block and D2H of the correlator outputs inside the timed region
     out_bytes = nch * _capi.GB200_MAX_TAPS * 8
     corr_out = eng.host_outputs(nch)  # caller-owned, kept across calls like the reference's d_correlator_outs
+    # the step's commands are written into ONE caller-owned array just before the call, as the loop closure does every
+    # period (dll_pll_veml_tracking.cc:1037-1062 fills the arguments right before do_correlation_step): untimed here, it
+    # only puts the 1.1 MB of commands where a closed loop would have left them (host caches) instead of cold in DRAM
+    step_cmds = type(cmd_sets[0])()
+    step_cmds._n_taps = cmd_sets[0]._n_taps
     e2e_t = 0.0
     for i in range(K + W):
         flush.zero_()
+        C.memmove(step_cmds, cmd_sets[i], C.sizeof(step_cmds))
         barrier(dist) if i == W else torch.cuda.synchronize()
         t0 = time.perf_counter()
         eng.push_iq(host_iq[(2 + i) * N_BLK:(3 + i) * N_BLK])
-        res = eng.correlate(cmd_sets[i], out=corr_out)
+        res = eng.correlate(step_cmds, out=corr_out)
         dt = time.perf_counter() - t0
         if i >= W:
             e2e_t += dt
