@@ -55,8 +55,9 @@ private:
     HostPool()
     {
         int want = (int)std::thread::hardware_concurrency() / 2 - 1;
-        if (const char* e = std::getenv("GB200_HOST_THREADS")) want = std::atoi(e) - 1;
-        want = std::max(0, std::min(want, 7));
+        want = std::min(want, 7);
+        if (const char* e = std::getenv("GB200_HOST_THREADS")) want = std::atoi(e) - 1;  // explicit: up to 32 threads
+        want = std::max(0, std::min(want, 31));
         if (const char* e = std::getenv("GB200_HOST_SPIN_US")) spin_us_ = std::max(0, std::atoi(e));
         for (int i = 0; i < want; i++) threads_.emplace_back([this, i] { loop(i); });
     }
