@@ -161,6 +161,27 @@ cudaError_t launch_run(gb200_trk* h)
         }
 }
 
+// Where the carrier angles of a command are computed: on the device by trk_phase_kernel (default) or with the host's float64
+// atan2 (GB200_HOST_PHASES=1; 50 ns more host time per command).  The two differ by rounding in the last bits of a 64-bit angle.
+constexpr bool kDevicePhasesDefault = true;
+inline bool device_phases()
+{
+    static const bool on = [] {
+        const char* e = getenv("GB200_HOST_PHASES");
+        return e ? std::atoi(e) == 0 : kDevicePhasesDefault;
+    }();
+    return on;
+}
+
+// phasors -> fixed-point angles, in place in d_cmds (trk_phase_kernel); queued behind the command upload on the engine's stream
+cudaError_t upload_phases(gb200_trk* h, int n_cmds)
+{
+    if (!device_phases()) return cudaSuccess;
+    trk_phase_kernel<<<(n_cmds + 255) / 256, 256, 0, h->stream>>>(h->d_cmds, n_cmds);
+    count_launch();
+    return cudaGetLastError();
+}
+
 cudaError_t launch(gb200_trk* h)
 {
     if (h->last_path == 1) return launch_run(h);

@@ -38,6 +38,28 @@ struct TrkDevCmd
     int pad_;
 };
 
+// Carrier angles of a batch of commands, on the device.  The host stores the two fp32-ROUNDED phasors the reference seeds its
+// rotator with (cpu_multicorrelator_real_codes.cc:114-123: (cos phi, -sin phi) and exp(-j*step), computed with the host's
+// cosf/sinf so that their rounding is the reference's) in the 8 bytes of u0 and du; this kernel replaces them in place by their
+// angles as 64-bit fixed-point turns (float64 atan2: an angle error of 1e-16 rad is 1e-12 over a 25 000-sample block).  One
+// thread per command, run once right after the command upload — 50 ns of host libm per command become a few microseconds here.
+__global__ void __launch_bounds__(256) trk_phase_kernel(TrkDevCmd* cmds, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long* slot = &cmds[i].u0;  // u0 and du are adjacent
+#pragma unroll
+    for (int k = 0; k < 2; k++)
+        {
+            const unsigned long long raw = slot[k];
+            const float re = __uint_as_float((unsigned)(raw & 0xffffffffu)), im = __uint_as_float((unsigned)(raw >> 32));
+            const double turns = atan2((double)im, (double)re) * 0.15915494309189533576888376337251;  // 1 / (2 pi)
+            double f = turns - floor(turns);
+            if (f >= 1.0) f = 0.0;
+            slot[k] = __double2ull_rz(f * 9007199254740992.0) << 11;  // 53 significant bits, shifted to the top
+        }
+}
+
 // reference chip index BEFORE the modulo: floor(step*(float)n + shift - rem), every operation rounded to fp32
 // separately (no FMA contraction), volk_gnsssdr_32f_xn_resampler_32f_xn.h:73.
 __device__ __forceinline__ int trk_raw_index(float step, float nf, float shift, float rem)
