@@ -364,7 +364,7 @@ def run_ours(args):
                      "sustained_ms_per_step": sustained_ms},
         "cpu_baseline": cpu, "clocks": clocks, "acq": acq,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_reference(args):
@@ -386,10 +386,29 @@ def run_reference(args):
             "ms_per_step": secs / K * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"C3-shaped tracking: GPS L1 C/A {FS / 1e6:g} MS/s gr_complex, N={N_BLK}/period, {N_TAPS} taps; CPU: one thread per channel on all host cores"},
             "cpu_baseline": cpu, "e2e": {"value": v, "unit": "channel-Msps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
+
+
+_JSON_FD = None
+
+
+def emit(line):
+    """The one JSON line, on the process's ORIGINAL stdout (see main: libraries such as NCCL print banners to fd 1)."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 def main():
+    global _JSON_FD
+    # keep stdout clean for the contract's single JSON line: everything else written to fd 1 during the run (e.g. the
+    # "NCCL version ..." banner of the first communicator) goes to stderr
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
