@@ -83,6 +83,7 @@ SYMBOLS = {
     "gb200_acq_threshold": (C.c_float, [_vp, C.c_float]),
     "gb200_acq_keep_grid": (C.c_int, [_vp, C.c_int]),
     "gb200_acq_read_grid": (C.c_int, [_vp, C.c_int, _vp]),
+    "gb200_acq_read_cells": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp]),
     "gb200_acq_fft": (C.c_int, [_vp, _vp, _vp, C.c_int]),
 }
 

@@ -77,7 +77,10 @@ SYMBOLS = {
     "gb200h_bank_channel_state": (_i, [_vp, _i, _vp]),
     "gb200h_bank_launches": (C.c_uint64, [_vp]),
     "gb200h_bank_run_threaded": (_i, [_vp, _vp, C.c_int64, C.c_uint64, _i, _vp, _i]),
+    "gb200h_engine_probe": (_s, [_s, _s, C.c_uint, _s, C.c_uint]),
     "gb200h_acq_create": (_i, [_s, _s, C.c_uint, C.POINTER(_vp)]),
+    "gb200h_acq_create2": (_i, [_s, _s, C.c_uint, C.c_char, _s, C.POINTER(_vp)]),
+    "gb200h_acq_local_code": (C.c_int64, [_vp, C.c_void_p, C.c_int64]),
     "gb200h_acq_destroy": (None, [_vp]),
     "gb200h_acq_arm": (_i, [_vp, _f]),
     "gb200h_acq_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
@@ -194,12 +197,20 @@ class TrackingBank:
 
 
 class AcquisitionBlock:
-    """One GpsL1CaPcpsAcquisitionB200 adapter + block, driven like Channel/ChannelFsm drive it."""
+    """One B200 acquisition adapter (GPS L1 C/A, Galileo E1, GPS L5I or Galileo E5a, chosen by `<role>.implementation`) + its
+    block, driven like Channel/ChannelFsm drive it.  `system` / `signal` fill the channel's Gnss_Synchro."""
 
-    def __init__(self, conf_text, role, prn):
+    def __init__(self, conf_text, role, prn, system="G", signal="1C"):
         self._lib = lib()
         self._h = _vp()
-        check(self._lib.gb200h_acq_create(conf_text.encode(), role.encode(), prn, C.byref(self._h)))
+        check(self._lib.gb200h_acq_create2(conf_text.encode(), role.encode(), prn, system.encode(), signal.encode(), C.byref(self._h)))
+
+    def local_code(self):
+        """the replica the adapter handed to pcps_acquisition::set_local_code (after arm())"""
+        n = self._lib.gb200h_acq_local_code(self._h, None, 0)
+        out = np.zeros(n, np.complex64)
+        self._lib.gb200h_acq_local_code(self._h, out.ctypes.data, n)
+        return out
 
     def close(self):
         if self._h:

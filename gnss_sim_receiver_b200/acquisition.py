@@ -45,6 +45,18 @@ class AcquisitionEngine:
     def set_wipeoff_mode(self, exact):
         check(self._lib.gb200_acq_set_wipeoff_mode(self._h, int(exact)))
 
+    def set_doppler_bins(self, freqs_hz):
+        """explicit wipe-off frequencies, one per bin (a Doppler tile of a sweep, or the fine grid of a two-step search)"""
+        f = np.ascontiguousarray(freqs_hz, dtype=np.float32)
+        check(self._lib.gb200_acq_set_doppler_bins(self._h, f.ctypes.data_as(C.POINTER(C.c_float)), len(f)))
+
+    def read_cells(self, n_slots):
+        """(vmax, imax, sum) of every (slot, bin) of the last run, each [n_slots, n_bins]"""
+        b = self.num_doppler_bins
+        v, i, s = np.zeros((n_slots, b), np.float32), np.zeros((n_slots, b), np.int32), np.zeros((n_slots, b), np.float32)
+        check(self._lib.gb200_acq_read_cells(self._h, n_slots, v.ctypes.data, i.ctypes.data, s.ctypes.data))
+        return v, i, s
+
     def set_doppler_grid(self, doppler_max, doppler_step, doppler_center=0):
         check(self._lib.gb200_acq_set_doppler_grid(self._h, doppler_max, doppler_step, doppler_center))
 

@@ -237,12 +237,14 @@ struct AcqSink
         // branch-free: samples outside [out_offset, out_offset + neff) add nothing and can never win
         const int i = n - out_offset;
         const bool ok = (unsigned)i < (unsigned)neff;
-        float g = y.x * y.x + y.y * y.y;
+        // volk_32fc_magnitude_squared_32f (pcps_acquisition.cc:659,663): two products and one sum, each rounded to fp32 (no FMA
+        // contraction), so a near-tie between two code phases resolves as it does in the reference's generic kernel
+        float g = __fadd_rn(__fmul_rn(y.x, y.x), __fmul_rn(y.y, y.y));
         if (grid_row)  // uniform
             {
                 if (ok)
                     {
-                        if (accumulate) g = grid_row[i] + g;
+                        if (accumulate) g = __fadd_rn(grid_row[i], g);  // volk_32f_x2_add_32f, :664
                         grid_row[i] = g;
                     }
             }

@@ -124,10 +124,10 @@ __global__ void __launch_bounds__(256) acq_gstage_inv_kernel(AcqParams p, const 
                             const int i = n - p.out_offset;
                             if (i >= 0 && i < p.neff)
                                 {
-                                    float g = acc.x * acc.x + acc.y * acc.y;
+                                    float g = __fadd_rn(__fmul_rn(acc.x, acc.x), __fmul_rn(acc.y, acc.y));  // as AcqSink: no FMA contraction
                                     if (grow)
                                         {
-                                            if (p.dwell_index > 0) g = grow[i] + g;
+                                            if (p.dwell_index > 0) g = __fadd_rn(grow[i], g);
                                             grow[i] = g;
                                         }
                                     sum += g;

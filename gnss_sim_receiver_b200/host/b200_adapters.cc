@@ -67,11 +67,18 @@ void B200DllPllTracking::start_tracking()
     if (!tracking_->tracking_code().empty() && tracking_->code_table_entries() > 0)
         {
             // attach to the GPU engine of the configured device on first use
+            // One engine per (device, item type, input stream).  Channels of different signals on the same stream share it (GPS L1 C/A
+            // and Galileo E1 on an L1 front-end), so it is sized for the longest code period of the band, not for this channel's:
+            // 4 ms (Galileo E1) on the L1 band, 1 ms on the L5 / E5a band.  `<role>.stream_id` overrides the band default.
+            const bool l5_band = std::string(trk_params_.signal) == "L5" || std::string(trk_params_.signal) == "5X";
+            const auto longest_period = static_cast<int64_t>(std::llround(trk_params_.fs_in * (l5_band ? 1e-3 : 4e-3)));
             EngineConfig ec;
             ec.device = trk_params_.device;
             ec.iq_dtype = item_type_iq(trk_params_.item_type);
-            ec.max_block = static_cast<int>(2 * trk_params_.vector_length);
-            ec.ring_samples = std::max<int64_t>(int64_t{1} << 22, 64LL * trk_params_.vector_length);
+            ec.stream_id = trk_params_.stream_id >= 0 ? trk_params_.stream_id : (l5_band ? 1 : 0);
+            ec.max_block = static_cast<int>(2 * std::max<int64_t>(longest_period, trk_params_.vector_length));
+            ec.max_code_len = 10230;  // longest table of the four signals (E1: 8184 entries, L5 / E5a: 10230)
+            ec.ring_samples = std::max<int64_t>(int64_t{1} << 22, 32LL * ec.max_block);
             tracking_->set_engine(B200CorrelatorEngine::instance(ec));
         }
     tracking_->start_tracking();
@@ -102,17 +109,20 @@ void B200DllPllTracking::disconnect(gr::top_block_sptr top_block)
 gr::basic_block_sptr B200DllPllTracking::get_left_block() { return tracking_; }
 gr::basic_block_sptr B200DllPllTracking::get_right_block() { return tracking_; }
 
-// ------------------------------------------------------------------ acquisition (adapters/gps_l1_ca_pcps_acquisition.cc:39-236)
-GpsL1CaPcpsAcquisitionB200::GpsL1CaPcpsAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams)
-    : role_(role), in_streams_(in_streams), out_streams_(out_streams)
+// ------------------------------------------------------------------ acquisition
+// Common constructor body of the four reference adapters (adapters/gps_l1_ca_pcps_acquisition.cc:39-98,
+// galileo_e1_pcps_ambiguous_acquisition.cc:36-98, gps_l5i_pcps_acquisition.cc:36-95, galileo_e5a_pcps_acquisition.cc:36-90)
+B200PcpsAcquisition::B200PcpsAcquisition(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams,
+    const char* implementation, uint32_t ms_per_code, double chip_rate_cps, double opt_acq_fs_sps, double code_length_chips)
+    : configuration_(configuration), role_(role), implementation_(implementation), in_streams_(in_streams), out_streams_(out_streams)
 {
-    acq_parameters_.ms_per_code = 1;
-    acq_parameters_.SetFromConfiguration(configuration, role, 1.023e6, 1000000.0);  // GPS_L1_CA_CODE_RATE_CPS, GPS_L1_CA_OPT_ACQ_FS_SPS
+    acq_parameters_.ms_per_code = ms_per_code;
+    acq_parameters_.SetFromConfiguration(configuration, role, chip_rate_cps, opt_acq_fs_sps);
     doppler_max_ = static_cast<unsigned int>(acq_parameters_.doppler_max);
     doppler_step_ = static_cast<unsigned int>(acq_parameters_.doppler_step);
     item_type_ = acq_parameters_.item_type;
     item_size_ = acq_parameters_.it_size;
-    code_length_ = static_cast<unsigned int>(std::floor(static_cast<double>(acq_parameters_.resampled_fs) / (1.023e6 / 1023.0)));
+    code_length_ = static_cast<unsigned int>(std::floor(static_cast<double>(acq_parameters_.resampled_fs) / (chip_rate_cps / code_length_chips)));
     vector_length_ = static_cast<unsigned int>(std::floor(acq_parameters_.sampled_ms * acq_parameters_.samples_per_ms) * (acq_parameters_.bit_transition_flag ? 2.0 : 1.0));
     code_.assign(vector_length_, std::complex<float>(0, 0));
     sampled_ms_ = acq_parameters_.sampled_ms;
@@ -127,67 +137,123 @@ GpsL1CaPcpsAcquisitionB200::GpsL1CaPcpsAcquisitionB200(const ConfigurationInterf
     if (out_streams_ > 0) std::cerr << "ERROR: This implementation does not provide an output stream\n";
 }
 
-void GpsL1CaPcpsAcquisitionB200::stop_acquisition() { acquisition_->set_active(false); }
-void GpsL1CaPcpsAcquisitionB200::set_threshold(float threshold)
+void B200PcpsAcquisition::stop_acquisition() { acquisition_->set_active(false); }
+void B200PcpsAcquisition::set_threshold(float threshold)
 {
     threshold_ = threshold;
     acquisition_->set_threshold(threshold_);
 }
-void GpsL1CaPcpsAcquisitionB200::set_doppler_max(unsigned int doppler_max)
+void B200PcpsAcquisition::set_doppler_max(unsigned int doppler_max)
 {
     doppler_max_ = doppler_max;
     acquisition_->set_doppler_max(doppler_max_);
 }
-void GpsL1CaPcpsAcquisitionB200::set_doppler_step(unsigned int doppler_step)
+void B200PcpsAcquisition::set_doppler_step(unsigned int doppler_step)
 {
     doppler_step_ = doppler_step;
     acquisition_->set_doppler_step(doppler_step_);
 }
-void GpsL1CaPcpsAcquisitionB200::set_doppler_center(int doppler_center)
+void B200PcpsAcquisition::set_doppler_center(int doppler_center)
 {
     doppler_center_ = doppler_center;
     acquisition_->set_doppler_center(doppler_center_);
 }
-void GpsL1CaPcpsAcquisitionB200::set_gnss_synchro(Gnss_Synchro* p)
+void B200PcpsAcquisition::set_gnss_synchro(Gnss_Synchro* p)
 {
     gnss_synchro_ = p;
     acquisition_->set_gnss_synchro(gnss_synchro_);
 }
-void GpsL1CaPcpsAcquisitionB200::set_channel(unsigned int channel)
+void B200PcpsAcquisition::set_channel(unsigned int channel)
 {
     channel_ = channel;
     acquisition_->set_channel(channel_);
 }
-void GpsL1CaPcpsAcquisitionB200::set_channel_fsm(std::weak_ptr<ChannelFsm> channel_fsm)
+void B200PcpsAcquisition::set_channel_fsm(std::weak_ptr<ChannelFsm> channel_fsm)
 {
     channel_fsm_ = std::move(channel_fsm);
     acquisition_->set_channel_fsm(channel_fsm_);
 }
-signed int GpsL1CaPcpsAcquisitionB200::mag() { return static_cast<signed int>(acquisition_->mag()); }
-void GpsL1CaPcpsAcquisitionB200::init() { acquisition_->init(); }
+signed int B200PcpsAcquisition::mag() { return static_cast<signed int>(acquisition_->mag()); }
+void B200PcpsAcquisition::init() { acquisition_->init(); }
 
-// one code period of the sampled replica, repeated sampled_ms times (:151-170)
-void GpsL1CaPcpsAcquisitionB200::set_local_code()
+// one period of the sampled replica, repeated to fill the block's local code (gps_l1_ca_pcps_acquisition.cc:151-170,
+// galileo_e1_pcps_ambiguous_acquisition.cc:149-199, gps_l5i_pcps_acquisition.cc:151-171, galileo_e5a_pcps_acquisition.cc:145-180)
+void B200PcpsAcquisition::set_local_code()
+{
+    make_local_code();
+    acquisition_->set_local_code(code_.data());
+}
+void B200PcpsAcquisition::make_local_code()
 {
     std::vector<std::complex<float>> code(code_length_);
     const auto fs = static_cast<int32_t>(acq_parameters_.use_automatic_resampler ? acq_parameters_.resampled_fs : acq_parameters_.fs_in);
-    gps_l1_ca_code_gen_complex_sampled(code.data(), static_cast<int>(code_length_), gnss_synchro_->PRN, fs, 0);
-    for (unsigned int i = 0; i < sampled_ms_ && (i + 1) * code_length_ <= vector_length_; i++) std::copy_n(code.data(), code_length_, code_.data() + i * code_length_);
-    acquisition_->set_local_code(code_.data());
+    generate_code(code.data(), fs);
+    const unsigned int copies = code_copies();
+    for (unsigned int i = 0; i < copies && (i + 1) * code_length_ <= vector_length_; i++) std::copy_n(code.data(), code_length_, code_.data() + i * code_length_);
 }
-void GpsL1CaPcpsAcquisitionB200::reset() { acquisition_->set_active(true); }
-void GpsL1CaPcpsAcquisitionB200::set_state(int state) { acquisition_->set_state(state); }
-void GpsL1CaPcpsAcquisitionB200::set_resampler_latency(uint32_t latency_samples) { acquisition_->set_resampler_latency(latency_samples); }
-void GpsL1CaPcpsAcquisitionB200::connect(gr::top_block_sptr top_block)
+void B200PcpsAcquisition::reset() { acquisition_->set_active(true); }
+void B200PcpsAcquisition::set_state(int state) { acquisition_->set_state(state); }
+void B200PcpsAcquisition::set_resampler_latency(uint32_t latency_samples) { acquisition_->set_resampler_latency(latency_samples); }
+void B200PcpsAcquisition::connect(gr::top_block_sptr top_block)
 {
-    if (top_block) { /* gr_complex, cshort and cbyte are ingested directly: no converter blocks to connect (cf. :187-203) */ }
+    if (top_block) { /* gr_complex, cshort and cbyte are ingested directly: no converter blocks to connect (cf. gps_l1_ca_pcps_acquisition.cc:187-203) */ }
 }
-void GpsL1CaPcpsAcquisitionB200::disconnect(gr::top_block_sptr top_block)
+void B200PcpsAcquisition::disconnect(gr::top_block_sptr top_block)
 {
     if (top_block) { /* nothing to disconnect */ }
 }
-gr::basic_block_sptr GpsL1CaPcpsAcquisitionB200::get_left_block() { return acquisition_; }
-gr::basic_block_sptr GpsL1CaPcpsAcquisitionB200::get_right_block() { return acquisition_; }
+gr::basic_block_sptr B200PcpsAcquisition::get_left_block() { return acquisition_; }
+gr::basic_block_sptr B200PcpsAcquisition::get_right_block() { return acquisition_; }
+
+// GPS_L1_CA_CODE_RATE_CPS, GPS_L1_CA_OPT_ACQ_FS_SPS, GPS_L1_CA_CODE_LENGTH_CHIPS (GPS_L1_CA.h)
+GpsL1CaPcpsAcquisitionB200::GpsL1CaPcpsAcquisitionB200(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
+    : B200PcpsAcquisition(c, role, in, out, "GPS_L1_CA_PCPS_Acquisition_B200", 1, 1.023e6, 2000000.0, 1023.0)
+{
+}
+void GpsL1CaPcpsAcquisitionB200::generate_code(std::complex<float>* code, int32_t fs)
+{
+    gps_l1_ca_code_gen_complex_sampled(code, static_cast<int>(code_length_), gnss_synchro_->PRN, fs, 0);
+}
+
+// GALILEO_E1_CODE_CHIP_RATE_CPS, GALILEO_E1_OPT_ACQ_FS_SPS, GALILEO_E1_B_CODE_LENGTH_CHIPS (Galileo_E1.h:39-53)
+GalileoE1PcpsAmbiguousAcquisitionB200::GalileoE1PcpsAmbiguousAcquisitionB200(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
+    : B200PcpsAcquisition(c, role, in, out, "Galileo_E1_PCPS_Ambiguous_Acquisition_B200", 4, 1.023e6, 2000000.0, 4092.0),
+      acquire_pilot_(c->property(role + ".acquire_pilot", false))
+{
+}
+void GalileoE1PcpsAmbiguousAcquisitionB200::generate_code(std::complex<float>* code, int32_t fs)
+{
+    // the reference reads "Acquisition<channel>.cboc" (no signal suffix) at every set_local_code (:151-152)
+    const bool cboc = configuration_->property("Acquisition" + std::to_string(channel_) + ".cboc", false);
+    char sig[3] = {'1', 'C', '\0'};
+    if (!acquire_pilot_)
+        {
+            sig[0] = gnss_synchro_->Signal[0];
+            sig[1] = gnss_synchro_->Signal[1];
+        }
+    galileo_e1_code_gen_complex_sampled(code, sig, cboc, gnss_synchro_->PRN, fs, 0, false);
+}
+
+// GPS_L5I_CODE_RATE_CPS, GPS_L5_OPT_ACQ_FS_SPS, GPS_L5I_CODE_LENGTH_CHIPS (GPS_L5.h)
+GpsL5iPcpsAcquisitionB200::GpsL5iPcpsAcquisitionB200(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
+    : B200PcpsAcquisition(c, role, in, out, "GPS_L5i_PCPS_Acquisition_B200", 1, 10.23e6, 10000000.0, 10230.0)
+{
+}
+void GpsL5iPcpsAcquisitionB200::generate_code(std::complex<float>* code, int32_t fs) { gps_l5i_code_gen_complex_sampled(code, gnss_synchro_->PRN, fs); }
+
+// GALILEO_E5A_CODE_CHIP_RATE_CPS, GALILEO_E5A_OPT_ACQ_FS_SPS, GALILEO_E5A_CODE_LENGTH_CHIPS (Galileo_E5a.h)
+GalileoE5aPcpsAcquisitionB200::GalileoE5aPcpsAcquisitionB200(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
+    : B200PcpsAcquisition(c, role, in, out, "Galileo_E5a_Pcps_Acquisition_B200", 1, 10.23e6, 10000000.0, 10230.0),
+      acq_pilot_(c->property(role + ".acquire_pilot", false)),
+      acq_iq_(c->property(role + ".acquire_iq", false))
+{
+    if (acq_iq_) acq_pilot_ = false;  // :77-80
+}
+void GalileoE5aPcpsAcquisitionB200::generate_code(std::complex<float>* code, int32_t fs)
+{
+    const char sig[3] = {'5', acq_iq_ ? 'X' : acq_pilot_ ? 'Q' : 'I', '\0'};
+    galileo_e5_a_code_gen_complex_sampled(code, gnss_synchro_->PRN, sig, fs, 0);
+}
 
 // ------------------------------------------------------------------ factory chain
 std::unique_ptr<TrackingInterface> GetB200TrkBlock(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
@@ -204,6 +270,9 @@ std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const ConfigurationInterfa
 {
     const std::string impl = c->property(role + ".implementation", std::string("Pass_Through"));
     if (impl == "GPS_L1_CA_PCPS_Acquisition_B200") return std::make_unique<GpsL1CaPcpsAcquisitionB200>(c, role, in, out);
+    if (impl == "Galileo_E1_PCPS_Ambiguous_Acquisition_B200") return std::make_unique<GalileoE1PcpsAmbiguousAcquisitionB200>(c, role, in, out);
+    if (impl == "GPS_L5i_PCPS_Acquisition_B200") return std::make_unique<GpsL5iPcpsAcquisitionB200>(c, role, in, out);
+    if (impl == "Galileo_E5a_Pcps_Acquisition_B200") return std::make_unique<GalileoE5aPcpsAcquisitionB200>(c, role, in, out);
     return nullptr;
 }
 

@@ -81,13 +81,17 @@ public:
     }
 };
 
-// ---- acquisition
-class GpsL1CaPcpsAcquisitionB200 : public AcquisitionInterface
+// ---- acquisition: one adapter class parameterised by signal (the four reference adapters differ only in the chip rate, the
+// code period, the replica generator and two E1 / E5a options), with the thin named subclasses the factory instantiates
+class B200PcpsAcquisition : public AcquisitionInterface
 {
 public:
-    GpsL1CaPcpsAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+    // adapters/gps_l1_ca_pcps_acquisition.cc:39-98, galileo_e1_pcps_ambiguous_acquisition.cc:36-98, gps_l5i_pcps_acquisition.cc:36-95,
+    // galileo_e5a_pcps_acquisition.cc:36-90: ms_per_code, SetFromConfiguration(chip rate, optimum resampled rate), code / vector lengths
+    B200PcpsAcquisition(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams,
+        const char* implementation, uint32_t ms_per_code, double chip_rate_cps, double opt_acq_fs_sps, double code_length_chips);
     std::string role() override { return role_; }
-    std::string implementation() override { return "GPS_L1_CA_PCPS_Acquisition_B200"; }
+    std::string implementation() override { return implementation_; }
     size_t item_size() override { return item_size_; }
     void connect(gr::top_block_sptr top_block) override;
     void disconnect(gr::top_block_sptr top_block) override;
@@ -109,18 +113,72 @@ public:
     void set_resampler_latency(uint32_t latency_samples) override;
     std::shared_ptr<b200_pcps_acquisition> block() { return acquisition_; }
     const Acq_Conf& conf() const { return acq_parameters_; }
+    // the replica of gnss_synchro_'s satellite as set_local_code() builds it, without handing it to the block (the batched
+    // all-PRN sweep of B200ChannelManager fills one code-spectrum slot per candidate satellite from it)
+    void make_local_code();
+    // the replica last built by make_local_code() / set_local_code()
+    const std::vector<std::complex<float>>& local_code() const { return code_; }
 
-private:
+protected:
+    // one code period of the sampled replica of gnss_synchro_->PRN at `fs` into code[0..code_length_)
+    virtual void generate_code(std::complex<float>* code, int32_t fs) = 0;
+    // how many copies of that period fill the block's local code (sampled_ms for 1 ms codes, sampled_ms / 4 for E1)
+    virtual unsigned int code_copies() const { return sampled_ms_; }
+
     Acq_Conf acq_parameters_;
+    const ConfigurationInterface* configuration_;
     std::shared_ptr<b200_pcps_acquisition> acquisition_;
     std::vector<std::complex<float>> code_;
     std::weak_ptr<ChannelFsm> channel_fsm_;
     Gnss_Synchro* gnss_synchro_{nullptr};
-    std::string role_, item_type_;
+    std::string role_, implementation_, item_type_;
     size_t item_size_;
     float threshold_{0.0F};
     int doppler_center_{0};
     unsigned int vector_length_, code_length_, channel_{0}, doppler_max_, doppler_step_, sampled_ms_, in_streams_, out_streams_;
+};
+
+// adapters/gps_l1_ca_pcps_acquisition.cc
+class GpsL1CaPcpsAcquisitionB200 : public B200PcpsAcquisition
+{
+public:
+    GpsL1CaPcpsAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+
+protected:
+    void generate_code(std::complex<float>* code, int32_t fs) override;
+};
+
+// adapters/galileo_e1_pcps_ambiguous_acquisition.cc: 4 ms codes, `acquire_pilot` (E1-C instead of the channel's signal), `Acquisition<ch>.cboc`
+class GalileoE1PcpsAmbiguousAcquisitionB200 : public B200PcpsAcquisition
+{
+public:
+    GalileoE1PcpsAmbiguousAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+
+protected:
+    void generate_code(std::complex<float>* code, int32_t fs) override;
+    unsigned int code_copies() const override { return sampled_ms_ / 4; }
+    bool acquire_pilot_;
+};
+
+// adapters/gps_l5i_pcps_acquisition.cc
+class GpsL5iPcpsAcquisitionB200 : public B200PcpsAcquisition
+{
+public:
+    GpsL5iPcpsAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+
+protected:
+    void generate_code(std::complex<float>* code, int32_t fs) override;
+};
+
+// adapters/galileo_e5a_pcps_acquisition.cc: `acquire_pilot` (5Q), `acquire_iq` (5X, wins over acquire_pilot), else 5I
+class GalileoE5aPcpsAcquisitionB200 : public B200PcpsAcquisition
+{
+public:
+    GalileoE5aPcpsAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+
+protected:
+    void generate_code(std::complex<float>* code, int32_t fs) override;
+    bool acq_pilot_, acq_iq_;
 };
 
 // The `.implementation` strings this tree serves; nullptr for any other string (the caller falls through to the

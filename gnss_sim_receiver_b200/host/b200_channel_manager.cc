@@ -15,7 +15,8 @@ B200ChannelManager::B200ChannelManager(const ConfigurationInterface* configurati
     // ---- acquisition side: one sweep engine with a code-spectrum slot per candidate satellite
     auto acq = GetB200AcqBlock(configuration, acq_role, 1, 0);
     if (!acq) throw std::runtime_error(acq_role + ".implementation is not a B200 acquisition block");
-    acq_conf_ = static_cast<GpsL1CaPcpsAcquisitionB200*>(acq.get())->conf();
+    auto* acq_adapter = static_cast<B200PcpsAcquisition*>(acq.get());
+    acq_conf_ = acq_adapter->conf();
     if (acq_conf_.pfa <= 0.0F) throw std::invalid_argument(acq_role + ".pfa must be set: the batched sweep judges every satellite against the CFAR threshold");
     item_bytes_ = acq_conf_.it_size;
     consumed_ = static_cast<uint32_t>(acq_conf_.sampled_ms * acq_conf_.samples_per_ms * (acq_conf_.bit_transition_flag ? 2.0 : 1.0));  // pcps_acquisition.cc:71
@@ -23,15 +24,22 @@ B200ChannelManager::B200ChannelManager(const ConfigurationInterface* configurati
     sweep_->set_doppler_grid(acq_conf_.doppler_max, static_cast<int>(acq_conf_.doppler_step), 0);
     threshold_ = sweep_->threshold(acq_conf_.pfa);
     {
-        // the sampled replica the adapter builds (adapters/gps_l1_ca_pcps_acquisition.cc:151-170)
-        const auto fs = static_cast<int32_t>(acq_conf_.use_automatic_resampler ? acq_conf_.resampled_fs : acq_conf_.fs_in);
-        const auto code_length = static_cast<unsigned>(std::floor(static_cast<double>(fs) / (1.023e6 / 1023.0)));
+        // the sampled replica of every candidate satellite, built by the signal's own adapter (GPS L1 C/A, Galileo E1, GPS L5I,
+        // Galileo E5a: adapters/*_pcps_acquisition.cc set_local_code); the channel's system / signal come from the tracking role
+        auto trk_probe = GetB200TrkBlock(configuration, trk_role, 1, 1);
+        if (!trk_probe) throw std::runtime_error(trk_role + ".implementation is not a B200 tracking block");
+        const Dll_Pll_Conf& tp = static_cast<B200DllPllTracking*>(trk_probe.get())->conf();
+        Gnss_Synchro probe{};
+        probe.System = tp.system;
+        std::memcpy(probe.Signal, tp.signal, 3);
+        acq_adapter->set_gnss_synchro(&probe);
         const unsigned n_code = acq_conf_.bit_transition_flag ? consumed_ / 2 : consumed_;
-        std::vector<std::complex<float>> one(code_length), code(n_code, std::complex<float>(0, 0));
         for (size_t s = 0; s < prns_.size(); s++)
             {
-                gps_l1_ca_code_gen_complex_sampled(one.data(), static_cast<int>(code_length), prns_[s], fs, 0);
-                for (unsigned i = 0; i < acq_conf_.sampled_ms && (i + 1) * code_length <= n_code; i++) std::copy_n(one.data(), code_length, code.data() + i * code_length);
+                probe.PRN = prns_[s];
+                acq_adapter->make_local_code();
+                const auto& code = acq_adapter->local_code();
+                if (code.size() < n_code) throw std::runtime_error("acquisition adapter produced a short local code");
                 sweep_->set_local_code(static_cast<int>(s), code.data(), static_cast<int>(n_code));
             }
     }

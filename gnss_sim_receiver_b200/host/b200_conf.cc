@@ -94,6 +94,7 @@ void Dll_Pll_Conf::SetFromConfiguration(const ConfigurationInterface* c, const s
     carrier_lock_test_smoother_samples = c->property(role + ".carrier_lock_test_smoother_samples", carrier_lock_test_smoother_samples);
     carrier_lock_test_smoother_alpha = c->property(role + ".carrier_lock_test_smoother_alpha", carrier_lock_test_smoother_alpha);
     device = c->property(role + ".device", device);
+    stream_id = c->property(role + ".stream_id", stream_id);
 }
 
 void Acq_Conf::SetFromConfiguration(const ConfigurationInterface* c, const std::string& role, double chip_rate, double opt_freq)

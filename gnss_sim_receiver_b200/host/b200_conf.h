@@ -1,7 +1,8 @@
 // Parameter bundles of the two blocks, read from the same .conf keys with the same defaults and clamps as the reference:
 //   Dll_Pll_Conf  src/algorithms/tracking/libs/dll_pll_conf.{h:30-88,cc:36-125}
 //   Acq_Conf      src/algorithms/acquisition/libs/acq_conf.{h:34-79,cc:24-118}
-// plus two keys of our own: `<role>.device` (CUDA ordinal, default 0) and `<role>.n_correlators` (extended-correlator taps).
+// plus keys of our own: `<role>.device` (CUDA ordinal, default 0), `<role>.n_correlators` (extended-correlator taps) and
+// `<role>.stream_id` (which input stream the channel reads; default -1 = by band: L1 signals share stream 0, L5 / E5a stream 1).
 #ifndef GB200_CONF_H
 #define GB200_CONF_H
 
@@ -63,6 +64,7 @@ public:
     bool dump_mat{true};
     // B200 additions
     int32_t device{0};
+    int32_t stream_id{-1};
 };
 
 class Acq_Conf

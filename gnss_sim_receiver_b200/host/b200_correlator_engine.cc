@@ -3,6 +3,7 @@
 #include <chrono>
 #include <cstring>
 #include <map>
+#include <tuple>
 #include <stdexcept>
 
 namespace gb200h
@@ -11,7 +12,7 @@ namespace
 {
 [[noreturn]] void fail(const char* what) { throw std::runtime_error(std::string(what) + ": " + gb200_last_error()); }
 std::mutex g_inst_mu;
-std::map<std::pair<int, int>, std::shared_ptr<B200CorrelatorEngine>> g_instances;
+std::map<std::tuple<int, int, int>, std::shared_ptr<B200CorrelatorEngine>> g_instances;
 int elem_bytes(int iq) { return iq == GB200_IQ_CF32 ? 8 : iq == GB200_IQ_CS16 ? 4 : 2; }
 }  // namespace
 
@@ -26,9 +27,17 @@ struct B200CorrelatorEngine::Batch
 std::shared_ptr<B200CorrelatorEngine> B200CorrelatorEngine::instance(const EngineConfig& cfg)
 {
     std::lock_guard<std::mutex> lk(g_inst_mu);
-    auto key = std::make_pair(cfg.device, cfg.iq_dtype);
+    auto key = std::make_tuple(cfg.device, cfg.iq_dtype, cfg.stream_id);
     auto it = g_instances.find(key);
-    if (it != g_instances.end()) return it->second;
+    if (it != g_instances.end())
+        {
+            const EngineConfig& have = it->second->config();
+            if (cfg.max_block > have.max_block || cfg.max_code_len > have.max_code_len)
+                throw std::invalid_argument("B200CorrelatorEngine: the engine of device " + std::to_string(cfg.device) + " stream " + std::to_string(cfg.stream_id) +
+                                            " was created for windows of " + std::to_string(have.max_block) + " samples and code tables of " + std::to_string(have.max_code_len) +
+                                            " entries; this channel needs " + std::to_string(cfg.max_block) + " / " + std::to_string(cfg.max_code_len));
+            return it->second;
+        }
     auto e = std::make_shared<B200CorrelatorEngine>(cfg);
     g_instances[key] = e;
     return e;
@@ -207,7 +216,7 @@ bool B200_Multicorrelator_Real_Codes::init(int max_signal_length_samples, int n_
 {
     if (!engine_) return false;
     if (n_correlators < 1 || n_correlators > GB200_MAX_TAPS) return false;
-    if (max_signal_length_samples > 2 * engine_->config().max_block) return false;
+    if (max_signal_length_samples > engine_->config().max_block) return false;  // the engine's longest window (prepare_cmd refuses longer ones)
     if (ch_ < 0) ch_ = engine_->attach_channel();
     n_correlators_ = n_correlators;
     max_len_ = max_signal_length_samples;

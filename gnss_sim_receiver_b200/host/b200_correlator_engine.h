@@ -26,6 +26,7 @@ struct EngineConfig
 {
     int device{0};
     int iq_dtype{GB200_IQ_CF32};
+    int stream_id{0};                // which input stream (RF band / antenna) the ring holds: one engine per (device, iq_dtype, stream)
     int max_channels{256};
     int max_code_len{10230};
     int max_block{1 << 17};          // longest correlation window, samples
@@ -36,7 +37,10 @@ struct EngineConfig
 class B200CorrelatorEngine
 {
 public:
-    // one engine per (device, iq_dtype); created on first use with `cfg`, later calls return the existing one.
+    // one engine per (device, iq_dtype, stream_id): the ring is ONE stream's samples addressed by nitems_read, so two streams of
+    // the same item type (an L1 band and an L5 band, two antennas) never share it.  Created on first use with `cfg`; a later call
+    // whose channel needs a longer window, a longer code table or a deeper ring than the existing engine was sized for throws
+    // std::invalid_argument (size the first one from the receiver-wide maximum, as the adapters do).
     // Throws std::runtime_error (message from gb200_last_error) when the GPU engine cannot be created: no CPU fallback.
     static std::shared_ptr<B200CorrelatorEngine> instance(const EngineConfig& cfg);
     // drop the process-wide instances (tests)

@@ -248,22 +248,30 @@ void b200_dll_pll_veml_tracking::set_data_code(const float* code, int n)
 void b200_dll_pll_veml_tracking::set_engine(std::shared_ptr<B200CorrelatorEngine> engine)
 {
     engine_ = std::move(engine);
+    const auto refuse = [&](const char* which) {
+        const EngineConfig& ec = engine_->config();
+        throw std::runtime_error(std::string("b200_dll_pll_veml_tracking: ") + which + " cannot attach to the correlator engine of device " + std::to_string(ec.device) +
+                                 " stream " + std::to_string(ec.stream_id) + " (engine: windows up to " + std::to_string(ec.max_block) + " samples, " +
+                                 std::to_string(ec.max_channels) + " channel slots; this channel: 2 x " + std::to_string(d_trk_parameters.vector_length) + " samples, " +
+                                 std::to_string(d_n_correlator_taps) + " taps)");
+    };
     d_multicorrelator.set_engine(engine_);
     d_multicorrelator.set_high_dynamics_resampler(d_trk_parameters.high_dyn);
-    d_multicorrelator.init(static_cast<int>(2 * d_trk_parameters.vector_length), d_n_correlator_taps);
+    if (!d_multicorrelator.init(static_cast<int>(2 * d_trk_parameters.vector_length), d_n_correlator_taps)) refuse("the multicorrelator");
     if (d_trk_parameters.track_pilot)
         {
             d_correlator_data.set_engine(engine_);
             d_correlator_data.set_high_dynamics_resampler(d_trk_parameters.high_dyn);
-            d_correlator_data.init(static_cast<int>(2 * d_trk_parameters.vector_length), 1);
+            if (!d_correlator_data.init(static_cast<int>(2 * d_trk_parameters.vector_length), 1)) refuse("the data-component correlator");
         }
 }
 
 void b200_dll_pll_veml_tracking::upload_codes()
 {
     if (!engine_) return;
-    d_multicorrelator.set_local_code_and_taps(code_table_entries(), d_tracking_code.data(), d_local_code_shift_chips.data());
-    if (d_trk_parameters.track_pilot) d_correlator_data.set_local_code_and_taps(code_table_entries(), d_data_code.data(), &d_local_code_shift_chips[idx_P_]);
+    bool ok = d_multicorrelator.set_local_code_and_taps(code_table_entries(), d_tracking_code.data(), d_local_code_shift_chips.data());
+    if (ok && d_trk_parameters.track_pilot) ok = d_correlator_data.set_local_code_and_taps(code_table_entries(), d_data_code.data(), &d_local_code_shift_chips[idx_P_]);
+    if (!ok) throw std::runtime_error("b200_dll_pll_veml_tracking: set_local_code_and_taps before a successful init() (channel not attached to the engine)");
 }
 
 // dll_pll_veml_tracking.cc:643-883
@@ -358,6 +366,7 @@ void b200_dll_pll_veml_tracking::start_tracking()
     d_code_loop_filter.initialize();
 
     d_state = 1;
+    pending_skip_ = 0;
     d_cloop = true;
     d_pull_in_transitory = true;
     d_Prompt_circular_buffer.clear();
@@ -831,12 +840,27 @@ void b200_dll_pll_veml_tracking::log_data()
 // The correlation goes through the shared engine (one upload per sample block, requests of concurrent channels batched).
 int b200_dll_pll_veml_tracking::general_work(const void* input_items, int ninput_items, uint64_t nitems_read, Gnss_Synchro* out, int* consumed)
 {
+    if (pending_skip_ > 0)
+        {
+            // rest of a pull-in alignment skip that did not fit into the previous call's input (see below)
+            const int c = static_cast<int>(std::min<int64_t>(pending_skip_, ninput_items));
+            pending_skip_ -= c;
+            *consumed = c;
+            return 0;
+        }
     Step s = plan(nitems_read, d_multicorrelator.channel(), d_correlator_data.channel());
     if (!s.correlate)
         {
+            // The reference's forecast() asks for 2 * vector_length items, so its consume_each(samples_offset) (dll_pll_veml_tracking.cc:1786)
+            // always fits; a caller of this blocking form may hand over less: plan() has already left state 1 and charged the full
+            // offset to d_acc_carrier_phase_rad, so the part that does not fit is skipped at the start of the following calls.
             *consumed = s.consume < 0 ? ninput_items : std::min(s.consume, ninput_items);
+            if (s.consume > ninput_items) pending_skip_ = static_cast<int64_t>(s.consume) - ninput_items;
             return 0;
         }
+    if (ninput_items < s.cmd.n_samples)
+        throw std::runtime_error("b200_dll_pll_veml_tracking::general_work: " + std::to_string(ninput_items) + " input items, the correlation needs " +
+                                 std::to_string(s.cmd.n_samples) + " (the reference's forecast() guarantees 2 * vector_length)");
     if (!engine_) throw std::runtime_error("b200_dll_pll_veml_tracking: no correlator engine (set_engine)");
     gr_complex data_out(0, 0);
     d_multicorrelator.set_input_output_vectors(d_correlator_outs.data(), input_items, nitems_read, ninput_items);

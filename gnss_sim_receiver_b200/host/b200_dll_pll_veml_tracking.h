@@ -62,6 +62,8 @@ public:
     // per-channel blocking form: returns the number of Gnss_Synchro produced (0/1); *consumed = consume_each
     int general_work(const void* input_items, int ninput_items, uint64_t nitems_read, Gnss_Synchro* out, int* consumed);
     void set_engine(std::shared_ptr<B200CorrelatorEngine> engine);
+    std::shared_ptr<B200CorrelatorEngine> engine() const { return engine_; }
+    int engine_channel() const { return d_multicorrelator.channel(); }
     // (re)upload the code tables of this block to its engine slots; start_tracking does it when an engine is attached
     void upload_codes();
 
@@ -127,6 +129,7 @@ private:
     double d_carrier_phase_step_rad{0}, d_carrier_phase_rate_step_rad{0}, d_code_phase_step_chips{0}, d_code_phase_rate_step_chips{0};
     double d_rem_code_phase_samples{0};
     uint64_t d_acq_sample_stamp{0}, last_nitems_read_{0};
+    int64_t pending_skip_{0};  // general_work: rest of the pull-in alignment skip that did not fit into one call
     float d_rem_carr_phase_rad{0};
     int32_t d_symbols_per_bit{0}, d_state{0}, d_correlation_length_ms{0}, d_n_correlator_taps{3}, d_current_prn_length_samples{0};
     int32_t d_extend_correlation_symbols_count{0}, d_extend_correlation_symbols{1}, d_cn0_estimation_counter{0};

@@ -94,11 +94,58 @@ const char* gb200h_factory(const char* conf_text, const char* role)
             const std::string impl = cfg.property(std::string(role) + ".implementation", std::string(""));
             if (auto t = GetB200TrkBlock(&cfg, role, 1, 1))
                 t_ret = t->implementation() + ";item_size=" + std::to_string(t->item_size()) + ";role=" + t->role() + ";";
-            else if (impl == "GPS_L1_CA_PCPS_Acquisition_B200")
+            else if (impl == "GPS_L1_CA_PCPS_Acquisition_B200" || impl == "Galileo_E1_PCPS_Ambiguous_Acquisition_B200" || impl == "GPS_L5i_PCPS_Acquisition_B200" ||
+                     impl == "Galileo_E5a_Pcps_Acquisition_B200")
                 t_ret = impl + ";acquisition;";
         }
     catch (const std::exception& e)
         {
+            t_ret = std::string("error=") + e.what();
+        }
+    return t_ret.c_str();
+}
+
+// Two tracking adapters built from one configuration and started the way Channel does (set_gnss_synchro, start_tracking): which
+// correlator engine each one attached to.  "same=<0|1>;stream_a=..;stream_b=..;slot_a=..;slot_b=..;max_block=..;" or "error=...".
+const char* gb200h_engine_probe(const char* conf_text, const char* role_a, unsigned prn_a, const char* role_b, unsigned prn_b)
+{
+    B200Configuration cfg;
+    cfg.load_string(conf_text);
+    t_ret.clear();
+    try
+        {
+            B200CorrelatorEngine::reset_instances();
+            auto a = GetB200TrkBlock(&cfg, role_a, 1, 1);
+            auto b = GetB200TrkBlock(&cfg, role_b, 1, 1);
+            if (!a || !b) throw std::runtime_error("not a B200 tracking implementation");
+            Gnss_Synchro sa{}, sb{};
+            auto* ta = static_cast<B200DllPllTracking*>(a.get());
+            auto* tb = static_cast<B200DllPllTracking*>(b.get());
+            sa.System = ta->conf().system;
+            std::memcpy(sa.Signal, ta->conf().signal, 3);
+            sa.PRN = prn_a;
+            sb.System = tb->conf().system;
+            std::memcpy(sb.Signal, tb->conf().signal, 3);
+            sb.PRN = prn_b;
+            a->set_gnss_synchro(&sa);
+            b->set_gnss_synchro(&sb);
+            a->set_channel(0);
+            b->set_channel(1);
+            a->start_tracking();
+            b->start_tracking();
+            auto ea = ta->block()->engine(), eb = tb->block()->engine();
+            if (!ea || !eb) throw std::runtime_error("a block did not attach to an engine");
+            std::ostringstream o;
+            o << "same=" << (ea == eb ? 1 : 0) << ";stream_a=" << ea->config().stream_id << ";stream_b=" << eb->config().stream_id << ";slot_a=" << ta->block()->engine_channel()
+              << ";slot_b=" << tb->block()->engine_channel() << ";max_block=" << ea->config().max_block << ";max_block_b=" << eb->config().max_block << ";";
+            t_ret = o.str();
+            a.reset();
+            b.reset();
+            B200CorrelatorEngine::reset_instances();
+        }
+    catch (const std::exception& e)
+        {
+            B200CorrelatorEngine::reset_instances();
             t_ret = std::string("error=") + e.what();
         }
     return t_ret.c_str();
@@ -450,14 +497,16 @@ int gb200h_bank_run_threaded(gb200h_bank* b, const void* iq, int64_t n_samples, 
 struct gb200h_acq
 {
     B200Configuration cfg;
-    std::unique_ptr<GpsL1CaPcpsAcquisitionB200> adapter;
+    std::unique_ptr<B200PcpsAcquisition> adapter;
     Gnss_Synchro synchro;
     int last_event{0};
 };
 
 extern "C" {
 
-int gb200h_acq_create(const char* conf_text, const char* role, unsigned prn, gb200h_acq** out)
+int gb200h_acq_create(const char* conf_text, const char* role, unsigned prn, gb200h_acq** out) { return gb200h_acq_create2(conf_text, role, prn, 'G', "1C", out); }
+
+int gb200h_acq_create2(const char* conf_text, const char* role, unsigned prn, char system, const char* signal, gb200h_acq** out)
 {
     try
         {
@@ -465,9 +514,10 @@ int gb200h_acq_create(const char* conf_text, const char* role, unsigned prn, gb2
             a->cfg.load_string(conf_text);
             auto blk = GetB200AcqBlock(&a->cfg, role, 1, 0);
             if (!blk) throw std::runtime_error(std::string(role) + ".implementation is not a B200 acquisition block");
-            a->adapter.reset(static_cast<GpsL1CaPcpsAcquisitionB200*>(blk.release()));
-            a->synchro.System = 'G';
-            std::memcpy(a->synchro.Signal, "1C", 3);
+            a->adapter.reset(static_cast<B200PcpsAcquisition*>(blk.release()));
+            a->synchro.System = system;
+            std::memset(a->synchro.Signal, 0, 3);
+            std::strncpy(a->synchro.Signal, signal, 2);
             a->synchro.PRN = prn;
             a->adapter->set_gnss_synchro(&a->synchro);
             a->adapter->set_channel(0);
@@ -545,6 +595,14 @@ int gb200h_acq_get_status(gb200h_acq* a, gb200h_acq_status* s)
     s->indext = blk.last_result().indext;
     s->doppler_index = blk.last_result().doppler_index;
     return 0;
+}
+
+int64_t gb200h_acq_local_code(gb200h_acq* a, float* dst, int64_t max_samples)
+{
+    const auto& c = a->adapter->local_code();
+    const int64_t n = std::min<int64_t>(max_samples, static_cast<int64_t>(c.size()));
+    if (dst && n > 0) std::memcpy(dst, c.data(), static_cast<size_t>(n) * sizeof(std::complex<float>));
+    return static_cast<int64_t>(c.size());
 }
 
 int gb200h_mat_write_sample(const char* filename, const float* grid, int rows, int cols, int32_t i32, uint32_t u32, uint64_t u64, float f32)

@@ -16,6 +16,9 @@ const char* gb200h_conf_get(const char* conf_text, const char* name, const char*
 /* Dll_Pll_Conf / Acq_Conf after SetFromConfiguration, as "key=value;" text */
 const char* gb200h_dll_pll_conf(const char* conf_text, const char* role);
 const char* gb200h_acq_conf(const char* conf_text, const char* role, double chip_rate, double opt_freq, int ms_per_code);
+/* two tracking adapters of one configuration, started like Channel starts them: which per-(device, item type, stream) engine each
+ * attached to ("same=..;stream_a=..;stream_b=..;slot_a=..;slot_b=..;max_block=..;" or "error=...").  Needs a GPU. */
+const char* gb200h_engine_probe(const char* conf_text, const char* role_a, unsigned prn_a, const char* role_b, unsigned prn_b);
 /* implementation()/item_size of the adapter GetB200Block selects for `role`, "" when the string is not ours */
 const char* gb200h_factory(const char* conf_text, const char* role);
 double gb200h_pll_cloop_two_quadrant_atan(float re, float im);
@@ -77,7 +80,11 @@ typedef struct
     uint32_t indext;
     int32_t doppler_index;
 } gb200h_acq_status;
-int gb200h_acq_create(const char* conf_text, const char* role, unsigned prn, gb200h_acq** out);
+int gb200h_acq_create(const char* conf_text, const char* role, unsigned prn, gb200h_acq** out); /* System 'G', Signal "1C" */
+/* same for any of the four acquisition adapters: `system` / `signal` fill the channel's Gnss_Synchro ('E' "1B", 'G' "L5", 'E' "5X" ...) */
+int gb200h_acq_create2(const char* conf_text, const char* role, unsigned prn, char system, const char* signal, gb200h_acq** out);
+/* the replica the adapter handed to set_local_code (complex float pairs); returns its length in samples */
+int64_t gb200h_acq_local_code(gb200h_acq* a, float* dst, int64_t max_samples);
 void gb200h_acq_destroy(gb200h_acq* a);
 /* adapter calls, in the order Channel/ChannelFsm make them: set_doppler_*, set_threshold (pfa = 0), init, set_local_code, start, set_state(1) */
 int gb200h_acq_arm(gb200h_acq* a, float threshold_if_no_pfa);

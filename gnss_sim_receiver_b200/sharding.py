@@ -116,6 +116,61 @@ def merge_doppler_tiles(dist, grid_tile, bin_lo, n_bins, neff, num_dwells=1, dev
     return dict(indext=indext, doppler_index=doppler_index, peak=float(peak[0]), input_power=float(power), test_statistics=float(stat))
 
 
+# ----------------------------------------------------------------- Doppler-tiled sweep on the GPUs: merge of per-bin cell reductions
+def merge_cells(vmax, imax, sums, neff, num_dwells=1, doppler_base=0, doppler_step=0, samples_per_code=None):
+    """Statistic of a sweep from its per-(slot, bin) reductions (gb200_acq_read_cells), bins in sweep order — the arithmetic of
+    acq_stats_kernel / max_to_input_power_statistic (pcps_acquisition.cc:496-528), operation for operation in fp32 / float64:
+    first Doppler bin wins among equal maxima (strict '>' over bins in order), first code phase within a bin (already in imax),
+    input power = sum of the OPPOSITE bin / N_eff / 2 / dwells.  Returns a list of dicts, one per slot."""
+    vmax = np.asarray(vmax, dtype=np.float32)
+    imax = np.asarray(imax, dtype=np.int64)
+    sums = np.asarray(sums, dtype=np.float32)
+    n_slots, n_bins = vmax.shape
+    out = []
+    for s in range(n_slots):
+        b = int(np.argmax(vmax[s]))  # first maximum in bin order
+        best = np.float32(vmax[s, b])
+        idx = int(imax[s, b])
+        if not best > 0:
+            best, b, idx = np.float32(0), 0, 0
+        opp = (b + n_bins // 2) % n_bins
+        power = np.float32(np.float64(np.float32(sums[s, opp]) / np.float32(neff)) / 2.0 / num_dwells)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            stat = np.float32(best) / power
+        r = dict(indext=idx, doppler_index=b, doppler_hz=int(doppler_base + doppler_step * b), peak=float(best), input_power=float(power), test_statistics=float(stat))
+        if samples_per_code is not None:
+            r["acq_delay_samples"] = float(np.fmod(np.float32(idx), np.float32(samples_per_code)))
+        out.append(r)
+    return out
+
+
+def gather_cell_tiles(dist, vmax, imax, sums, world, device="cpu"):
+    """All-gather of every rank's Doppler tile of cell reductions ([n_slots, bins_of_this_rank] each; tiles may differ in width) into
+    the full [n_slots, n_bins] tables on EVERY rank, tiles in rank order = bin order (doppler_tiles).  One collective of
+    3 x 4 bytes per (slot, bin): NCCL on the GPUs, gloo in the CPU tests."""
+    if dist is None or world == 1:
+        return np.asarray(vmax), np.asarray(imax), np.asarray(sums)
+    import torch
+    n_slots, nb = np.asarray(vmax).shape
+    widths = torch.zeros(world, dtype=torch.int64, device=device)
+    mine = torch.tensor([nb], dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(widths, mine)
+    widths = [int(w) for w in widths.tolist()]
+    wmax = max(widths)
+    pack = np.zeros((3, n_slots, wmax), np.float32)
+    pack[0, :, :nb] = vmax
+    pack[1, :, :nb] = np.ascontiguousarray(imax, dtype=np.int32).view(np.float32)  # the index bits travel in a float lane
+    pack[2, :, :nb] = sums
+    t = torch.from_numpy(pack).to(device).reshape(-1)
+    allt = torch.empty(world * t.numel(), dtype=t.dtype, device=device)
+    dist.all_gather_into_tensor(allt, t)
+    a = allt.cpu().numpy().reshape((world,) + pack.shape)
+    v = np.concatenate([a[r, 0, :, :widths[r]] for r in range(world)], axis=1)
+    i = np.concatenate([np.ascontiguousarray(a[r, 1, :, :widths[r]]).view(np.int32) for r in range(world)], axis=1)
+    sm = np.concatenate([a[r, 2, :, :widths[r]] for r in range(world)], axis=1)
+    return v, i, sm
+
+
 # --------------------------------------------------------------------------------------------------------- plumbing
 def reduce_max(dist, x, device="cpu"):
     """Max over ranks of a host scalar (timing: the slowest rank defines the step)."""

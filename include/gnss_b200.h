@@ -194,7 +194,7 @@ typedef struct
 {
     int32_t device;
     int32_t iq_dtype;         /* GB200_IQ_*: acq_parameters.it_size / item_type (acq_conf.cc:24-31) */
-    int32_t fft_size;         /* d_fft_size           pcps_acquisition.cc:84-93  (factors 2,3,5,7 only) */
+    int32_t fft_size;         /* d_fft_size           pcps_acquisition.cc:84-93  (prime factors up to 61; larger ones are refused with GB200_EINVAL) */
     int32_t consumed_samples; /* d_consumed_samples   pcps_acquisition.cc:84-91  (input zero-padded to fft_size, :612-619) */
     int32_t bit_transition;   /* acq_parameters.bit_transition_flag */
     int32_t use_cfar;         /* d_use_CFAR_algorithm_flag (pfa > 0), pcps_acquisition.cc:81 */
@@ -251,6 +251,11 @@ float gb200_acq_threshold(const gb200_acq* h, float pfa);
  * Only available when the engine keeps a grid (max_dwells > 1 or keep_grid set through gb200_acq_keep_grid). */
 int gb200_acq_keep_grid(gb200_acq* h, int keep);
 int gb200_acq_read_grid(gb200_acq* h, int slot, float* grid_host);
+/* Per-(slot, Doppler bin) reductions of the last run, [n_slots][n_bins] each: the maximum over code phase (what
+ * volk_gnsssdr_32f_index_max_32u finds in one grid row, pcps_acquisition.cc:505-514), its first index, and the row sum (the CFAR
+ * input power of the opposite bin, :518-519).  This is all a rank has to publish when ONE sweep is tiled over several GPUs by
+ * Doppler bin (gb200_acq_set_doppler_bins per rank): the merge keeps the reference's first-bin / first-index tie rule. */
+int gb200_acq_read_cells(gb200_acq* h, int n_slots, float* vmax, int32_t* imax, float* sum);
 /* forward transform of one fft_size block through the engine's FFT (test hook: natural-order output) */
 int gb200_acq_fft(gb200_acq* h, const gb200_cf32* in_host, gb200_cf32* out_host, int inverse);
 

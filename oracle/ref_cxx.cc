@@ -5,6 +5,7 @@
 // filters, lock detectors, exponential smoother. Used to pin oracle/ (the C
 // restatement) and to generate tests/golden/*. Lives in oracle/_ref/libgnssref.so.
 #include "cpu_multicorrelator.h"
+#include "cpu_multicorrelator_16sc.h"
 #include "cpu_multicorrelator_real_codes.h"
 #include "exponential_smoother.h"
 #include "galileo_e1_signal_replica.h"
@@ -64,6 +65,23 @@ int ref_mc_complex_codes(int arch, const float* sig_ri, int n, const float* code
     std::memcpy(out_ri, out.data(), sizeof(cf) * ntaps);
     mc.free();
     ref_set_arch(0);
+    return 0;
+}
+
+// cpu_multicorrelator_16sc.cc:64-91 — the int16 path: rotate in fp32, rintf to int16, SATURATING int16 multiply-accumulate
+// (volk_gnsssdr_16ic_x2_rotator_dot_prod_16ic_xn.h:66-102); sig / code / out are interleaved int16 (re, im)
+int ref_mc_16sc(const int16_t* sig_ri, int n, const int16_t* code_ri, int L, const float* shifts, int ntaps, float rem_carr, float phase_step,
+    float rem_code, float code_step, int16_t* out_ri)
+{
+    Cpu_Multicorrelator_16sc mc;
+    mc.init(2 * n, ntaps);
+    std::vector<float> sh(shifts, shifts + ntaps);
+    mc.set_local_code_and_taps(L, reinterpret_cast<const lv_16sc_t*>(code_ri), sh.data());
+    std::vector<lv_16sc_t> out(ntaps);
+    mc.set_input_output_vectors(out.data(), reinterpret_cast<const lv_16sc_t*>(sig_ri));
+    mc.Carrier_wipeoff_multicorrelator_resampler(rem_carr, phase_step, rem_code, code_step, n);
+    std::memcpy(out_ri, out.data(), sizeof(lv_16sc_t) * ntaps);
+    mc.free();
     return 0;
 }
 

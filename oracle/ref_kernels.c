@@ -19,6 +19,8 @@
 #include <volk_gnsssdr/volk_gnsssdr_s32f_sincos_32fc.h>
 #include <volk_gnsssdr/volk_gnsssdr_32f_index_max_32u.h>
 #include <volk_gnsssdr/volk_gnsssdr_16ic_convert_32fc.h>
+#include <volk_gnsssdr/volk_gnsssdr_16ic_xn_resampler_16ic_xn.h>
+#include <volk_gnsssdr/volk_gnsssdr_16ic_x2_rotator_dot_prod_16ic_xn.h>
 
 /* 0 = generic protokernels (normative for parity), 1 = AVX protokernels (what an x86 host runs) */
 static int g_arch = 0;
@@ -78,6 +80,17 @@ void volk_gnsssdr_32fc_x2_rotator_dot_prod_32fc_xn(lv_32fc_t* result, const lv_3
         volk_gnsssdr_32fc_x2_rotator_dot_prod_32fc_xn_u_avx(result, in_common, phase_inc, phase, in_a, num_a_vectors, num_points);
     else
         volk_gnsssdr_32fc_x2_rotator_dot_prod_32fc_xn_generic(result, in_common, phase_inc, phase, in_a, num_a_vectors, num_points);
+}
+
+/* the int16 path of Cpu_Multicorrelator_16sc (cpu_multicorrelator_16sc.cc:64-91): generic protokernels (the saturating int16 law) */
+void volk_gnsssdr_16ic_xn_resampler_16ic_xn(lv_16sc_t** result, const lv_16sc_t* local_code, float rem_code_phase_chips, float code_phase_step_chips, float* shifts_chips, unsigned int code_length_chips, int num_out_vectors, unsigned int num_points)
+{
+    volk_gnsssdr_16ic_xn_resampler_16ic_xn_generic(result, local_code, rem_code_phase_chips, code_phase_step_chips, shifts_chips, code_length_chips, num_out_vectors, num_points);
+}
+
+void volk_gnsssdr_16ic_x2_rotator_dot_prod_16ic_xn(lv_16sc_t* result, const lv_16sc_t* in_common, const lv_32fc_t phase_inc, lv_32fc_t* phase, const lv_16sc_t** in_a, int num_a_vectors, unsigned int num_points)
+{
+    volk_gnsssdr_16ic_x2_rotator_dot_prod_16ic_xn_generic(result, in_common, phase_inc, phase, in_a, num_a_vectors, num_points);
 }
 
 /* ---- explicit-protokernel entry points used by the tests ---- */

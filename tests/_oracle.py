@@ -115,6 +115,20 @@ def mc_complex_codes(sig, code, shifts, rem_carr, phase_step, rem_code, code_ste
     return out
 
 
+def mc_16sc(sig_i16, code_i16, shifts, rem_carr, phase_step, rem_code, code_step):
+    """The reference's own int16 path (Cpu_Multicorrelator_16sc over the generic 16ic protokernels, oracle/_ref): interleaved int16
+    (re, im) signal and code -> int16 complex outputs (saturating accumulation) as complex64."""
+    sig = np.ascontiguousarray(sig_i16, dtype=np.int16)
+    code = np.ascontiguousarray(code_i16, dtype=np.int16)
+    shifts = np.ascontiguousarray(shifts, dtype=np.float32)
+    out = np.zeros(2 * len(shifts), dtype=np.int16)
+    f = C.c_float
+    rc = ref().ref_mc_16sc(sig.ctypes.data_as(C.c_void_p), len(sig) // 2, code.ctypes.data_as(C.c_void_p), len(code) // 2, _p(shifts), len(shifts), f(rem_carr), f(phase_step),
+                           f(rem_code), f(code_step), out.ctypes.data_as(C.c_void_p))
+    assert rc == 0
+    return (out[0::2].astype(np.float32) + 1j * out[1::2].astype(np.float32)).astype(np.complex64)
+
+
 def mc_real_codes_f64(sig, code, shifts, rem_carr, phase_step, rem_code, code_step, mimic_inc=False):
     sig = np.ascontiguousarray(sig, dtype=np.complex64)
     code = np.ascontiguousarray(code, dtype=np.float32)

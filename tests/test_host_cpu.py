@@ -85,6 +85,18 @@ def test_acq_conf_derived_params():
     # pfa <= 0 disables CFAR; pfa2 falls back to pfa (acq_conf.cc:73-90)
     kv = H.kv(H.lib().gb200h_acq_conf(b"GNSS-SDR.internal_fs_sps=25000000\nA.item_type=cshort\n", b"A", 1.023e6, 1e6, 1))
     assert int(kv["use_CFAR_algorithm_flag"]) == 0 and int(kv["it_size"]) == 4 and int(kv["samples_per_chip"]) == 25
+    # the per-signal constants the four adapters hand to SetFromConfiguration (chip rate, optimum resampled rate, ms per code):
+    # Galileo E1 at 4 MS/s (C2): 4 ms code -> sampled_ms snaps to a multiple of 4, samples_per_code = 16000, 4 samples per chip
+    kv = H.kv(H.lib().gb200h_acq_conf(b"GNSS-SDR.internal_fs_sps=4000000\nA.coherent_integration_time_ms=4\nA.bit_transition_flag=true\n", b"A", 1.023e6, 2e6, 4))
+    assert int(kv["sampled_ms"]) == 4 and abs(float(kv["samples_per_code"]) - 16000.0) < 0.01 and int(kv["samples_per_chip"]) == 4 and int(kv["bit_transition_flag"]) == 1
+    kv = H.kv(H.lib().gb200h_acq_conf(b"GNSS-SDR.internal_fs_sps=4000000\nA.coherent_integration_time_ms=3\n", b"A", 1.023e6, 2e6, 4))
+    assert int(kv["sampled_ms"]) == 4  # not a multiple of ms_per_code: reset to one code (acq_conf.cc:48-53)
+    # GPS L5 / Galileo E5a at 20 MS/s (C4): 10.23 Mchip/s -> 2 samples per chip, 20000 samples per code, 20 dwells
+    kv = H.kv(H.lib().gb200h_acq_conf(b"GNSS-SDR.internal_fs_sps=20000000\nA.max_dwells=20\nA.pfa=0.01\n", b"A", 10.23e6, 1e7, 1))
+    assert int(kv["samples_per_chip"]) == 2 and abs(float(kv["samples_per_code"]) - 20000.0) < 0.01 and int(kv["max_dwells"]) == 20 and int(kv["use_CFAR_algorithm_flag"]) == 1
+    # automatic resampler: fs 20 MS/s over the 10 MS/s optimum -> decimation 2 (acq_conf.cc:92-107)
+    kv = H.kv(H.lib().gb200h_acq_conf(b"GNSS-SDR.internal_fs_sps=20000000\nGNSS-SDR.use_acquisition_resampler=true\n", b"A", 10.23e6, 1e7, 1))
+    assert int(kv["resampled_fs"]) == 10000000 and float(kv["resampler_ratio"]) == 2.0
     # unknown item type throws std::invalid_argument like the reference (acq_conf.cc:28-31)
     kv = H.kv(H.lib().gb200h_acq_conf(b"A.item_type=bogus\n", b"A", 1.023e6, 1e6, 1))
     assert "invalid_argument" in kv
@@ -95,6 +107,9 @@ def test_factory_strings():
     assert f(CONF_C1, "Tracking_1C").startswith("GPS_L1_CA_DLL_PLL_Tracking_B200;item_size=8;role=Tracking_1C")
     assert f(CONF_C1, "Acquisition_1C").startswith("GPS_L1_CA_PCPS_Acquisition_B200")
     assert f("T.implementation=Galileo_E1_DLL_PLL_VEML_Tracking_B200\nT.item_type=cshort\n", "T").startswith("Galileo_E1_DLL_PLL_VEML_Tracking_B200;item_size=4")
+    # the four acquisition adapters (gnss_block_factory.cc GetAcqBlock chain): GPS L1 C/A, Galileo E1, GPS L5I, Galileo E5a
+    for impl in ("GPS_L1_CA_PCPS_Acquisition_B200", "Galileo_E1_PCPS_Ambiguous_Acquisition_B200", "GPS_L5i_PCPS_Acquisition_B200", "Galileo_E5a_Pcps_Acquisition_B200"):
+        assert f(f"A.implementation={impl}\n", "A").startswith(impl + ";acquisition")
     assert f("T.implementation=GPS_L1_CA_DLL_PLL_Tracking\n", "T") == ""  # the reference's own string is not ours
     # unknown item type -> item_size 0, which makes Channel::connect throw (channel.cc:118-122); Dll_Pll_Conf first resets it to gr_complex
     assert "item_size=8" in f("T.implementation=GPS_L5_DLL_PLL_Tracking_B200\nT.item_type=bogus\n", "T")

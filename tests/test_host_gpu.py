@@ -305,3 +305,40 @@ def test_two_bit_packed_stream_tracks_like_its_unpacked_bytes():
     assert len(ra) > 50 and sa["state"] == 4 and abs(sa["carrier_doppler_hz"] - doppler) < 5.0, sa
     assert ra.tobytes() == rb.tobytes()
     assert sa == sb
+
+
+MIXED = """
+GNSS-SDR.internal_fs_sps=4000000
+Tracking_1C.implementation=GPS_L1_CA_DLL_PLL_Tracking_B200
+Tracking_1C.item_type=gr_complex
+Tracking_1B.implementation=Galileo_E1_DLL_PLL_VEML_Tracking_B200
+Tracking_1B.item_type=gr_complex
+Tracking_1B.track_pilot=true
+Tracking_L5.implementation=GPS_L5_DLL_PLL_Tracking_B200
+Tracking_L5.item_type=gr_complex
+Tracking_5X.implementation=Galileo_E5a_DLL_PLL_Tracking_B200
+Tracking_5X.item_type=gr_complex
+Tracking_5X.stream_id=7
+"""
+
+
+def test_engine_is_per_stream_and_sized_for_the_band():
+    """the per-GPU engine is keyed on (device, item type, input stream) and sized for the band's longest code
+    period, so (a) a GPS L1 channel that starts first no longer locks a Galileo E1 channel (4 x longer windows) out of the shared
+    L1-band engine, and (b) an L5 / E5a channel never shares the L1 band's ring; a failed attach is an error, not a silent ch = -1."""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    probe = lambda ra, pa, rb, pb: H.kv(H.lib().gb200h_engine_probe(MIXED.encode(), ra.encode(), pa, rb.encode(), pb))
+    # (a) L1 first, then E1: one engine (same stream), both attached, windows of 2 x 16000 samples fit
+    r = probe("Tracking_1C", 3, "Tracking_1B", 11)
+    assert "error" not in r, r
+    assert int(r["same"]) == 1 and int(r["stream_a"]) == int(r["stream_b"]) == 0
+    assert int(r["slot_a"]) >= 0 and int(r["slot_b"]) >= 0 and int(r["slot_a"]) != int(r["slot_b"])
+    assert int(r["max_block"]) >= 2 * 16000
+    # (b) L1 band and L5 band: two engines, two rings
+    r = probe("Tracking_1C", 3, "Tracking_L5", 5)
+    assert "error" not in r, r
+    assert int(r["same"]) == 0 and int(r["stream_a"]) == 0 and int(r["stream_b"]) == 1
+    # an explicit <role>.stream_id wins over the band default
+    r = probe("Tracking_L5", 5, "Tracking_5X", 9)
+    assert "error" not in r, r
+    assert int(r["same"]) == 0 and int(r["stream_b"]) == 7

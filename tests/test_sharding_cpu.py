@@ -55,6 +55,22 @@ def test_antenna_shard_keeps_a_stream_on_one_gpu():
     assert sorted(allch) == list(range(9))
 
 
+def test_merge_cells_tie_rules_and_statistic():
+    """merge_cells = acq_stats_kernel's arithmetic on the host: first bin among equal maxima, the opposite bin's sum as input power"""
+    v = np.zeros((2, 8), np.float32)
+    i = np.zeros((2, 8), np.int32)
+    s = np.ones((2, 8), np.float32) * 100
+    v[0, 2] = v[0, 5] = 7.0
+    i[0, 2], i[0, 5] = 40, 3
+    s[0, 6] = 50.0   # opposite of bin 2 in an 8-bin grid
+    r = S.merge_cells(v, i, s, neff=10, num_dwells=1, doppler_base=-1000, doppler_step=250, samples_per_code=16.0)
+    assert (r[0]["indext"], r[0]["doppler_index"], r[0]["doppler_hz"]) == (40, 2, -500)
+    assert r[0]["input_power"] == np.float32(np.float64(np.float32(50.0) / np.float32(10)) / 2.0) and r[0]["test_statistics"] == np.float32(7.0) / np.float32(2.5)
+    assert r[0]["acq_delay_samples"] == 8.0
+    # an all-zero grid leaves (0, 0) like the reference's strict '>' from grid_maximum = 0 (pcps_acquisition.cc:505-514)
+    assert (r[1]["indext"], r[1]["doppler_index"], r[1]["peak"]) == (0, 0, 0.0)
+
+
 def test_prn_shard_and_doppler_tiles():
     prns = list(range(1, 33))
     parts = [S.prn_shard(prns, r, 3) for r in range(3)]
@@ -142,6 +158,13 @@ def _worker(rank, world, port, outdir):
         tie = np.zeros((conf.num_doppler_bins, N), dtype=np.float32)
         tie[3, 77] = tie[30, 5] = 9.0
         tied = S.merge_doppler_tiles(dist, tie[lo:hi], lo, conf.num_doppler_bins, N)
+        # the form the GPUs use (bench.py --gpus N): every rank publishes (max, first index, sum) per (PRN, bin) of ITS tile
+        # (gb200_acq_read_cells), one all-gather, then the reference's first-bin / first-index rule on the full table
+        tile = grid[lo:hi]
+        v, im, sm = tile.max(axis=1)[None, :], tile.argmax(axis=1).astype(np.int32)[None, :], tile.sum(axis=1, dtype=np.float32)[None, :]
+        fv, fi, fs_ = S.gather_cell_tiles(dist, v, im, sm, world)
+        cells = S.merge_cells(fv, fi, fs_, N, 1, -conf.doppler_max, conf.doppler_step, conf.samples_per_code)[0]
+        np.save(os.path.join(outdir, f"cells{rank}.npy"), np.array([cells["indext"], cells["doppler_index"], cells["doppler_hz"], cells["peak"], cells["acq_delay_samples"]]))
         # timing plumbing: the slowest rank defines the step
         slow = S.reduce_max(dist, 1.0 + rank)
         dist.barrier()
@@ -179,6 +202,7 @@ def test_world_size_2_gloo_matches_single_process():
             assert p.exitcode == 0
         trk, acq = np.load(os.path.join(d, "trk.npy")), np.load(os.path.join(d, "acq.npy"))
         tiled = [np.load(os.path.join(d, f"tiled{r}.npy")) for r in range(world)]
+        cells = [np.load(os.path.join(d, f"cells{r}.npy")) for r in range(world)]
     prns, codes, x, t = _scene()
     one_trk = _track(codes, x, t, np.arange(len(t["off"])))
     one_acq = _acquire(x, prns)
@@ -195,6 +219,9 @@ def test_world_size_2_gloo_matches_single_process():
         assert abs(v[2] - r.test_statistics) <= 1e-5 * r.test_statistics
         assert (int(v[3]), int(v[4])) == (77, 3)
         assert v[5] == 2.0
+    for c in cells:  # the all-gathered cell tables give the oracle's answer on every rank, peak value bit for bit
+        assert (int(c[0]), int(c[1]), int(c[2])) == (r.indext, r.doppler_index, r.doppler_hz)
+        assert np.float32(c[3]) == np.float32(r.peak) and np.float32(c[4]) == np.float32(r.acq_delay_samples)
 
 
 def test_bench_reference_arm_runs_on_rank_0_only():

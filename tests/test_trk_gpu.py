@@ -112,6 +112,45 @@ def test_integer_iq_ingest(iq_dtype, np_t, scale):
     eng.close()
 
 
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("n,nt,amp", [(2048, 3, 12.0), (4096, 3, 6.0), (8111, 3, 3.0), (4000, 5, 6.0)])
+def test_int16_path_vs_reference_16ic_kernels(n, nt, amp):
+    """a6: the reference's own int16 path — Cpu_Multicorrelator_16sc (cpu_multicorrelator_16sc.cc:77-91) over
+    volk_gnsssdr_16ic_xn_resampler_16ic_xn (:60-78) and volk_gnsssdr_16ic_x2_rotator_dot_prod_16ic_xn (:66-102), compiled from the
+    reference into oracle/_ref — against the engine's int16 ingest.  The reference rounds every rotated sample to int16 (rintf) and
+    accumulates in SATURATING int16, so the comparison is at the reference's own QA tolerance for its 16-bit kernels, +-16 LSB absolute
+    (volk_gnsssdr/lib/kernel_tests.h:49,101-102), on inputs small enough that the int16 accumulators do not saturate; the engine
+    accumulates in fp32 and is additionally held to 1e-4 of the float64 truth."""
+    rng = np.random.default_rng(n + nt)
+    L = 1023
+    code = rng.choice([-1.0, 1.0], L).astype(np.float32)
+    shifts = _taps(nt, 0.5)
+    code_step, rem_code, rem_carr, phase_step = 0.3, 0.4, 0.25, 0.01
+    # a signal-bearing block: the code itself under a carrier, plus noise, in int16 LSBs
+    idx = O.resampler_index(rem_code, code_step, np.zeros(1, np.float32), L, n)[0]
+    carrier = np.exp(1j * (rem_carr + phase_step * np.arange(n)))
+    x = amp * code[idx] * carrier + amp * 0.7 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))
+    raw = np.empty(2 * n, np.int16)
+    raw[0::2] = np.rint(x.real)
+    raw[1::2] = np.rint(x.imag)
+    sig = (raw[0::2].astype(np.float32) + 1j * raw[1::2].astype(np.float32)).astype(np.complex64)
+    code16 = np.zeros(2 * L, np.int16)
+    code16[0::2] = code.astype(np.int16)
+    ref16 = O.mc_16sc(raw, code16, shifts, rem_carr, phase_step, rem_code, code_step)
+    assert np.max(np.abs(ref16.real)) < 32000 and np.max(np.abs(ref16.imag)) < 32000, "test input saturates the reference's int16 accumulators"
+    eng = _engine(max_channels=1, max_code_len=L, iq_dtype=1, ring_samples=4 * 8192, max_block=8192)
+    eng.set_code(0, code)
+    first = eng.push_iq(raw)
+    got = eng.correlate(eng.make_cmds([0], [first], [n], shifts[None, :], [rem_carr], [phase_step], [rem_code], [code_step]))[0]
+    eng.close()
+    r64 = O.mc_real_codes_f64(sig, code, shifts, rem_carr, phase_step, rem_code, code_step, mimic_inc=True)
+    assert rel_err(got, r64) < TOL
+    # per-sample rintf noise of the reference: ~0.29 LSB rms per component and sample -> sqrt(n) * 0.29 LSB on a sum; +-16 LSB is its QA bound
+    d = got - ref16
+    assert max(np.max(np.abs(d.real)), np.max(np.abs(d.imag))) <= 16.0 + 3.0 * 0.29 * np.sqrt(n), (got, ref16)
+    assert abs(np.max(np.abs(ref16)) - np.max(np.abs(got))) / np.max(np.abs(got)) < 2e-2
+
+
 def test_complex_code_sibling():
     """Cpu_Multicorrelator (cpu_multicorrelator.cc:73-100): complex code table."""
     rng = np.random.default_rng(5)
@@ -201,7 +240,8 @@ def test_run_based_kernel_many_channels(fs, L, chip_rate, nt, spacing, iq_dtype,
     # loses phase increments below one ulp at tiny Doppler): wherever it disagrees with the GPU by more than TOL, the float64
     # truth decides, and the GPU must be within TOL of it
     suspects = np.nonzero(err32 >= TOL)[0]
-    assert len(suspects) < nch // 4
+    print(f"[noise-only] {eng.last_kernel}: {len(suspects)} of {nch} channels differ from the sequential fp32 reference by >= 1e-4 (worst {np.max(err32):.2e})")
+    assert len(suspects) <= nch // 20
     for c in list(suspects) + list(rng.choice(nch, 48, replace=False)):
         r64 = O.mc_real_codes_f64(ring[offs[c]:offs[c] + lens[c]], codes[c], shifts[c], remc[c], step[c], remcode[c], cstep[c], mimic_inc=True)
         assert rel_err(got[c], r64) < TOL, (c, eng.last_kernel)
@@ -209,6 +249,80 @@ def test_run_based_kernel_many_channels(fs, L, chip_rate, nt, spacing, iq_dtype,
     again = eng.collect()[:, :nt]
     assert np.array_equal(again.view(np.uint32), got.view(np.uint32))
     eng.close()
+
+
+@pytest.mark.parametrize("fs,L,chip_rate,nt,spacing,iq_dtype,nch", [
+    (25e6, 1023, 1.023e6, 11, 0.1, 0, 1024),      # C3 GPS L1, the benched shape
+    (100e6, 1023, 1.023e6, 11, 0.05, 2, 640),     # C5 int8
+    (4e6, 1023, 1.023e6, 3, 0.5, 0, 512),         # C1 (general kernel today: code step 0.256 per sample)
+    (20e6, 10230, 10.23e6, 11, 0.1, 0, 512),      # C4 L5 / E5a
+])
+def test_signal_bearing_many_channels_hard_gate(fs, L, chip_rate, nt, spacing, iq_dtype, nch):
+    """north_star's gate on SIGNAL-BEARING IF, hard: every channel within 1e-4 (relative to max_t |out_t|) of the fp32 oracle — the
+    restatement that tests/test_oracle_pin.py pins bit-for-bit to the reference's compiled objects — AND of the float64 truth, AND
+    within the reference's own QA tolerance (1e-3, volk_gnsssdr/lib/kernel_tests.h:43) of the reference's generic protokernels run
+    directly from oracle/_ref.  32 satellites at 47-53 dB-Hz in one stream; channel c tracks satellite c mod 32 within +-0.15 chip and
+    +-15 Hz of the truth, so |prompt| is large against the noise and nothing is left to a soft gate."""
+    rng = np.random.default_rng(int(fs / 1e6) * 7 + nt)
+    n = int(round(fs * L / chip_rate))
+    nsat = 32
+    codes_sat = rng.choice([-1.0, 1.0], (nsat, L)).astype(np.float32)
+    dopp = rng.uniform(-5e3, 5e3, nsat)
+    delay = rng.uniform(0, L, nsat)
+    ph0 = rng.uniform(0, 2 * np.pi, nsat)
+    cn0 = rng.uniform(47, 53, nsat)
+    total = 2 * n + 64
+    ring = O.gen_if(total, 0, fs, codes_sat, dopp, delay, ph0, cn0, f_chip=chip_rate, seed=5)
+    if iq_dtype == 0:
+        raw = ring
+    else:
+        scale = 25.0 * np.sqrt(2.0)
+        rawi = np.empty(2 * total, np.int8)
+        rawi[0::2] = np.clip(np.rint(ring.real * scale), -127, 127)
+        rawi[1::2] = np.clip(np.rint(ring.imag * scale), -127, 127)
+        ring = (rawi[0::2].astype(np.float32) + 1j * rawi[1::2].astype(np.float32)).astype(np.complex64)
+        raw = rawi
+    sat = np.arange(nch) % nsat
+    codes = codes_sat[sat]
+    # like a tracking loop, every window starts at the first sample of a code period of its satellite (orc_gen_if: chip index =
+    # floor(t f_chip (1 + fd / fc) - delay)), so |rem_code_phase| stays below a chip; the replica is off by up to +-0.15 chip
+    rate = chip_rate * (1 + dopp[sat] / 1575.42e6)
+    offs = np.ceil((delay[sat] + L * rng.integers(0, 2, nch) * (delay[sat] + L < 0.9 * rate * n / fs)) / rate * fs).astype(np.int64)
+    lens = n + rng.integers(-1, 2, nch)
+    f_d = dopp[sat] + rng.uniform(-15, 15, nch)
+    t0 = offs / fs
+    code_ph = (t0 * rate - delay[sat]) % L
+    code_ph = np.where(code_ph > L / 2, code_ph - L, code_ph) + rng.uniform(-0.15, 0.15, nch)
+    remcode = (-code_ph).astype(np.float32)            # index law: floor(step n + shift - rem)
+    cstep = (chip_rate * (1 + dopp[sat] / 1575.42e6) / fs).astype(np.float32)
+    step = (2 * np.pi * f_d / fs).astype(np.float32)
+    remc = ((2 * np.pi * dopp[sat] * t0 + ph0[sat] + rng.uniform(-0.3, 0.3, nch)) % (2 * np.pi)).astype(np.float32)
+    shifts = np.tile(_taps(nt, spacing), (nch, 1))
+    eng = _engine(max_channels=nch, max_code_len=L, iq_dtype=iq_dtype, ring_samples=2 * total, max_block=n + 8, max_cmds=nch)
+    for c in range(nch):
+        eng.set_code(c, codes[c])
+    first = eng.push_iq(raw)
+    got = eng.correlate(eng.make_cmds(np.arange(nch), offs + first, lens, shifts, remc, step, remcode, cstep))
+    kernel = eng.last_kernel
+    eng.close()
+    ref32 = O.mc_batch(ring, offs, lens, codes, shifts, remc, step, remcode, cstep)
+    scale = np.max(np.abs(ref32), axis=1)
+    # the satellites are really there: |prompt| well above the noise-only level sqrt(n) * sigma
+    sigma = np.sqrt(np.mean(np.abs(ring) ** 2))
+    assert np.median(scale) > 4 * np.sqrt(n) * sigma, (np.median(scale), np.sqrt(n) * sigma)
+    err32 = np.max(np.abs(got - ref32), axis=1) / scale
+    assert np.max(err32) < TOL, (kernel, int(np.argmax(err32)), float(np.max(err32)))
+    worst64 = worstref = 0.0
+    for c in range(nch):
+        w = ring[offs[c]:offs[c] + lens[c]]
+        r64 = O.mc_real_codes_f64(w, codes[c], shifts[c], remc[c], step[c], remcode[c], cstep[c], mimic_inc=True)
+        worst64 = max(worst64, rel_err(got[c], r64))
+        if O.ref_available() and c % 4 == 0:
+            rr = O.mc_real_codes(w, codes[c], shifts[c], remc[c], step[c], remcode[c], cstep[c], impl="ref")
+            worstref = max(worstref, rel_err(got[c], rr))
+    print(f"[hard gate] {kernel}: worst vs fp32 oracle {np.max(err32):.2e}, vs float64 {worst64:.2e}, vs reference generic protokernels {worstref:.2e}")
+    assert worst64 < TOL, (kernel, worst64)
+    assert worstref < TOL, (kernel, worstref)
 
 
 @pytest.mark.parametrize("n,fs,nt,spacing,phase_rate,code_rate", [
