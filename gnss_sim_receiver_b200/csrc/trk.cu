@@ -36,12 +36,9 @@ struct gb200_trk
     float* d_partials{nullptr};
     unsigned* d_counters{nullptr};
     size_t partial_ctas{0};
-    TrkGroup* h_groups{nullptr};  // pinned
-    TrkGroup* d_groups{nullptr};
-    std::vector<std::pair<long long, int>> order;  // scratch of plan_run_kernel
     bool scan_ok{false};                            // all commands of the call pass run_applicable (set with the preprocessing)
     float scan_min_step{0}, scan_max_step{0};
-    int last_path{0}, last_groups{0}, last_R{16}, last_G{4};  // path 0: chunked kernel, 1: run-based kernel, 2: high-dynamics kernel
+    int last_path{0}, last_R{18};  // path 0: chunked kernel, 1: run-based kernel, 2: high-dynamics kernel
     // last enqueued launch (for collect / replay)
     int last_n{0}, last_T{0}, last_chunks{0}, last_cplx{0};
     size_t last_smem{0};
@@ -107,28 +104,15 @@ int padded_taps(int t)
     return 16;
 }
 
-template <int T, int IQ, int CH, int G>
+template <int T, int IQ, int CH>
 cudaError_t launch_run_one(gb200_trk* h)
 {
-    constexpr int EB = IqRow<IQ>::EB;
-    constexpr int R = CH * 16 / EB;
-    const size_t smem = (size_t)TRK2_THREADS * R * EB + (size_t)(R + 2) * TRK2_THREADS * sizeof(float2) + (size_t)G * TRK2_TAB * sizeof(float2);
-    cudaError_t e = cudaFuncSetAttribute(trk_run_kernel<T, IQ, CH, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = trk2_smem_bytes<IQ, CH>();
+    cudaError_t e = cudaFuncSetAttribute(trk_run_kernel<T, IQ, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    trk_run_kernel<T, IQ, CH, G><<<h->last_groups, TRK2_THREADS, smem, h->stream>>>(h->d_cmds, h->last_G == 1 ? nullptr : h->d_groups, reinterpret_cast<const unsigned char*>(h->d_ring), h->d_out);
+    trk_run_kernel<T, IQ, CH><<<h->last_n, TRK2_THREADS, smem, h->stream>>>(h->d_cmds, reinterpret_cast<const unsigned char*>(h->d_ring), h->d_out);
     count_launch();
     return cudaGetLastError();
-}
-
-template <int T, int IQ, int CH>
-cudaError_t launch_run_G(gb200_trk* h)
-{
-    switch (h->last_G)
-        {
-        case 4: return launch_run_one<T, IQ, CH, 4>(h);
-        case 2: return launch_run_one<T, IQ, CH, 2>(h);
-        default: return launch_run_one<T, IQ, CH, 1>(h);
-        }
 }
 
 // run lengths: an odd number of 16-byte chunks (see trk_kernel2.cuh); long and short variant per sample type
@@ -137,7 +121,7 @@ cudaError_t launch_run_RG(gb200_trk* h)
 {
     constexpr int CH_LONG = IQ == GB200_IQ_CF32 ? 9 : IQ == GB200_IQ_CS16 ? 5 : 3;
     constexpr int CH_SHORT = IQ == GB200_IQ_CF32 ? 5 : IQ == GB200_IQ_CS16 ? 3 : 1;
-    return h->last_R == trk_run_len(IQ, true) ? launch_run_G<T, IQ, CH_LONG>(h) : launch_run_G<T, IQ, CH_SHORT>(h);
+    return h->last_R == trk_run_len(IQ, true) ? launch_run_one<T, IQ, CH_LONG>(h) : launch_run_one<T, IQ, CH_SHORT>(h);
 }
 
 template <int IQ>
@@ -243,8 +227,6 @@ int gb200_trk_create(const gb200_trk_config* cfg, gb200_trk** out)
     // + RING_SLACK: the run-based kernel stages whole tiles, which may extend past the last window (masked, but must be mapped)
     GB_CUDA(cudaMalloc(&h->d_ring, (size_t)(cfg->ring_samples + cfg->max_block + RING_SLACK) * h->elem_bytes));
     GB_CUDA(cudaMemsetAsync(h->d_ring, 0, (size_t)(cfg->ring_samples + cfg->max_block + RING_SLACK) * h->elem_bytes, h->stream));
-    GB_CUDA(cudaMallocHost(&h->h_groups, (size_t)cfg->max_cmds * sizeof(TrkGroup)));
-    GB_CUDA(cudaMalloc(&h->d_groups, (size_t)cfg->max_cmds * sizeof(TrkGroup)));
     GB_CUDA(cudaMalloc(&h->d_codes, (size_t)cfg->max_channels * cfg->max_code_len * sizeof(float2)));
     h->code_len.assign(cfg->max_channels, 0);
     h->code_cplx.assign(cfg->max_channels, 0);
@@ -276,8 +258,6 @@ int gb200_trk_destroy(gb200_trk* h)
     cudaFreeHost(h->h_out);
     cudaFree(h->d_partials);
     cudaFree(h->d_counters);
-    cudaFreeHost(h->h_groups);
-    cudaFree(h->d_groups);
     cudaEventDestroy(h->ev0);
     cudaEventDestroy(h->ev1);
     cudaStreamDestroy(h->stream);

@@ -19,6 +19,60 @@ constexpr int TRK_THREADS = 128;
 constexpr int TRK_RESEED = 16;  // exact phasor re-seed period (in per-thread samples)
 constexpr int TRK_OUT_STRIDE = GB200_MAX_TAPS;
 
+// ---- packed f32x2 helpers: a pair lives in one 64-bit register pair; ptxas folds scalar broadcasts ({a, a}) and swaps into operand
+// selectors (R.F32 / .LO_HI), so building those pairs costs no instruction
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void up2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ void st_shared_b64(unsigned addr, f32x2 v) { asm volatile("st.shared.b64 [%0], %1;" ::"r"(addr), "l"(v) : "memory"); }
+__device__ __forceinline__ f32x2 ld_shared_b64(unsigned addr)
+{
+    f32x2 v;
+    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ float2 ld_shared_f2(unsigned addr)
+{
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ f32x2 add2_rd(f32x2 a, f32x2 b)  // round towards -inf, like __fadd_rd in both lanes
+{
+    f32x2 r;
+    asm("add.rm.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
 // host-preprocessed command, one per Carrier_wipeoff_multicorrelator_resampler call
 struct TrkDevCmd
 {
@@ -111,9 +165,11 @@ __global__ void __launch_bounds__(TRK_THREADS) trk_correlate_kernel(const TrkDev
     const int n0 = blockIdx.x * chunk_len;
     const int n1 = min(n, n0 + chunk_len);
 
-    float acc_re[T], acc_im[T];
+    // accumulators as packed (re, im) pairs; taps are evaluated two at a time (f32x2 index law), see trk_kernel2.cuh for the packing rules
+    constexpr int TP = (T + 1) / 2;
+    f32x2 acc[T];
 #pragma unroll
-    for (int t = 0; t < T; t++) acc_re[t] = acc_im[t] = 0.0f;
+    for (int t = 0; t < T; t++) acc[t] = 0ull;
 
     if (n0 < n1)
         {
@@ -138,13 +194,15 @@ __global__ void __launch_bounds__(TRK_THREADS) trk_correlate_kernel(const TrkDev
             }
             __syncthreads();
 
-            float sh[T];
+            f32x2 shp[TP];
 #pragma unroll
-            for (int t = 0; t < T; t++) sh[t] = c.shifts[t];
+            for (int p = 0; p < TP; p++) shp[p] = pk2(c.shifts[2 * p], c.shifts[2 * p + 1 < T ? 2 * p + 1 : T - 1]);
             // floor(x) for |x| < 2^22 as the low mantissa bits of RD(x + 1.5*2^23)
             const float MAGIC = 12582912.0f;
+            const f32x2 MG = pk2(MAGIC, MAGIC), REM = pk2(rem, rem);
             const int bias = 0x4B400000 + idx_lo;
             const float2 stp = trk_phasor(c.du * (unsigned long long)TRK_THREADS);
+            const f32x2 stpx = pk2(stp.x, stp.x), stpy = pk2(stp.y, stp.y);
             float nf = (float)(n0 + tid);
             for (int base = n0 + tid; base < n1; base += TRK_THREADS * TRK_RESEED)
                 {
@@ -155,35 +213,48 @@ __global__ void __launch_bounds__(TRK_THREADS) trk_correlate_kernel(const TrkDev
                             const int s = base + k * TRK_THREADS;
                             if (s >= n1) break;
                             const float2 x = trk_load_iq<IQ>(c.iq, s);
-                            const float wr = x.x * ph.x - x.y * ph.y;
-                            const float wi = x.x * ph.y + x.y * ph.x;
-                            const float pr = ph.x * stp.x - ph.y * stp.y;
-                            const float pi = ph.x * stp.y + ph.y * stp.x;
-                            ph.x = pr;
-                            ph.y = pi;
-                            const float a = __fmul_rn(step, nf);
-                            nf += (float)TRK_THREADS;
-#pragma unroll
-                            for (int t = 0; t < T; t++)
+                            const f32x2 A = pk2(ph.x, ph.y), B = pk2(-ph.y, ph.x);               // ph and j * ph
+                            const f32x2 W = fma2(pk2(x.y, x.y), B, mul2(pk2(x.x, x.x), A));      // wiped sample x * ph
+                            up2(fma2(stpy, B, mul2(stpx, A)), ph.x, ph.y);                        // ph *= exp(j 2 pi du 128)
+                            f32x2 JW = 0ull;
+                            if (CPLX)
                                 {
-                                    const float xi = __fsub_rn(__fadd_rn(a, sh[t]), rem);
-                                    const int j = __float_as_int(__fadd_rd(xi, MAGIC)) - bias;
-                                    if (CPLX)
+                                    float wr, wi;
+                                    up2(W, wr, wi);
+                                    JW = pk2(-wi, wr);
+                                }
+                            const float a = __fmul_rn(step, nf);  // the reference's law: rounded product, rounded add, rounded sub
+                            nf += (float)TRK_THREADS;
+                            const f32x2 A0 = pk2(a, a);
+#pragma unroll
+                            for (int p = 0; p < TP; p++)
+                                {
+                                    float m0, m1;
+                                    up2(add2_rd(sub2(add2(A0, shp[p]), REM), MG), m0, m1);
+#pragma unroll
+                                    for (int q = 0; q < 2; q++)
                                         {
-                                            const float2 cc = reinterpret_cast<const float2*>(s_tab)[j];
-                                            acc_re[t] += wr * cc.x - wi * cc.y;
-                                            acc_im[t] += wr * cc.y + wi * cc.x;
-                                        }
-                                    else
-                                        {
-                                            const float cc = s_tab[j];
-                                            acc_re[t] += wr * cc;
-                                            acc_im[t] += wi * cc;
+                                            const int t = 2 * p + q;
+                                            if (t >= T) continue;
+                                            const int j = __float_as_int(q ? m1 : m0) - bias;
+                                            if (CPLX)
+                                                {
+                                                    const float2 cc = reinterpret_cast<const float2*>(s_tab)[j];
+                                                    acc[t] = fma2(pk2(cc.y, cc.y), JW, fma2(pk2(cc.x, cc.x), W, acc[t]));
+                                                }
+                                            else
+                                                {
+                                                    const float cc = s_tab[j];
+                                                    acc[t] = fma2(pk2(cc, cc), W, acc[t]);
+                                                }
                                         }
                                 }
                         }
                 }
         }
+    float acc_re[T], acc_im[T];
+#pragma unroll
+    for (int t = 0; t < T; t++) up2(acc[t], acc_re[t], acc_im[t]);
 
     // block reduce: warp shuffle, then across the 4 warps through shared memory
 #pragma unroll

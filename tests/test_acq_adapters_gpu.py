@@ -88,8 +88,9 @@ def test_gps_l5i_adapter_from_conf_with_dwells():
         O.ref().ref_gps_l5i_code_gen_complex_sampled(want.ctypes.data_as(O.f32p), 20000, prn, int(fs))
         assert np.array_equal(local.view(np.float32), want)
     base = dict(f_chip=10.23e6, doppler=doppler, delay=delay, phase=2.2)
-    # too weak for one 1 ms dwell at pfa 1e-4 over 1.6 M cells, found after the dwells accumulate (pcps_acquisition.cc:795-815)
-    x = S.synth_if(5 * 20000, fs, [dict(table=S.l5_table(prn), cn0=39.5, weight=np.sqrt(0.5), **base), dict(table=1j * S.l5_table(prn, q=True), cn0=39.5, weight=np.sqrt(0.5), **base)],
+    # too weak for one 1 ms dwell at pfa 1e-4 over 1.6 M cells (statistic ~ 2 d (1 + SNR) after d dwells against a threshold of ~72),
+    # found once the dwells accumulate (pcps_acquisition.cc:795-815)
+    x = S.synth_if(5 * 20000, fs, [dict(table=S.l5_table(prn), cn0=46.0, weight=np.sqrt(0.5), **base), dict(table=1j * S.l5_table(prn, q=True), cn0=46.0, weight=np.sqrt(0.5), **base)],
                    seed=62, f_carrier=1176.45e6)
     consumed = a.work(x, chunk=20000)
     s = a.status()
@@ -113,7 +114,7 @@ def test_galileo_e5a_adapter_from_conf(opts, sig):
         want = np.zeros(2 * 20000, np.float32)
         O.ref().ref_galileo_e5_a_code_gen_complex_sampled(want.ctypes.data_as(O.f32p), 20000, prn, sig.encode(), int(fs), 0)
         assert np.array_equal(local.view(np.float32), want)
-    x = S.synth_if(2 * 20000, fs, [dict(table=S.e5a_primary(prn, "5X"), f_chip=10.23e6, doppler=doppler, delay=delay, cn0=49.0, phase=0.4, weight=np.sqrt(0.5))], seed=63, f_carrier=1176.45e6)
+    x = S.synth_if(2 * 20000, fs, [dict(table=S.e5a_primary(prn, "5X"), f_chip=10.23e6, doppler=doppler, delay=delay, cn0=53.0, phase=0.4, weight=np.sqrt(0.5))], seed=63, f_carrier=1176.45e6)
     consumed = a.work(x, chunk=5000)
     s = a.status()
     conf, ro = _oracle(fs, 20000, 20000, float(np.float32(np.float32(fs) * np.float32(0.001))), 2, local, [x[:20000]])
