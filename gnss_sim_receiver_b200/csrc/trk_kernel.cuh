@@ -16,7 +16,8 @@
 namespace gb200
 {
 constexpr int TRK_THREADS = 128;
-constexpr int TRK_RESEED = 16;  // exact phasor re-seed period (in per-thread samples)
+constexpr int TRK_RESEED = 16;    // exact phasor re-seed period (in per-thread samples)
+constexpr int TRK_PREFETCH = 8;   // samples a thread fetches ahead of the arithmetic (general kernel)
 constexpr int TRK_OUT_STRIDE = GB200_MAX_TAPS;
 
 // ---- packed f32x2 helpers: a pair lives in one 64-bit register pair; ptxas folds scalar broadcasts ({a, a}) and swaps into operand
@@ -64,6 +65,12 @@ __device__ __forceinline__ float2 ld_shared_f2(unsigned addr)
 {
     float2 v;
     asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ld_shared_f1(unsigned addr)
+{
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
     return v;
 }
 __device__ __forceinline__ f32x2 add2_rd(f32x2 a, f32x2 b)  // round towards -inf, like __fadd_rd in both lanes
@@ -200,21 +207,46 @@ __global__ void __launch_bounds__(TRK_THREADS) trk_correlate_kernel(const TrkDev
             // floor(x) for |x| < 2^22 as the low mantissa bits of RD(x + 1.5*2^23)
             const float MAGIC = 12582912.0f;
             const f32x2 MG = pk2(MAGIC, MAGIC), REM = pk2(rem, rem);
-            const int bias = 0x4B400000 + idx_lo;
-            const float2 stp = trk_phasor(c.du * (unsigned long long)TRK_THREADS);
+            // shared address of table entry j = bits(RD(x + MAGIC)) - bias:  tab_adj + ESZ * bits  (one multiply-add per tap)
+            constexpr unsigned ESZ = CPLX ? 8u : 4u;
+            const unsigned tab_adj = smem_u32(s_tab) - (unsigned)(0x4B400000 + idx_lo) * ESZ;
+            const unsigned long long u0 = c.u0, du = c.du;
+            const void* iq = c.iq;
+            const float2 stp = trk_phasor(du * (unsigned long long)TRK_THREADS);
             const f32x2 stpx = pk2(stp.x, stp.x), stpy = pk2(stp.y, stp.y);
             float nf = (float)(n0 + tid);
-            for (int base = n0 + tid; base < n1; base += TRK_THREADS * TRK_RESEED)
+            // samples of a thread are TRK_THREADS apart; they are fetched TRK_PREFETCH at a time, one group ahead of the arithmetic, so the
+            // L2 latency of a group is covered by the previous group's taps
+            float2 xn[TRK_PREFETCH];
+            auto fetch = [&](int first) {
+#pragma unroll
+                for (int k = 0; k < TRK_PREFETCH; k++)
+                    {
+                        const int s = first + k * TRK_THREADS;
+                        xn[k] = s < n1 ? trk_load_iq<IQ>(iq, s) : make_float2(0.0f, 0.0f);
+                    }
+            };
+            fetch(n0 + tid);
+            int since_seed = TRK_RESEED;
+            float2 ph = make_float2(1.0f, 0.0f);
+            for (int base = n0 + tid; base < n1; base += TRK_THREADS * TRK_PREFETCH)
                 {
-                    float2 ph = trk_phasor(c.u0 + c.du * (unsigned long long)base);
-#pragma unroll 4
-                    for (int k = 0; k < TRK_RESEED; k++)
+                    float2 x[TRK_PREFETCH];
+#pragma unroll
+                    for (int k = 0; k < TRK_PREFETCH; k++) x[k] = xn[k];
+                    if (base + TRK_THREADS * TRK_PREFETCH < n1) fetch(base + TRK_THREADS * TRK_PREFETCH);
+                    if (since_seed >= TRK_RESEED)
                         {
-                            const int s = base + k * TRK_THREADS;
-                            if (s >= n1) break;
-                            const float2 x = trk_load_iq<IQ>(c.iq, s);
+                            ph = trk_phasor(u0 + du * (unsigned long long)base);  // exact re-seed every TRK_RESEED samples of the thread
+                            since_seed = 0;
+                        }
+                    since_seed += TRK_PREFETCH;
+#pragma unroll
+                    for (int k = 0; k < TRK_PREFETCH; k++)
+                        {
+                            if (base + k * TRK_THREADS >= n1) break;  // (the table window only covers the chunk's own samples)
                             const f32x2 A = pk2(ph.x, ph.y), B = pk2(-ph.y, ph.x);               // ph and j * ph
-                            const f32x2 W = fma2(pk2(x.y, x.y), B, mul2(pk2(x.x, x.x), A));      // wiped sample x * ph
+                            const f32x2 W = fma2(pk2(x[k].y, x[k].y), B, mul2(pk2(x[k].x, x[k].x), A));  // wiped sample x * ph
                             up2(fma2(stpy, B, mul2(stpx, A)), ph.x, ph.y);                        // ph *= exp(j 2 pi du 128)
                             f32x2 JW = 0ull;
                             if (CPLX)
@@ -236,15 +268,15 @@ __global__ void __launch_bounds__(TRK_THREADS) trk_correlate_kernel(const TrkDev
                                         {
                                             const int t = 2 * p + q;
                                             if (t >= T) continue;
-                                            const int j = __float_as_int(q ? m1 : m0) - bias;
+                                            const unsigned addr = tab_adj + ESZ * (unsigned)__float_as_int(q ? m1 : m0);
                                             if (CPLX)
                                                 {
-                                                    const float2 cc = reinterpret_cast<const float2*>(s_tab)[j];
+                                                    const float2 cc = ld_shared_f2(addr);
                                                     acc[t] = fma2(pk2(cc.y, cc.y), JW, fma2(pk2(cc.x, cc.x), W, acc[t]));
                                                 }
                                             else
                                                 {
-                                                    const float cc = s_tab[j];
+                                                    const float cc = ld_shared_f1(addr);
                                                     acc[t] = fma2(pk2(cc, cc), W, acc[t]);
                                                 }
                                         }
