@@ -33,6 +33,29 @@ class TrkCmd(C.Structure):
                 ("shifts_chips", C.c_float * GB200_MAX_TAPS)]
 
 
+class LoopConfig(C.Structure):
+    """gb200_loop_config (include/gnss_b200.h): the signal table + Dll_Pll_Conf values the device-resident loop closure needs"""
+    _fields_ = [("fs_in", C.c_double), ("code_period_s", C.c_double), ("code_chip_rate", C.c_double), ("signal_carrier_freq", C.c_double),
+                ("code_length_chips", C.c_int32), ("code_samples_per_chip", C.c_int32), ("vector_length", C.c_int32), ("veml", C.c_int32),
+                ("symbols_per_bit", C.c_int32), ("secondary", C.c_int32), ("secondary_code_length", C.c_int32), ("interchange_iq", C.c_int32),
+                ("secondary_code", C.c_char * 192),
+                ("pll_bw_hz", C.c_float), ("dll_bw_hz", C.c_float), ("fll_bw_hz", C.c_float), ("pll_bw_narrow_hz", C.c_float), ("dll_bw_narrow_hz", C.c_float),
+                ("early_late_space_chips", C.c_float), ("very_early_late_space_chips", C.c_float), ("early_late_space_narrow_chips", C.c_float),
+                ("very_early_late_space_narrow_chips", C.c_float), ("slope", C.c_float), ("y_intercept", C.c_float),
+                ("carrier_lock_th", C.c_float), ("cn0_smoother_alpha", C.c_float), ("carrier_lock_test_smoother_alpha", C.c_float),
+                ("pll_filter_order", C.c_int32), ("dll_filter_order", C.c_int32), ("extend_correlation_symbols", C.c_int32),
+                ("enable_fll_pull_in", C.c_int32), ("enable_fll_steady_state", C.c_int32), ("carrier_aiding", C.c_int32),
+                ("cn0_samples", C.c_int32), ("cn0_min", C.c_int32), ("max_code_lock_fail", C.c_int32), ("max_carrier_lock_fail", C.c_int32),
+                ("cn0_smoother_samples", C.c_int32), ("carrier_lock_test_smoother_samples", C.c_int32),
+                ("pull_in_time_s", C.c_uint32), ("bit_synchronization_time_limit_s", C.c_uint32)]
+
+
+class LoopChannelState(C.Structure):
+    _fields_ = [("state", C.c_int32), ("pull_in_transitory", C.c_int32), ("current_prn_length_samples", C.c_int32), ("narrow", C.c_int32),
+                ("carrier_doppler_hz", C.c_double), ("cn0_db_hz", C.c_double), ("carrier_lock_test", C.c_double), ("code_freq_chips", C.c_double),
+                ("rem_code_phase_samples", C.c_double), ("acc_carrier_phase_rad", C.c_double), ("nitems_read", C.c_uint64)]
+
+
 class AcqConfig(C.Structure):
     _fields_ = [("device", C.c_int32), ("iq_dtype", C.c_int32), ("fft_size", C.c_int32), ("consumed_samples", C.c_int32),
                 ("bit_transition", C.c_int32), ("use_cfar", C.c_int32), ("samples_per_chip", C.c_int32), ("max_dwells", C.c_int32),
@@ -69,6 +92,14 @@ SYMBOLS = {
     "gb200_trk_collect": (C.c_int, [_vp, _vp]),
     "gb200_trk_replay": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
     "gb200_trk_last_kernel": (C.c_char_p, [_vp]),
+    "gb200_loop_create": (C.c_int, [_vp, C.POINTER(LoopConfig), C.c_int, C.POINTER(_vp)]),
+    "gb200_loop_destroy": (C.c_int, [_vp]),
+    "gb200_loop_start": (C.c_int, [_vp, C.c_int, C.c_uint32, C.c_double, C.c_double, C.c_uint64, C.c_uint64]),
+    "gb200_loop_stop": (C.c_int, [_vp, C.c_int]),
+    "gb200_loop_step": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int, C.POINTER(C.c_int)]),
+    "gb200_loop_channel": (C.c_int, [_vp, C.c_int, C.POINTER(LoopChannelState)]),
+    "gb200_loop_last_step": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "gb200_loop_kernel": (C.c_char_p, [_vp]),
     "gb200_acq_create": (C.c_int, [C.POINTER(AcqConfig), C.POINTER(_vp)]),
     "gb200_acq_destroy": (C.c_int, [_vp]),
     "gb200_acq_set_local_code": (C.c_int, [_vp, C.c_int, _vp, C.c_int]),

@@ -1,6 +1,7 @@
 // Tracking multicorrelator engine: C ABI (include/gnss_b200.h) over trk_kernel.cuh.
 #include "trk_kernel2.cuh"
 #include "trk_kernel3.cuh"
+#include "trk_loop.cuh"
 #include "ingest_kernel.cuh"
 #include "host_pool.h"
 #include <chrono>
@@ -356,3 +357,4 @@ uint64_t gb200_trk_head(const gb200_trk* h) { return h ? h->head : 0; }
 
 #include "ingest.inc"
 #include "trk_submit.inc"
+#include "trk_loop.inc"

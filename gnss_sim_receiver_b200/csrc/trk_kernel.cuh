@@ -168,6 +168,7 @@ __global__ void __launch_bounds__(TRK_THREADS) trk_correlate_kernel(const TrkDev
     const TrkDevCmd& c = cmds[blockIdx.y];
     const int tid = threadIdx.x;
     const int n = c.n;
+    if (n <= 0) return;  // an empty slot of a device-formed command array (trk_loop.cuh): uniform for the CTA, before any barrier
     const int chunk_len = (((n + n_chunks - 1) / n_chunks) + TRK_THREADS - 1) & ~(TRK_THREADS - 1);
     const int n0 = blockIdx.x * chunk_len;
     const int n1 = min(n, n0 + chunk_len);

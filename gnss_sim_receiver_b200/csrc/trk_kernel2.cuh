@@ -175,6 +175,7 @@ __global__ void __launch_bounds__(TRK2_THREADS, trk2_min_blocks<IQ, CH>()) trk_r
     const long long ws = (long long)((static_cast<const unsigned char*>(c.iq) - ring) / EB);  // ring element index of the window's first sample
     const long long tile0 = ws & ~7LL;                                                           // 16-byte aligned for every sample type
     const int n = c.n, L = c.L;
+    if (n <= 0) return;  // an empty slot of a device-formed command array (trk_loop.cuh): uniform for the CTA, before any barrier
     const int n_tiles = (int)((ws + n - tile0 + TILE - 1) / TILE);
     const int lead = (int)(tile0 - ws);  // <= 0: sample index of the first staged sample
     const unsigned long long u0 = c.u0, du = c.du;

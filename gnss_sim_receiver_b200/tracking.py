@@ -9,7 +9,7 @@ import ctypes as C
 import numpy as np
 
 from . import _capi
-from ._capi import GB200_MAX_TAPS, IQ_CF32, IQ_CS16, IQ_CS8, IngestFormat, TrkCmd, TrkConfig, check
+from ._capi import GB200_MAX_TAPS, IQ_CF32, IQ_CS16, IQ_CS8, IngestFormat, LoopChannelState, LoopConfig, TrkCmd, TrkConfig, check
 
 SRC_CF32, SRC_CS16, SRC_CS8, SRC_S16, SRC_S8, SRC_2BIT, SRC_LABSAT2, SRC_LABSAT4 = range(8)  # GB200_SRC_*
 TWOBIT_REAL, TWOBIT_IQ, TWOBIT_QI = range(3)  # GB200_2BIT_*
@@ -157,3 +157,105 @@ class TrackingEngine:
         ms = C.c_float()
         check(self._lib.gb200_trk_replay(self._h, iters, C.byref(ms)))
         return ms.value
+
+
+# one emitted Gnss_Synchro (gb200_loop_record); same layout as the host bank's record (gb200h_trk_record)
+LOOP_REC = np.dtype([("channel", "<i4"), ("prn", "<u4"), ("valid", "<i4"), ("correlation_length_ms", "<i4"), ("prompt_i", "<f8"), ("prompt_q", "<f8"),
+                     ("cn0_db_hz", "<f8"), ("carrier_doppler_hz", "<f8"), ("carrier_phase_rads", "<f8"), ("code_phase_samples", "<f8"),
+                     ("tracking_sample_counter", "<u8")])
+
+_GPS_CA_PREAMBLE_SYMBOLS = "".join(c * 20 for c in "10001011")  # GPS_CA_PREAMBLE_SYMBOLS_STR (GPS_L1_CA.h:73)
+# the signal table of dll_pll_veml_tracking.cc:171-447 for the data-component (track_pilot = false) signals the device loop serves
+_SIGNALS = {
+    "1C": dict(code_period_s=0.001, code_chip_rate=1.023e6, signal_carrier_freq=1575.42e6, code_length_chips=1023, code_samples_per_chip=1, veml=0, symbols_per_bit=20,
+               secondary=0, secondary_code=_GPS_CA_PREAMBLE_SYMBOLS, interchange_iq=0),
+    "L5": dict(code_period_s=0.001, code_chip_rate=10.23e6, signal_carrier_freq=1176.45e6, code_length_chips=10230, code_samples_per_chip=1, veml=0, symbols_per_bit=10,
+               secondary=1, secondary_code="0000110101", interchange_iq=1),
+    "1B": dict(code_period_s=0.004, code_chip_rate=1.023e6, signal_carrier_freq=1575.42e6, code_length_chips=4092, code_samples_per_chip=2, veml=1, symbols_per_bit=1,
+               secondary=0, secondary_code="", interchange_iq=0),
+    "5X": dict(code_period_s=0.001, code_chip_rate=10.23e6, signal_carrier_freq=1176.45e6, code_length_chips=10230, code_samples_per_chip=1, veml=0, symbols_per_bit=20,
+               secondary=1, secondary_code="10000100001011101001", interchange_iq=0),
+}
+
+
+def loop_config(signal, fs_in, **overrides):
+    """gb200_loop_config of one signal with the reference's Dll_Pll_Conf defaults (src/algorithms/tracking/libs/dll_pll_conf.cc:36-125,
+    gnss_sdr_flags.cc:48-57); keyword arguments override fields by name."""
+    sig = dict(_SIGNALS[signal])
+    code = sig.pop("secondary_code")
+    c = LoopConfig()
+    c.fs_in = float(fs_in)
+    for k, v in sig.items():
+        setattr(c, k, v)
+    c.secondary_code = code.encode()
+    c.secondary_code_length = len(code)
+    c.vector_length = int(round(fs_in / (c.code_chip_rate / c.code_length_chips)))
+    d = dict(pll_bw_hz=35.0, dll_bw_hz=2.0, fll_bw_hz=35.0, pll_bw_narrow_hz=5.0, dll_bw_narrow_hz=0.75, early_late_space_chips=0.25 if signal != "1B" else 0.25,
+             very_early_late_space_chips=0.5, early_late_space_narrow_chips=0.15, very_early_late_space_narrow_chips=0.5, slope=1.0, y_intercept=1.0,
+             carrier_lock_th=0.7, cn0_smoother_alpha=0.002, carrier_lock_test_smoother_alpha=0.002, pll_filter_order=3, dll_filter_order=2,
+             extend_correlation_symbols=1, enable_fll_pull_in=0, enable_fll_steady_state=0, carrier_aiding=1, cn0_samples=20, cn0_min=25,
+             max_code_lock_fail=50, max_carrier_lock_fail=5000, cn0_smoother_samples=200, carrier_lock_test_smoother_samples=25, pull_in_time_s=10,
+             bit_synchronization_time_limit_s=20)
+    d.update(overrides)
+    for k, v in d.items():
+        if not hasattr(c, k):
+            raise AttributeError(f"gb200_loop_config has no field {k!r}")
+        setattr(c, k, v)
+    return c
+
+
+class TrackingLoop:
+    """Device-resident DLL/PLL loop closure over a TrackingEngine (C ABI gb200_loop_*): channel i uses the engine's code slot i."""
+
+    def __init__(self, engine, config, n_channels):
+        self._lib = _capi.lib()
+        self.engine, self.cfg, self.n = engine, config, n_channels
+        self._h = C.c_void_p()
+        check(self._lib.gb200_loop_create(engine._h, C.byref(config), n_channels, C.byref(self._h)))
+        self._rec = np.zeros(max(4096, 9 * n_channels), dtype=LOOP_REC)
+        assert LOOP_REC.itemsize == 72
+
+    def close(self):
+        if self._h:
+            self._lib.gb200_loop_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def start(self, ch, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp=0, nitems_read=0):
+        check(self._lib.gb200_loop_start(self._h, ch, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, nitems_read))
+
+    def stop(self, ch):
+        check(self._lib.gb200_loop_stop(self._h, ch))
+
+    def step(self, iq=None, copy=True):
+        """Append `iq` (host samples of the engine's item type) and run the rounds that are due; returns the records emitted."""
+        n = C.c_int()
+        if iq is None:
+            ptr, ns = None, 0
+        else:
+            iq = np.ascontiguousarray(iq)
+            ns = iq.size if self.engine.iq_dtype == IQ_CF32 else iq.size // 2
+            ptr = iq.ctypes.data
+        check(self._lib.gb200_loop_step(self._h, ptr, ns, self._rec.ctypes.data, len(self._rec), C.byref(n)))
+        k = min(n.value, len(self._rec))
+        return self._rec[:k].copy() if copy else self._rec[:k]
+
+    def channel(self, ch):
+        s = LoopChannelState()
+        check(self._lib.gb200_loop_channel(self._h, ch, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in LoopChannelState._fields_}
+
+    @property
+    def last_step(self):
+        ms, nc, nr = C.c_float(), C.c_int(), C.c_int()
+        check(self._lib.gb200_loop_last_step(self._h, C.byref(ms), C.byref(nc), C.byref(nr)))
+        return dict(device_ms=ms.value, commands=nc.value, rounds=nr.value)
+
+    @property
+    def kernel(self):
+        return self._lib.gb200_loop_kernel(self._h).decode()

@@ -180,6 +180,88 @@ int gb200_trk_replay(gb200_trk* h, int iters, float* ms_per_iter);
 const char* gb200_trk_last_kernel(const gb200_trk* h);
 
 /* ======================================================================
+ * Device-resident DLL/PLL loop closure over a tracking engine
+ *
+ * Replaces, for every channel of a GPU at once, what dll_pll_veml_tracking::general_work does AROUND the correlator call once per
+ * code period (src/algorithms/tracking/gnuradio_blocks/dll_pll_veml_tracking.cc): start_tracking :643-883, the pull-in alignment
+ * :1757-1788, do_correlation_step's argument casts :1037-1062, save_correlation_results :1263-1373,
+ * cn0_and_tracking_lock_status :972-1029, run_dll_pll :1065-1152, update_tracking_vars :1189-1260 and the state machine :1791-2094
+ * (0 standby, 1 pull-in, 2 wide tracking + symbol synchronisation, 3 extended integration, 4 narrow tracking), with the channel
+ * state resident in HBM: one gb200_loop_step = upload the new IQ block, [correlate kernel -> loop kernel] for every channel whose
+ * next window is in the ring, download the Gnss_Synchro records emitted in this step.  No per-channel host work.
+ * Served: real-code channels with track_pilot = false and high_dyn = false (GPS L1 C/A, GPS L5I, Galileo E1B, Galileo E5aI); the
+ * host block (gnss_sim_receiver_b200/host/b200_dll_pll_veml_tracking.cc) serves the rest.
+ * ====================================================================== */
+typedef struct gb200_loop gb200_loop;
+
+typedef struct
+{
+    /* the signal table of dll_pll_veml_tracking.cc:171-447 */
+    double fs_in;                /* Dll_Pll_Conf::fs_in */
+    double code_period_s;        /* d_code_period */
+    double code_chip_rate;       /* d_code_chip_rate */
+    double signal_carrier_freq;  /* d_signal_carrier_freq */
+    int32_t code_length_chips;   /* d_code_length_chips */
+    int32_t code_samples_per_chip; /* d_code_samples_per_chip: table entries per chip (2 for sinBOC(1,1)) */
+    int32_t vector_length;       /* Dll_Pll_Conf::vector_length: samples correlated per code period */
+    int32_t veml;                /* d_veml: 5 taps (VE, E, P, L, VL) instead of 3 */
+    int32_t symbols_per_bit;     /* d_symbols_per_bit */
+    int32_t secondary;           /* d_secondary: the tracked component carries a secondary code */
+    int32_t secondary_code_length; /* d_secondary_code_length (GPS L1 C/A: the 160-symbol preamble pattern used for bit synchronisation) */
+    int32_t interchange_iq;      /* d_interchange_iq */
+    char secondary_code[192];    /* d_secondary_code_string: '0' / '1' */
+    /* Dll_Pll_Conf (src/algorithms/tracking/libs/dll_pll_conf.h:30-88) */
+    float pll_bw_hz, dll_bw_hz, fll_bw_hz, pll_bw_narrow_hz, dll_bw_narrow_hz;
+    float early_late_space_chips, very_early_late_space_chips, early_late_space_narrow_chips, very_early_late_space_narrow_chips;
+    float slope, y_intercept;    /* of |R| at the early-late spacing (1, 1 for BPSK) */
+    float carrier_lock_th, cn0_smoother_alpha, carrier_lock_test_smoother_alpha;
+    int32_t pll_filter_order, dll_filter_order, extend_correlation_symbols;
+    int32_t enable_fll_pull_in, enable_fll_steady_state, carrier_aiding;
+    int32_t cn0_samples, cn0_min, max_code_lock_fail, max_carrier_lock_fail;
+    int32_t cn0_smoother_samples, carrier_lock_test_smoother_samples;
+    uint32_t pull_in_time_s, bit_synchronization_time_limit_s;
+} gb200_loop_config;
+
+/* one emitted Gnss_Synchro (what general_work writes to its output, :2063-2090), or a loss of lock (flag_valid_symbol_output = 0) */
+typedef struct
+{
+    int32_t channel;
+    uint32_t prn;
+    int32_t flag_valid_symbol_output;
+    int32_t correlation_length_ms;
+    double prompt_i, prompt_q, cn0_db_hz, carrier_doppler_hz, carrier_phase_rads, code_phase_samples;
+    uint64_t tracking_sample_counter;
+} gb200_loop_record;
+
+/* diagnostics: the loop variables of one channel (d_state, d_carrier_doppler_hz, d_CN0_SNV_dB_Hz, ...) */
+typedef struct
+{
+    int32_t state, pull_in_transitory, current_prn_length_samples, narrow;
+    double carrier_doppler_hz, cn0_db_hz, carrier_lock_test, code_freq_chips, rem_code_phase_samples, acc_carrier_phase_rad;
+    uint64_t nitems_read;
+} gb200_loop_channel_state;
+
+/* `engine`: the tracking engine whose ring, code tables and kernels the loop drives; channel ch of the loop uses the engine's
+ * code-table slot ch (gb200_trk_set_code).  The engine must outlive the loop; while a loop is attached, call gb200_trk_push_iq
+ * only through gb200_loop_step. */
+int gb200_loop_create(gb200_trk* engine, const gb200_loop_config* cfg, int n_channels, gb200_loop** out);
+int gb200_loop_destroy(gb200_loop* l);
+/* start_tracking() of channel ch (:643-883): acquisition results as left in Gnss_Synchro; `nitems_read` = absolute index of the
+ * first sample the channel has not consumed yet (where its block would start reading) */
+int gb200_loop_start(gb200_loop* l, int ch, uint32_t prn, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp_samples, uint64_t nitems_read);
+/* stop_tracking(): back to standby */
+int gb200_loop_stop(gb200_loop* l, int ch);
+/* One step.  Appends n_samples of the engine's item type from host memory (NULL / 0: none), runs every round that is due and
+ * copies the records emitted during this step to `records` (at most max_records; *n_records receives how many were emitted). */
+int gb200_loop_step(gb200_loop* l, const void* iq_host, int64_t n_samples, gb200_loop_record* records, int max_records, int* n_records);
+int gb200_loop_channel(gb200_loop* l, int ch, gb200_loop_channel_state* out);
+/* CUDA-event time of the kernels of the last step (correlate + loop closure, without the copies), and how many correlation
+ * commands they served */
+int gb200_loop_last_step(const gb200_loop* l, float* device_ms, int* n_correlated, int* n_rounds);
+/* name of the correlator kernel the loop drives, e.g. "trk_run_kernel<T=3,R=18>" */
+const char* gb200_loop_kernel(const gb200_loop* l);
+
+/* ======================================================================
  * PCPS acquisition engine
  *
  * Replaces pcps_acquisition (src/algorithms/acquisition/gnuradio_blocks/pcps_acquisition.{h:92-290,cc:175-899})

@@ -305,3 +305,142 @@ def test_closed_loop_galileo_e1_pilot_vs_reference_objects():
     for lp in loops:
         lp.close()
     bank.close()
+
+
+# ------------------------------------------------------------------------------------------------ device-resident loop closure
+def _device_loop(nsat, sc, iq_dtype=0, **cfg_over):
+    from gnss_sim_receiver_b200.tracking import TrackingEngine, TrackingLoop, loop_config
+    eng = TrackingEngine(max_channels=nsat, max_code_len=1023, iq_dtype=iq_dtype, ring_samples=4 * CHUNK, max_block=2 * 4000, max_cmds=nsat)
+    cfg = loop_config("1C", FS, pll_bw_hz=35.0, dll_bw_hz=2.0, early_late_space_chips=0.5, pull_in_time_s=1, cn0_samples=20, cn0_min=25, max_code_lock_fail=50,
+                      max_carrier_lock_fail=5000, carrier_lock_th=0.5, **cfg_over)
+    for k in range(nsat):
+        eng.set_code(k, sc["codes"][k])
+    loop = TrackingLoop(eng, cfg, nsat)
+    for k in range(nsat):
+        loop.start(k, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+    return eng, loop
+
+
+@pytest.mark.gpu
+@needs_ref
+def test_device_loop_parity_vs_reference_objects():
+    """gb200_loop_*: the loop closure on the DEVICE (csrc/trk_loop.cuh: state in HBM, one thread per channel, commands formed on the
+    device) against the loops made of the reference's own objects, same gates as the host bank above: every channel locked, same
+    number of telemetry symbols with identical signs, sample counters within one sample, CN0 within 0.1 dB, Doppler within 0.5 Hz RMS."""
+    nsat = 8
+    seconds = min(SECONDS, 30.0)
+    sc = scenario(nsat)
+    eng, loop = _device_loop(nsat, sc)
+    loops = [O.RefLoop(ref_params(0), sc["codes"][k], None, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+             for k in range(nsat)]
+    got, ref = [[] for _ in range(nsat)], [[] for _ in range(nsat)]
+    for _, x in stream_chunks(sc, seconds):
+        r = loop.step(x)
+        for k in range(nsat):
+            got[k].append(r[r["channel"] == k])
+            ref[k].append(loops[k].feed(x))
+    tail = loop.step(None)  # the commands formed by the last step are still pending: nothing new may appear without samples
+    assert len(tail) <= nsat
+    for k in range(nsat):
+        g, r = np.concatenate(got[k]), np.concatenate(ref[k])
+        gs, rs = loop.channel(k), loops[k].state()
+        assert rs["state"] == 4 and gs["state"] == 4, (k, gs, rs)
+        assert np.all(g["prn"] == sc["prn"][k]) and np.all(g["valid"] == 1)
+        # the device loop runs one round behind the host loops (its last command is formed but not yet correlated): compare the common part
+        m = min(len(g), len(r))
+        assert m > 0.9 * len(r) and len(r) - len(g) <= 6, (k, len(g), len(r))
+        g, r = g[:m], r[:m]
+        d_cnt = np.abs(g["tracking_sample_counter"].astype(np.int64) - r["tracking_sample_counter"].astype(np.int64))
+        assert d_cnt.max() <= 1, (k, d_cnt.max())
+        assert np.array_equal(np.sign(g["prompt_i"]), np.sign(r["prompt_i"])), k
+        half = m // 2
+        d_cn0 = np.max(np.abs(g["cn0_db_hz"][half:] - r["cn0_db_hz"][half:]))
+        d_dop = np.sqrt(np.mean((g["carrier_doppler_hz"][half:] - r["carrier_doppler_hz"][half:]) ** 2))
+        print(f"[device loop] ch {k}: records {m}, CN0 diff {d_cn0:.4f} dB, Doppler diff {d_dop:.4f} Hz rms")
+        assert d_cn0 < 0.1, (k, d_cn0)
+        assert d_dop < 0.5, (k, d_dop)
+        assert abs(gs["cn0_db_hz"] - sc["cn0"][k]) < 2.0 and abs(np.mean(g["carrier_doppler_hz"][half:]) - sc["doppler"][k]) < 2.0
+    for lp in loops:
+        lp.close()
+    loop.close()
+    eng.close()
+
+
+@pytest.mark.gpu
+def test_device_loop_matches_host_bank_and_loses_lock_like_it():
+    """Device loop against the product's host loop (B200TrackingBank) on a signal that disappears: both lock, both declare loss of lock
+    (carrier / CN0 fail counters, dll_pll_veml_tracking.cc:991-1027) and fall back to standby, records of the locked stretch agree."""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    nsat = 4
+    sc = scenario(nsat, seed=7)
+    seconds_on, seconds = 3.0, 5.0
+    eng, loop = _device_loop(nsat, sc)
+    bank = H.TrackingBank(CONF, "Tracking_1C", nsat)
+    for k in range(nsat):
+        bank.start(k, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+    got, ref = [], []
+    for first, x in stream_chunks(sc, seconds):
+        if first >= seconds_on * FS:  # the satellites vanish: noise only
+            x = O.gen_if(len(x), first, FS, sc["codes"], sc["doppler"], sc["delay"], sc["phase"], np.full(nsat, -30.0), nav_bits=sc["bits"], seed=77)
+        got.append(loop.step(x))
+        bank.push(x)
+        ref.append(bank.step())
+    got, ref = np.concatenate(got), np.concatenate(ref)
+    for k in range(nsat):
+        g, r = got[got["channel"] == k], ref[ref["channel"] == k]
+        assert loop.channel(k)["state"] == 0 and bank.channel_state(k)["state"] == 0, (k, loop.channel(k), bank.channel_state(k))
+        gl, rl = g[g["valid"] == 0], r[r["valid"] == 0]
+        assert len(gl) == 1 and len(rl) == 1  # exactly one loss-of-lock record each
+        gv, rv = g[g["valid"] == 1], r[r["valid"] == 1]
+        m = min(len(gv), len(rv))
+        assert m > 20 and abs(len(gv) - len(rv)) <= 3
+        on = gv["tracking_sample_counter"][:m] < seconds_on * FS
+        assert np.array_equal(np.sign(gv["prompt_i"][:m][on]), np.sign(rv["prompt_i"][:m][on]))
+        assert np.max(np.abs(gv["carrier_doppler_hz"][:m][on] - rv["carrier_doppler_hz"][:m][on])) < 1.0
+        # the loss is declared within a few code periods of the host loop's
+        assert abs(int(gl["tracking_sample_counter"][0]) - int(rl["tracking_sample_counter"][0])) <= 40 * 4000
+    bank.close()
+    loop.close()
+    eng.close()
+
+
+@pytest.mark.gpu
+def test_device_loop_many_channels_run_kernel():
+    """2048 channels at 25 MS/s (the run-based correlator kernel drives the loop): every channel reaches narrow tracking on its own
+    satellite of a 32-satellite stream and reports Doppler / CN0 near the truth; one correlate launch + one loop kernel per code period."""
+    from gnss_sim_receiver_b200 import _capi
+    from gnss_sim_receiver_b200.tracking import TrackingEngine, TrackingLoop, loop_config
+    fs, n, nsat, nch, periods = 25e6, 25000, 32, 2048, 2600
+    rng = np.random.default_rng(5)
+    codes = np.stack([O.gps_l1_ca_code(p) for p in range(1, 33)])
+    dopp, delay, ph0, cn0 = rng.uniform(-4000, 4000, nsat), rng.uniform(0, 1023, nsat), rng.uniform(0, 6.28, nsat), rng.uniform(42, 48, nsat)
+    bits = rng.choice(np.array([-1, 1], dtype=np.int8), (nsat, 400))
+    pre = np.array([1, -1, -1, -1, 1, -1, 1, 1], dtype=np.int8)
+    for b in range(0, 400, 10):
+        bits[:, b:b + 8] = pre
+    eng = TrackingEngine(max_channels=nch, max_code_len=1023, ring_samples=16 * n, max_block=n + 8, max_cmds=nch)
+    cfg = loop_config("1C", fs, pull_in_time_s=1, cn0_samples=20, cn0_min=25, max_code_lock_fail=50, max_carrier_lock_fail=5000, carrier_lock_th=0.5, early_late_space_chips=0.5)
+    sat = np.arange(nch) % nsat
+    for c in range(nch):
+        eng.set_code(c, codes[sat[c]])
+    loop = TrackingLoop(eng, cfg, nch)
+    assert loop.kernel.startswith("trk_run_kernel"), loop.kernel
+    f_chip = 1.023e6 * (1 + dopp / 1575.42e6)
+    acq_delay = np.mod(delay / f_chip * fs, fs / 1000.0)
+    for c in range(nch):
+        loop.start(c, int(sat[c]) + 1, float(acq_delay[sat[c]] + rng.uniform(-2, 2)), float(dopp[sat[c]] + rng.uniform(-30, 30)), 0, 0)
+    lib = _capi.lib()
+    l0 = lib.gb200_launch_count()
+    nrec = 0
+    for p in range(periods):
+        x = O.gen_if(n, p * n, fs, codes, dopp, delay, ph0, cn0, nav_bits=bits, seed=9)
+        nrec += len(loop.step(x, copy=False))
+    launches = lib.gb200_launch_count() - l0
+    states = [loop.channel(c) for c in range(0, nch, 37)]
+    assert all(s["state"] == 4 for s in states), [s["state"] for s in states]
+    for c, s in zip(range(0, nch, 37), states):
+        assert abs(s["carrier_doppler_hz"] - dopp[sat[c]]) < 6.0 and abs(s["cn0_db_hz"] - cn0[sat[c]]) < 3.5, (c, s, dopp[sat[c]], cn0[sat[c]])  # 31 other satellites in the stream: their cross-correlation reads as noise
+    assert nrec > nch * (periods - 2200) // 20 // 2
+    assert launches <= 2 * periods + 2 * 40, launches  # correlate + loop kernel per period, a few catch-up rounds
+    loop.close()
+    eng.close()
