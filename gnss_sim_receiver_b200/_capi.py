@@ -47,7 +47,7 @@ class LoopConfig(C.Structure):
                 ("enable_fll_pull_in", C.c_int32), ("enable_fll_steady_state", C.c_int32), ("carrier_aiding", C.c_int32),
                 ("cn0_samples", C.c_int32), ("cn0_min", C.c_int32), ("max_code_lock_fail", C.c_int32), ("max_carrier_lock_fail", C.c_int32),
                 ("cn0_smoother_samples", C.c_int32), ("carrier_lock_test_smoother_samples", C.c_int32),
-                ("pull_in_time_s", C.c_uint32), ("bit_synchronization_time_limit_s", C.c_uint32)]
+                ("pull_in_time_s", C.c_uint32), ("bit_synchronization_time_limit_s", C.c_uint32), ("n_correlators", C.c_int32), ("reserved_", C.c_int32)]
 
 
 class LoopChannelState(C.Structure):
@@ -98,6 +98,7 @@ SYMBOLS = {
     "gb200_loop_stop": (C.c_int, [_vp, C.c_int]),
     "gb200_loop_step": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int, C.POINTER(C.c_int)]),
     "gb200_loop_channel": (C.c_int, [_vp, C.c_int, C.POINTER(LoopChannelState)]),
+    "gb200_loop_read_taps": (C.c_int, [_vp, C.c_int, _vp]),
     "gb200_loop_last_step": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "gb200_loop_kernel": (C.c_char_p, [_vp]),
     "gb200_acq_create": (C.c_int, [C.POINTER(AcqConfig), C.POINTER(_vp)]),

@@ -195,7 +195,7 @@ def loop_config(signal, fs_in, **overrides):
              carrier_lock_th=0.7, cn0_smoother_alpha=0.002, carrier_lock_test_smoother_alpha=0.002, pll_filter_order=3, dll_filter_order=2,
              extend_correlation_symbols=1, enable_fll_pull_in=0, enable_fll_steady_state=0, carrier_aiding=1, cn0_samples=20, cn0_min=25,
              max_code_lock_fail=50, max_carrier_lock_fail=5000, cn0_smoother_samples=200, carrier_lock_test_smoother_samples=25, pull_in_time_s=10,
-             bit_synchronization_time_limit_s=20)
+             bit_synchronization_time_limit_s=20, n_correlators=0)
     d.update(overrides)
     for k, v in d.items():
         if not hasattr(c, k):
@@ -249,6 +249,12 @@ class TrackingLoop:
         s = LoopChannelState()
         check(self._lib.gb200_loop_channel(self._h, ch, C.byref(s)))
         return {k: getattr(s, k) for k, _ in LoopChannelState._fields_}
+
+    def read_taps(self, ch):
+        """correlator outputs of channel ch's last correlated round (n_correlators complex values)"""
+        out = np.zeros(GB200_MAX_TAPS, np.complex64)
+        check(self._lib.gb200_loop_read_taps(self._h, ch, out.ctypes.data))
+        return out[:max(self.cfg.n_correlators, 5 if self.cfg.veml else 3)]
 
     @property
     def last_step(self):

@@ -220,6 +220,12 @@ typedef struct
     int32_t cn0_samples, cn0_min, max_code_lock_fail, max_carrier_lock_fail;
     int32_t cn0_smoother_samples, carrier_lock_test_smoother_samples;
     uint32_t pull_in_time_s, bit_synchronization_time_limit_s;
+    /* extended multicorrelator: total taps per channel, 0 or 3 (5 with veml) = the loop's own E, P, L (VE, VL) only.  With more taps
+     * (odd, up to GB200_MAX_TAPS; veml = 0) they are spread uniformly over [-early_late_space, +early_late_space] (the narrow spacing once
+     * the loop narrows): E is the first, P the middle, L the last; the others are correlated in the same launch and stay readable on
+     * the device through gb200_loop_read_taps (multipath / signal-quality monitors). */
+    int32_t n_correlators;
+    int32_t reserved_;
 } gb200_loop_config;
 
 /* one emitted Gnss_Synchro (what general_work writes to its output, :2063-2090), or a loss of lock (flag_valid_symbol_output = 0) */
@@ -255,6 +261,8 @@ int gb200_loop_stop(gb200_loop* l, int ch);
  * copies the records emitted during this step to `records` (at most max_records; *n_records receives how many were emitted). */
 int gb200_loop_step(gb200_loop* l, const void* iq_host, int64_t n_samples, gb200_loop_record* records, int max_records, int* n_records);
 int gb200_loop_channel(gb200_loop* l, int ch, gb200_loop_channel_state* out);
+/* correlator outputs of the last correlated round of channel ch: n_correlators complex values (out[t] = tap t) */
+int gb200_loop_read_taps(gb200_loop* l, int ch, gb200_cf32* out);
 /* CUDA-event time of the kernels of the last step (correlate + loop closure, without the copies), and how many correlation
  * commands they served */
 int gb200_loop_last_step(const gb200_loop* l, float* device_ms, int* n_correlated, int* n_rounds);
