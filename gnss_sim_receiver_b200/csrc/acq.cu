@@ -18,6 +18,7 @@ struct gb200_acq
     int threads{1024};
     size_t smem{0};
     int n_bins{0}, neff{0}, out_offset{0}, n_parts{1};
+    bool cluster_inv{false};  // split transforms: the blocks of a cell run as a thread-block cluster (acq_inv_kernel<3>) instead of staging in global memory
     int doppler_max{0}, doppler_step{0}, doppler_center{0};
     int keep_grid{0}, user_keep{0};
     std::vector<int> pos_of_k;  // natural index -> digit-reversed position
@@ -214,7 +215,25 @@ int make_plan(gb200_acq* h, int max_smem)
     const bool fuse = getenv("GB200_ACQ_PLAIN_RADIX") == nullptr;
     std::vector<int> radix;
     int g = 0;
-    for (int r = 1; r <= 8 && !g; r++)
+    // smallest split that fits one SM's shared memory; a transform that fits only ONCE per SM is split in two when its halves fit twice
+    // (two cells resident per SM, the halves of a cell joined through distributed shared memory: acq_inv_kernel<3>).
+    // GB200_ACQ_SPLIT=<r> forces the split (tuning / tests).
+    int r_first = 1;
+    if (const char* e = getenv("GB200_ACQ_SPLIT")) r_first = std::max(1, std::min(8, atoi(e)));
+    else if (N % 2 == 0 && N >= 8192 && getenv("GB200_ACQ_AUTOSPLIT") != nullptr)  // opt-in: measured slower on B200 (25000: 0.705 ms per C3 sweep against 0.459 unsplit; one more pass and the DSMEM stage outweigh the second resident cell)
+        {
+            std::vector<int> rx;
+            FftPlan probe{};
+            probe.m = N;
+            if (factor_235(N, rx, fuse))
+                {
+                    probe.n_stages = (int)rx.size();
+                    for (int s = 0; s < probe.n_stages; s++) probe.radix[s] = rx[s];
+                    const size_t whole = ((size_t)N + build_stage_tables(probe, nullptr)) * sizeof(float2);
+                    if (whole <= (size_t)max_smem && 2 * (whole + 1024) > (size_t)228 * 1024 && 2 * (whole / 2 + 4096) <= (size_t)228 * 1024) r_first = 2;
+                }
+        }
+    for (int r = r_first; r <= 8 && !g; r++)
         {
             if (N % r) continue;
             pl.m = N / r;

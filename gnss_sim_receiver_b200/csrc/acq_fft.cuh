@@ -49,8 +49,18 @@ constexpr int FFT_TW_STAGE_LO = 32;
 
 __device__ __forceinline__ float2 cmul(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 __device__ __forceinline__ float2 cmulc(float2 a, float2 b) { return make_float2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y); }  // a * conj(b)
-__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+// complex add / subtract / scale as ONE packed f32x2 instruction each (FADD2 / FMUL2 / FFMA2; every lane rounds like the scalar op)
+__device__ __forceinline__ float2 f2(f32x2 v)
+{
+    float2 r;
+    up2(v, r.x, r.y);
+    return r;
+}
+__device__ __forceinline__ f32x2 p2(float2 a) { return pk2(a.x, a.y); }
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return f2(add2(p2(a), p2(b))); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return f2(sub2(p2(a), p2(b))); }
+__device__ __forceinline__ float2 cscale(float s, float2 a) { return f2(mul2(pk2(s, s), p2(a))); }                 // s * a
+__device__ __forceinline__ float2 caxpy(float s, float2 a, float2 y) { return f2(fma2(pk2(s, s), p2(a), p2(y))); }  // s * a + y
 // multiply by -i (forward) / +i (inverse)
 template <bool INV>
 __device__ __forceinline__ float2 rot90(float2 a)
@@ -147,8 +157,8 @@ struct Dft<3, INV>
     {
         const float2 t = cadd(v[1], v[2]);
         const float2 d = csub(v[1], v[2]);
-        const float2 a = make_float2(v[0].x - 0.5f * t.x, v[0].y - 0.5f * t.y);
-        const float2 b = rot90<INV>(make_float2(0.86602540378443865f * d.x, 0.86602540378443865f * d.y));
+        const float2 a = caxpy(-0.5f, t, v[0]);
+        const float2 b = rot90<INV>(cscale(0.86602540378443865f, d));
         v[0] = cadd(v[0], t);
         v[1] = cadd(a, b);
         v[2] = csub(a, b);
@@ -178,11 +188,11 @@ struct Dft<5, INV>
         const float s1 = 0.95105651629515357f, s2 = 0.58778525229247313f;
         const float2 t1 = cadd(v[1], v[4]), t2 = cadd(v[2], v[3]);
         const float2 t3 = csub(v[1], v[4]), t4 = csub(v[2], v[3]);
-        const float2 a1 = make_float2(v[0].x + c1 * t1.x + c2 * t2.x, v[0].y + c1 * t1.y + c2 * t2.y);
-        const float2 a2 = make_float2(v[0].x + c2 * t1.x + c1 * t2.x, v[0].y + c2 * t1.y + c1 * t2.y);
-        const float2 b1 = rot90<INV>(make_float2(s1 * t3.x + s2 * t4.x, s1 * t3.y + s2 * t4.y));
-        const float2 b2 = rot90<INV>(make_float2(s2 * t3.x - s1 * t4.x, s2 * t3.y - s1 * t4.y));
-        v[0] = make_float2(v[0].x + t1.x + t2.x, v[0].y + t1.y + t2.y);
+        const float2 a1 = caxpy(c2, t2, caxpy(c1, t1, v[0]));
+        const float2 a2 = caxpy(c1, t2, caxpy(c2, t1, v[0]));
+        const float2 b1 = rot90<INV>(caxpy(s2, t4, cscale(s1, t3)));
+        const float2 b2 = rot90<INV>(caxpy(-s1, t4, cscale(s2, t3)));
+        v[0] = cadd(cadd(v[0], t1), t2);
         v[1] = cadd(a1, b1);
         v[4] = csub(a1, b1);
         v[2] = cadd(a2, b2);

@@ -80,18 +80,33 @@ __device__ __forceinline__ float2 acq_wiped_sample(const void* iq, int n, int co
     return cmul(x, acq_phasor(dphi * (unsigned long long)n));
 }
 
-// fp32 phase accumulation of the reference, one thread per Doppler bin: tab[bin][n] = phase before sample n
-__global__ void acq_phase_table_kernel(const float* __restrict__ inc, int n_bins, int n, float* __restrict__ tab)
+// fp32 phase accumulation of the reference: tab[bin][n] = phase before sample n, accumulated by repeated fp32 addition (the order of
+// volk_gnsssdr_s32f_sincos_32fc_generic, so the values are the reference's bit for bit).  The recurrence is serial per bin: a lane owns
+// a bin; every 32 samples the warp transposes its 32 x 32 tile through shared memory so that the rows go out as coalesced 128-byte
+// stores (one thread per bin with strided 4-byte stores took as long as a whole sweep).
+constexpr int ACQ_PT_WARPS = 4;
+__global__ void __launch_bounds__(32 * ACQ_PT_WARPS) acq_phase_table_kernel(const float* __restrict__ inc, int n_bins, int n, float* __restrict__ tab)
 {
-    const int bin = blockIdx.x * blockDim.x + threadIdx.x;
-    if (bin >= n_bins) return;
-    const float d = inc[bin];
+    __shared__ float tile[ACQ_PT_WARPS][32][33];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bin0 = (blockIdx.x * ACQ_PT_WARPS + w) * 32;
+    if (bin0 >= n_bins) return;
+    const int bin = bin0 + lane;
+    const float d = bin < n_bins ? inc[bin] : 0.0f;
+    const int rows = min(32, n_bins - bin0);
     float ph = 0.0f;
-    float* row = tab + (size_t)bin * n;
-    for (int i = 0; i < n; i++)
+    for (int i0 = 0; i0 < n; i0 += 32)
         {
-            row[i] = ph;
-            ph = __fadd_rn(ph, d);
+#pragma unroll
+            for (int k = 0; k < 32; k++)
+                {
+                    tile[w][lane][k] = ph;
+                    ph = __fadd_rn(ph, d);
+                }
+            __syncwarp();
+            if (i0 + lane < n)
+                for (int r = 0; r < rows; r++) tab[(size_t)(bin0 + r) * n + i0 + lane] = tile[w][r][lane];
+            __syncwarp();
         }
 }
 

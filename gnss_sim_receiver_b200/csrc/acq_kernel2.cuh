@@ -1,5 +1,6 @@
 // Inverse side of the acquisition search (included by acq_kernel.cuh).
 #pragma once
+#include <cooperative_groups.h>
 
 namespace gb200
 {
@@ -10,9 +11,13 @@ namespace gb200
 //           registers                                                      -> cells[(slot_i * n_bins + bin)]
 //   MODE 1: (g_radix  > 1) store the block to scratch[(slot_i * n_bins + bin)][N] for the global inverse stage
 //   MODE 2: test hook — no code product, store the natural-order complex output to scratch
+//   MODE 3: (g_radix  > 1) the g_radix CTAs of a cell form a THREAD-BLOCK CLUSTER: each transforms its block in its own shared memory,
+//           then the last (radix g_radix) stage of the transform is taken straight out of the partners' shared memory (DSMEM): CTA r
+//           combines the butterflies j2 in its slice of [0, m), feeds |.|^2 / grid / max / sum and writes part r of the cell.  Nothing
+//           is staged in global memory; with two blocks of 12500 points, two cells are resident per SM for N = 25000.
 template <int MODE>
 __global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_inv_kernel(AcqParams p, const float2* __restrict__ X, const float2* __restrict__ Cs, const int* __restrict__ slots,
-    const float2* __restrict__ gT, float2* __restrict__ scratch, float* __restrict__ grid, AcqCell* __restrict__ cells)
+    const float2* __restrict__ gT, float2* __restrict__ scratch, float* __restrict__ grid, AcqCell* __restrict__ cells, const float2* __restrict__ gA, const float2* __restrict__ gB)
 {
     extern __shared__ __align__(16) float2 sm[];
     const FftPlan& pl = p.plan;
@@ -52,7 +57,7 @@ __global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_inv_kernel(AcqParams p, c
             AcqCodeProduct pre;
             pre.c = Cs + (size_t)slots[si] * pl.n + blk_off;
             pre.nb = pl.m / pl.perm_rl;
-            if (MODE == 1)
+            if (MODE == 1 || MODE == 3)
                 {
                     FftNoPost post;
                     fft_smem_inverse(pl, x, sT, pre, post);
@@ -80,6 +85,73 @@ __global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_inv_kernel(AcqParams p, c
                         }
                     return;
                 }
+        }
+    if (MODE == 3)
+        {
+            namespace cg = cooperative_groups;
+            cg::cluster_group cluster = cg::this_cluster();
+            cluster.sync();  // every block of the cell is transformed
+            const int R = pl.g_radix, r = (int)cluster.block_rank(), unit = pl.n / R;
+            const float2* xb[8];
+#pragma unroll
+            for (int k1 = 0; k1 < 8; k1++) xb[k1] = k1 < R ? cluster.map_shared_rank(x, k1) : x;
+            AcqSink sink;
+            sink.out_offset = p.out_offset;
+            sink.neff = p.neff;
+            sink.accumulate = p.dwell_index > 0;
+            sink.grid_row = p.keep_grid ? grid + ((size_t)slots[si] * p.n_bins + bin) * p.neff : nullptr;
+            sink.best = -1.0f;
+            sink.sum = 0.0f;
+            sink.besti = 0x7fffffff;
+            const int per = (pl.m + R - 1) / R;
+            const int lo = r * per, hi = min(pl.m, lo + per);
+#pragma unroll 2
+            for (int j2 = lo + threadIdx.x; j2 < hi; j2 += blockDim.x)
+                {
+                    // y[j1 * m + j2] = sum_k1 conj(W_N^{j2 k1}) z_k1[j2] conj(W_R^{j1 k1})   (last DIT stage)
+                    float2 v[8];
+#pragma unroll
+                    for (int k1 = 0; k1 < 8; k1++)
+                        if (k1 < R)
+                            {
+                                const float2 t = xb[k1][j2];
+                                v[k1] = k1 ? cmulc(t, fft_twiddle(gA, gB, (int)((long long)j2 * k1))) : t;
+                            }
+                    switch (R)
+                        {
+                        case 2: Dft<2, true>::run(v); break;
+                        case 3: Dft<3, true>::run(v); break;
+                        case 4: Dft<4, true>::run(v); break;
+                        case 5: Dft<5, true>::run(v); break;
+                        case 7: Dft<7, true>::run(v); break;
+                        default:
+                            {
+                                float2 y[8];
+                                for (int j1 = 0; j1 < R; j1++)
+                                    {
+                                        float2 acc = v[0];
+                                        for (int k1 = 1; k1 < R; k1++) acc = cadd(acc, cmulc(v[k1], fft_twiddle(gA, gB, ((j1 * k1) % R) * unit)));
+                                        y[j1] = acc;
+                                    }
+                                for (int j1 = 0; j1 < R; j1++) v[j1] = y[j1];
+                            }
+                        }
+#pragma unroll
+                    for (int j1 = 0; j1 < 8; j1++)
+                        if (j1 < R) sink(v[j1], j1 * pl.m + j2);
+                }
+            acq_block_reduce(sink.best, sink.besti, sink.sum);
+            if (threadIdx.x == 0)
+                {
+                    AcqCell c;
+                    c.vmax = sink.best;
+                    c.imax = sink.besti;
+                    c.sum = sink.sum;
+                    c.pad_ = 0;
+                    cells[cell * p.n_parts + r] = c;
+                }
+            cluster.sync();  // no block leaves while a partner may still read its shared memory
+            return;
         }
     float2* d = scratch + cell * pl.n + blk_off;
     for (int i = threadIdx.x; i < pl.m; i += blockDim.x) d[i] = x[i];

@@ -20,66 +20,6 @@ constexpr int TRK_RESEED = 16;    // exact phasor re-seed period (in per-thread 
 constexpr int TRK_PREFETCH = 8;   // samples a thread fetches ahead of the arithmetic (general kernel)
 constexpr int TRK_OUT_STRIDE = GB200_MAX_TAPS;
 
-// ---- packed f32x2 helpers: a pair lives in one 64-bit register pair; ptxas folds scalar broadcasts ({a, a}) and swaps into operand
-// selectors (R.F32 / .LO_HI), so building those pairs costs no instruction
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pk2(float lo, float hi)
-{
-    f32x2 r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-    return r;
-}
-__device__ __forceinline__ void up2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
-{
-    f32x2 r;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-    return r;
-}
-__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
-{
-    f32x2 r;
-    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
-__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b)
-{
-    f32x2 r;
-    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
-__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b)
-{
-    f32x2 r;
-    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
-__device__ __forceinline__ void st_shared_b64(unsigned addr, f32x2 v) { asm volatile("st.shared.b64 [%0], %1;" ::"r"(addr), "l"(v) : "memory"); }
-__device__ __forceinline__ f32x2 ld_shared_b64(unsigned addr)
-{
-    f32x2 v;
-    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v) : "r"(addr) : "memory");
-    return v;
-}
-__device__ __forceinline__ float2 ld_shared_f2(unsigned addr)
-{
-    float2 v;
-    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr) : "memory");
-    return v;
-}
-__device__ __forceinline__ float ld_shared_f1(unsigned addr)
-{
-    float v;
-    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
-    return v;
-}
-__device__ __forceinline__ f32x2 add2_rd(f32x2 a, f32x2 b)  // round towards -inf, like __fadd_rd in both lanes
-{
-    f32x2 r;
-    asm("add.rm.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
-
 // host-preprocessed command, one per Carrier_wipeoff_multicorrelator_resampler call
 struct TrkDevCmd
 {

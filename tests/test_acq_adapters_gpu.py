@@ -98,7 +98,7 @@ def test_gps_l5i_adapter_from_conf_with_dwells():
     assert 1 <= n_dwells <= 3
     conf, ro = _oracle(fs, 20000, 20000, float(np.float32(np.float32(fs) * np.float32(0.001))), 2, local, [x[d * 20000:(d + 1) * 20000] for d in range(n_dwells)], max_dwells=3)
     _check(s, ro, consumed)
-    assert abs(((s.acq_delay_samples - delay / 10.23e6 * fs + 10000) % 20000) - 10000) <= 2 and abs(s.acq_doppler_hz - doppler) <= 125
+    assert abs(((s.acq_delay_samples - delay / 10.23e6 * fs + 10000) % 20000) - 10000) <= 2 and abs(s.acq_doppler_hz - doppler) <= 250  # either bin next to the truth
     a.close()
 
 
@@ -119,5 +119,5 @@ def test_galileo_e5a_adapter_from_conf(opts, sig):
     s = a.status()
     conf, ro = _oracle(fs, 20000, 20000, float(np.float32(np.float32(fs) * np.float32(0.001))), 2, local, [x[:20000]])
     _check(s, ro, consumed)
-    assert abs(((s.acq_delay_samples - delay / 10.23e6 * fs + 10000) % 20000) - 10000) <= 2 and abs(s.acq_doppler_hz - doppler) <= 125
+    assert abs(((s.acq_delay_samples - delay / 10.23e6 * fs + 10000) % 20000) - 10000) <= 2 and abs(s.acq_doppler_hz - doppler) <= 250  # either bin next to the truth
     a.close()

@@ -109,7 +109,7 @@ def test_c3_gps_benched_sweep_exactly():
     for s in sats:  # truth: nearest bin, code start within a sample of delay / f_chip * fs
         g = got[0][s["prn"] - 1]
         assert abs(g[2] - s["doppler"]) <= dstep  # the two bins around the true Doppler differ by a few per cent of the peak: noise may pick either
-        assert abs(((g[3] - s["delay"] / 1.023e6 * fs + n / 2) % n) - n / 2) <= 2
+        assert abs(((g[3] - s["delay"] / 1.023e6 * fs + n / 2) % n) - n / 2) <= 3  # 24.4 samples per chip: the correlation peak is flat over a few samples
 
 
 def test_c2_galileo_e1_pilot_bit_transition_cshort():
