@@ -402,6 +402,7 @@ def run_acq(args, rank, world, local, dist, flush, parity):
         # (2) by Doppler tile: rank k sweeps bins [kB/G, (k+1)B/G) for every PRN; the per-(PRN, bin) reductions are all-gathered (NCCL) and
         # merged with the reference's first-bin / first-index rule on every rank
         lo, hi = sharding.doppler_tiles(bins, world)[rank]
+        tile_widths = [b1 - b0 for b0, b1 in sharding.doppler_tiles(bins, world)]
         e2 = AcquisitionEngine(fs_in=FS, fft_size=n, samples_per_code=float(n), samples_per_chip=spchip, max_prns=ACQ_PRNS, device=local)
         e2.set_doppler_bins([float(-ACQ_DMAX + ACQ_DSTEP * k) for k in range(lo, hi)])
         for p in range(ACQ_PRNS):
@@ -413,7 +414,7 @@ def run_acq(args, rank, world, local, dist, flush, parity):
             t0 = time.perf_counter()
             e2.run(blk_host)
             v, im, sm = e2.read_cells(ACQ_PRNS)
-            v, im, sm = sharding.gather_cell_tiles(dist, v, im, sm, world, device=f"cuda:{local}")
+            v, im, sm = sharding.gather_cell_tiles(dist, v, im, sm, world, device=f"cuda:{local}", widths=tile_widths)
             out = sharding.merge_cells(v, im, sm, n, 1, -ACQ_DMAX, ACQ_DSTEP, float(n))
             dt = time.perf_counter() - t0
             if i >= W:

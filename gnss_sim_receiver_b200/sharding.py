@@ -126,25 +126,30 @@ def merge_cells(vmax, imax, sums, neff, num_dwells=1, doppler_base=0, doppler_st
     imax = np.asarray(imax, dtype=np.int64)
     sums = np.asarray(sums, dtype=np.float32)
     n_slots, n_bins = vmax.shape
+    rows = np.arange(n_slots)
+    b = np.argmax(vmax, axis=1)  # first maximum in bin order
+    best = vmax[rows, b]
+    idx = imax[rows, b]
+    dead = ~(best > 0)           # an all-zero grid leaves (0, 0): the reference starts from grid_maximum = 0 with a strict '>'
+    best = np.where(dead, np.float32(0), best).astype(np.float32)
+    b = np.where(dead, 0, b)
+    idx = np.where(dead, 0, idx)
+    opp = (b + n_bins // 2) % n_bins
+    power = ((sums[rows, opp] / np.float32(neff)).astype(np.float64) / 2.0 / num_dwells).astype(np.float32)  # float / int, then double (:519)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        stat = (best / power).astype(np.float32)
+    delay = np.fmod(idx.astype(np.float32), np.float32(samples_per_code)) if samples_per_code is not None else None
     out = []
     for s in range(n_slots):
-        b = int(np.argmax(vmax[s]))  # first maximum in bin order
-        best = np.float32(vmax[s, b])
-        idx = int(imax[s, b])
-        if not best > 0:
-            best, b, idx = np.float32(0), 0, 0
-        opp = (b + n_bins // 2) % n_bins
-        power = np.float32(np.float64(np.float32(sums[s, opp]) / np.float32(neff)) / 2.0 / num_dwells)
-        with np.errstate(divide="ignore", invalid="ignore"):
-            stat = np.float32(best) / power
-        r = dict(indext=idx, doppler_index=b, doppler_hz=int(doppler_base + doppler_step * b), peak=float(best), input_power=float(power), test_statistics=float(stat))
-        if samples_per_code is not None:
-            r["acq_delay_samples"] = float(np.fmod(np.float32(idx), np.float32(samples_per_code)))
+        r = dict(indext=int(idx[s]), doppler_index=int(b[s]), doppler_hz=int(doppler_base + doppler_step * int(b[s])), peak=float(best[s]), input_power=float(power[s]),
+                 test_statistics=float(stat[s]))
+        if delay is not None:
+            r["acq_delay_samples"] = float(delay[s])
         out.append(r)
     return out
 
 
-def gather_cell_tiles(dist, vmax, imax, sums, world, device="cpu"):
+def gather_cell_tiles(dist, vmax, imax, sums, world, device="cpu", widths=None):
     """All-gather of every rank's Doppler tile of cell reductions ([n_slots, bins_of_this_rank] each; tiles may differ in width) into
     the full [n_slots, n_bins] tables on EVERY rank, tiles in rank order = bin order (doppler_tiles).  One collective of
     3 x 4 bytes per (slot, bin): NCCL on the GPUs, gloo in the CPU tests."""
@@ -152,10 +157,11 @@ def gather_cell_tiles(dist, vmax, imax, sums, world, device="cpu"):
         return np.asarray(vmax), np.asarray(imax), np.asarray(sums)
     import torch
     n_slots, nb = np.asarray(vmax).shape
-    widths = torch.zeros(world, dtype=torch.int64, device=device)
-    mine = torch.tensor([nb], dtype=torch.int64, device=device)
-    dist.all_gather_into_tensor(widths, mine)
-    widths = [int(w) for w in widths.tolist()]
+    if widths is None:  # tile widths of the other ranks (known beforehand when the tiles come from doppler_tiles: pass them and save a collective)
+        wt = torch.zeros(world, dtype=torch.int64, device=device)
+        mine = torch.tensor([nb], dtype=torch.int64, device=device)
+        dist.all_gather_into_tensor(wt, mine)
+        widths = [int(w) for w in wt.tolist()]
     wmax = max(widths)
     pack = np.zeros((3, n_slots, wmax), np.float32)
     pack[0, :, :nb] = vmax
