@@ -79,6 +79,8 @@ SYMBOLS = {
     "gb200h_bank_run_threaded": (_i, [_vp, _vp, C.c_int64, C.c_uint64, _i, _vp, _i]),
     "gb200h_engine_probe": (_s, [_s, _s, C.c_uint, _s, C.c_uint]),
     "gb200h_acq_create": (_i, [_s, _s, C.c_uint, C.POINTER(_vp)]),
+    "gb200h_acq_work_gr": (C.c_int64, [_vp, _vp, C.c_int64, C.POINTER(C.c_int)]),
+    "gb200h_gr_tracking_run": (_i, [_s, _s, C.c_uint, _d, _d, _vp, C.c_int64, C.c_int64, _vp, _i, _vp]),
     "gb200h_acq_create2": (_i, [_s, _s, C.c_uint, C.c_char, _s, C.POINTER(_vp)]),
     "gb200h_acq_local_code": (C.c_int64, [_vp, C.c_void_p, C.c_int64]),
     "gb200h_acq_destroy": (None, [_vp]),
@@ -231,6 +233,14 @@ class AcquisitionBlock:
         n = items.size if np.iscomplexobj(items) else items.size // 2
         return check(self._lib.gb200h_acq_work(self._h, items.ctypes.data, n, chunk))
 
+    def work_gr(self, items):
+        """the same items through the block's gr::block face (b200_acquisition_gr); returns (consumed, last event on the "events" port)"""
+        items = np.ascontiguousarray(items)
+        n = items.size if np.iscomplexobj(items) else items.size // 2
+        ev = C.c_int()
+        done = check(self._lib.gb200h_acq_work_gr(self._h, items.ctypes.data, n, C.byref(ev)))
+        return done, ev.value
+
     def status(self):
         s = AcqStatus()
         check(self._lib.gb200h_acq_get_status(self._h, C.byref(s)))
@@ -319,3 +329,13 @@ class SynchroMonitor:
 
     def __del__(self):
         self.close()
+
+
+def gr_tracking_run(conf_text, role, prn, acq_delay_samples, acq_doppler_hz, iq, telemetry_fault_at=-1):
+    """One tracking adapter behind its gr::block face (b200_tracking_gr over the GNU Radio stub): returns (records, events dict)."""
+    iq = np.ascontiguousarray(iq)
+    n = iq.size if np.iscomplexobj(iq) else iq.size // 2
+    rec = np.zeros(n // 1000 + 64, dtype=REC_DTYPE)
+    ev = (C.c_int64 * 4)()
+    k = check(lib().gb200h_gr_tracking_run(conf_text.encode(), role.encode(), prn, acq_delay_samples, acq_doppler_hz, iq.ctypes.data, n, telemetry_fault_at, rec.ctypes.data, len(rec), ev))
+    return rec[:k].copy(), dict(n_events=ev[0], last_event=ev[1], consumed=ev[2], state=ev[3])

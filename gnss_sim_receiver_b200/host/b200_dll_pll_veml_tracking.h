@@ -34,8 +34,12 @@ public:
     void stop_tracking();
     // "events" message port: 3 = loss of lock (dll_pll_veml_tracking.cc:1023)
     void set_event_sink(std::function<void(int)> sink) { event_sink_ = std::move(sink); }
-    // "telemetry_to_trk" message: half-cycle PLL ambiguity resolved by the telemetry decoder (:141-152, msg_handler)
-    void telemetry_to_trk(bool flag_pll_180_deg_phase_locked) { d_Flag_PLL_180_deg_phase_locked = flag_pll_180_deg_phase_locked; }
+    // "telemetry_to_trk" message port (msg_handler_telemetry_to_trk, dll_pll_veml_tracking.cc:617-641): event 1 = the telemetry decoder
+    // reports a fault -> the loss-of-lock condition is forced (d_carrier_lock_fail_counter = 200000); other events are ignored
+    void telemetry_to_trk(int tlm_event)
+    {
+        if (tlm_event == 1) d_carrier_lock_fail_counter = 200000;
+    }
 
     // Code tables for signals whose generators are not part of this tree (Galileo E1/E5a, GPS L5...): the adapter hands
     // them over before start_tracking().  GPS L1 C/A tables are generated here when none was supplied.

@@ -5,6 +5,7 @@
 #include "b200_mat_writer.h"
 #include "b200_configuration.h"
 #include "b200_gnss_codes.h"
+#include "b200_gr_blocks.h"
 #include "b200_tracking_bank.h"
 #include <algorithm>
 #include <cstring>
@@ -493,6 +494,74 @@ int gb200h_bank_run_threaded(gb200h_bank* b, const void* iq, int64_t n_samples, 
 
 }  // extern "C"
 
+extern "C" {
+// One tracking adapter started like Channel starts it and run behind its gr::block face (b200_tracking_gr): the stream goes through
+// forecast / general_work / consume_each of the wrapper, Gnss_Synchro items come out of its output buffer.  `telemetry_fault_at` >= 0:
+// a "telemetry_to_trk" message with event 1 is posted once nitems_read passes that sample.  Returns the records written; events[0..3] =
+// number of messages on "events", the last one's value, items consumed, the block's final state.
+int gb200h_gr_tracking_run(const char* conf_text, const char* role, unsigned prn, double acq_delay_samples, double acq_doppler_hz, const void* iq, int64_t n_samples,
+    int64_t telemetry_fault_at, gb200h_trk_record* records, int max_records, int64_t* events)
+{
+    try
+        {
+            B200Configuration cfg;
+            cfg.load_string(conf_text);
+            B200CorrelatorEngine::reset_instances();
+            auto adapter = GetB200TrkBlock(&cfg, role, 1, 1);
+            if (!adapter) throw std::runtime_error(std::string(role) + ".implementation is not a B200 tracking block");
+            auto* a = static_cast<B200DllPllTracking*>(adapter.get());
+            Gnss_Synchro syn{};
+            syn.System = a->conf().system;
+            std::memcpy(syn.Signal, a->conf().signal, 3);
+            syn.PRN = prn;
+            syn.Acq_delay_samples = acq_delay_samples;
+            syn.Acq_doppler_hz = acq_doppler_hz;
+            syn.Acq_samplestamp_samples = 0;
+            a->set_gnss_synchro(&syn);
+            a->set_channel(0);
+            a->start_tracking();
+            auto blk = make_b200_tracking_gr(a->block(), a->item_size(), a->conf().vector_length);
+            const size_t isz = a->item_size();
+            std::vector<char> out;
+            int64_t done = 0;
+            bool posted = telemetry_fault_at < 0;
+            const int64_t piece = 64 * static_cast<int64_t>(a->conf().vector_length);
+            while (done < n_samples)
+                {
+                    // the scheduler hands the block what its input buffer holds: here pieces of the stream, each piece's unconsumed tail carried over
+                    const int64_t n = std::min<int64_t>(piece, n_samples - done);
+                    const int64_t c = blk->stub_feed(static_cast<const char*>(iq) + done * isz, n, &out);
+                    if (c == 0) break;  // what is left does not meet the block's forecast
+                    done += c;
+                    if (!posted && done >= telemetry_fault_at)
+                        {
+                            blk->stub_post("telemetry_to_trk", pmt::from_long(1));
+                            posted = true;
+                        }
+                }
+            const int n_rec = static_cast<int>(out.size() / sizeof(Gnss_Synchro));
+            for (int i = 0; i < n_rec && i < max_records; i++) to_record(0, reinterpret_cast<const Gnss_Synchro*>(out.data())[i], &records[i]);
+            auto& pub = blk->stub_published("events");
+            if (events)
+                {
+                    events[0] = static_cast<int64_t>(pub.size());
+                    events[1] = pub.empty() ? 0 : pmt::to_long(pub.back());
+                    events[2] = done;
+                    events[3] = a->block()->state();
+                }
+            adapter.reset();
+            B200CorrelatorEngine::reset_instances();
+            return std::min(n_rec, max_records);
+        }
+    catch (const std::exception& e)
+        {
+            B200CorrelatorEngine::reset_instances();
+            return fail(e);
+        }
+}
+
+}  // extern "C"
+
 // ------------------------------------------------------------------ acquisition block
 struct gb200h_acq
 {
@@ -595,6 +664,27 @@ int gb200h_acq_get_status(gb200h_acq* a, gb200h_acq_status* s)
     s->indext = blk.last_result().indext;
     s->doppler_index = blk.last_result().doppler_index;
     return 0;
+}
+
+// The acquisition block behind its gr::block face (b200_gr_blocks.h): items go through general_work(noutput, ninput_items, input_items, ...)
+// and consume_each, events come out of the "events" message port.  Returns the items consumed; *last_event_from_port = the last PMT published.
+int64_t gb200h_acq_work_gr(gb200h_acq* a, const void* items, int64_t n_items, int* last_event_from_port)
+{
+    try
+        {
+            auto blk = make_b200_acquisition_gr(a->adapter->block(), a->adapter->item_size());  // re-points the block's event sink at the port
+            const int64_t done = blk->stub_feed(items, n_items, nullptr);
+            auto& pub = blk->stub_published("events");
+            if (last_event_from_port) *last_event_from_port = pub.empty() ? 0 : static_cast<int>(pmt::to_long(pub.back()));
+            if (!pub.empty()) a->last_event = static_cast<int>(pmt::to_long(pub.back()));
+            gb200h_acq* raw = a;
+            a->adapter->block()->set_event_sink([raw](int ev) { raw->last_event = ev; });
+            return done;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
 }
 
 int64_t gb200h_acq_local_code(gb200h_acq* a, float* dst, int64_t max_samples)

@@ -67,6 +67,10 @@ int gb200h_bank_channel_state(gb200h_bank* b, int ch, double* v);
 uint64_t gb200h_bank_launches(gb200h_bank* b);
 /* per-channel blocking form from `n_threads` host threads (the GNU Radio thread-per-block shape): every thread runs
  * general_work over the same host stream for its share of channels; returns the records like bank_step */
+/* one tracking adapter behind its gr::block face (b200_tracking_gr): forecast / general_work / consume_each, "events" and "telemetry_to_trk"
+ * message ports.  events[4] = messages published on "events", the last one's value, items consumed, the block's final d_state. */
+int gb200h_gr_tracking_run(const char* conf_text, const char* role, unsigned prn, double acq_delay_samples, double acq_doppler_hz, const void* iq, int64_t n_samples,
+    int64_t telemetry_fault_at, gb200h_trk_record* records, int max_records, int64_t* events);
 int gb200h_bank_run_threaded(gb200h_bank* b, const void* iq, int64_t n_samples, uint64_t first_index, int n_threads, gb200h_trk_record* records, int max_records);
 
 /* ---- acquisition block (one channel) */
@@ -83,6 +87,9 @@ typedef struct
 int gb200h_acq_create(const char* conf_text, const char* role, unsigned prn, gb200h_acq** out); /* System 'G', Signal "1C" */
 /* same for any of the four acquisition adapters: `system` / `signal` fill the channel's Gnss_Synchro ('E' "1B", 'G' "L5", 'E' "5X" ...) */
 int gb200h_acq_create2(const char* conf_text, const char* role, unsigned prn, char system, const char* signal, gb200h_acq** out);
+/* the same through the block's gr::block face (host/b200_gr_blocks.h; GNU Radio stub outside GNSS-SDR): general_work + consume_each, events
+ * read back from the "events" message port */
+int64_t gb200h_acq_work_gr(gb200h_acq* a, const void* items, int64_t n_items, int* last_event_from_port);
 /* the replica the adapter handed to set_local_code (complex float pairs); returns its length in samples */
 int64_t gb200h_acq_local_code(gb200h_acq* a, float* dst, int64_t max_samples);
 void gb200h_acq_destroy(gb200h_acq* a);

@@ -342,3 +342,54 @@ def test_engine_is_per_stream_and_sized_for_the_band():
     r = probe("Tracking_L5", 5, "Tracking_5X", 9)
     assert "error" not in r, r
     assert int(r["same"]) == 0 and int(r["stream_b"]) == 7
+
+
+def test_gr_block_faces_forward_to_the_blocks():
+    """INTEGRATION.md §4 as code (host/b200_gr_blocks.{h,cc}, compiled here against the GNU Radio stub): the gr::block wrappers obey the
+    reference's scheduler contract — forecast 2 * vector_length, one Gnss_Synchro per general_work, consume_each — and its message ports:
+    acquisition publishes 1 on "events"; tracking gives the records the lock-step bank gives, publishes 3 on loss of lock, and a
+    "telemetry_to_trk" event 1 forces that loss (dll_pll_veml_tracking.cc:617-641)."""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    prn, doppler, delay, cn0 = 9, 1430.0, 455.2, 47.0
+    bits = np.ones((1, 3000), dtype=np.int8)
+    bits[0, ::2] = -1
+    pre = np.array([1, -1, -1, -1, 1, -1, 1, 1], dtype=np.int8)
+    for b in range(0, 3000, 50):
+        bits[0, b:b + 8] = pre
+    codes = np.stack([O.gps_l1_ca_code(prn)])
+    n = int(3.5 * FS)
+    x = O.gen_if(n, 0, FS, codes, [doppler], [delay], [0.4], [cn0], nav_bits=bits, seed=33)
+    conf = CONF.format(item="gr_complex", pfa=0.01, dwells=1)
+    # acquisition through the wrapper: same detection as through the block, event 1 on the port
+    a = H.AcquisitionBlock(conf, "Acquisition_1C", prn)
+    a.arm()
+    consumed, ev = a.work_gr(x[:12000])
+    s = a.status()
+    assert ev == 1 and consumed == 4000 and s.acq_doppler_hz == 1500.0
+    b = H.AcquisitionBlock(conf, "Acquisition_1C", prn)
+    b.arm()
+    b.work(x[:12000], chunk=2000)
+    sb = b.status()
+    assert (s.indext, s.doppler_index, s.test_statistics) == (sb.indext, sb.doppler_index, sb.test_statistics)
+    a.close()
+    b.close()
+    # tracking through the wrapper against the lock-step bank
+    recs, ev = H.gr_tracking_run(conf, "Tracking_1C", prn, s.acq_delay_samples, s.acq_doppler_hz, x)
+    bank = H.TrackingBank(conf, "Tracking_1C", 1)
+    bank.start(0, prn, s.acq_delay_samples, s.acq_doppler_hz, 0, 0)
+    ref = []
+    for first in range(0, n, 400000):
+        bank.push(x[first:first + 400000])
+        ref.append(bank.step())
+    ref = np.concatenate(ref)
+    assert ev["state"] == 4 and ev["n_events"] == 0 and len(recs) > 20
+    m = min(len(recs), len(ref))
+    assert abs(len(recs) - len(ref)) <= 2
+    assert np.array_equal(recs["tracking_sample_counter"][:m], ref["tracking_sample_counter"][:m])
+    assert np.array_equal(np.sign(recs["prompt_i"][:m]), np.sign(ref["prompt_i"][:m]))
+    assert np.max(np.abs(recs["carrier_doppler_hz"][:m] - ref["carrier_doppler_hz"][:m])) < 1e-6
+    bank.close()
+    # a telemetry fault posted on "telemetry_to_trk" forces the loss of lock: event 3 on "events", block back in standby
+    recs2, ev2 = H.gr_tracking_run(conf, "Tracking_1C", prn, s.acq_delay_samples, s.acq_doppler_hz, x, telemetry_fault_at=int(3.0 * FS))
+    assert ev2["n_events"] == 1 and ev2["last_event"] == 3 and ev2["state"] == 0
+    assert np.sum(recs2["valid"] == 0) == 1 and len(recs2) < len(recs)
