@@ -97,6 +97,8 @@ SYMBOLS = {
     "gb200_loop_start": (C.c_int, [_vp, C.c_int, C.c_uint32, C.c_double, C.c_double, C.c_uint64, C.c_uint64]),
     "gb200_loop_stop": (C.c_int, [_vp, C.c_int]),
     "gb200_loop_step": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int, C.POINTER(C.c_int)]),
+    "gb200_loop_submit": (C.c_int, [_vp, _vp, C.c_int64]),
+    "gb200_loop_collect": (C.c_int, [_vp, _vp, C.c_int, C.POINTER(C.c_int)]),
     "gb200_loop_channel": (C.c_int, [_vp, C.c_int, C.POINTER(LoopChannelState)]),
     "gb200_loop_read_taps": (C.c_int, [_vp, C.c_int, _vp]),
     "gb200_loop_last_step": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_int), C.POINTER(C.c_int)]),

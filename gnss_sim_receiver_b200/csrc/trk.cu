@@ -284,8 +284,9 @@ int gb200_trk_set_code(gb200_trk* h, int ch, const float* code, int code_len) { 
 int gb200_trk_set_code_complex(gb200_trk* h, int ch, const gb200_cf32* code, int code_len) { return set_code_impl(h, ch, code, code_len, true); }
 
 // copy n samples to the ring positions of absolute indices [abs_start, abs_start + n), with the mirror of [0, max_block)
-static int write_at(gb200_trk* h, uint64_t abs_start, const void* src, int64_t n, cudaMemcpyKind kind)
+static int write_at(gb200_trk* h, uint64_t abs_start, const void* src, int64_t n, cudaMemcpyKind kind, cudaStream_t stream = nullptr)
 {
+    if (!stream) stream = h->stream;
     const int64_t cap = h->cfg.ring_samples, mb = h->cfg.max_block;
     const int eb = h->elem_bytes;
     int64_t done = 0;
@@ -294,24 +295,24 @@ static int write_at(gb200_trk* h, uint64_t abs_start, const void* src, int64_t n
             const int64_t pos = (int64_t)((abs_start + (uint64_t)done) % (uint64_t)cap);
             const int64_t run = std::min<int64_t>(n - done, cap - pos);
             const char* s = static_cast<const char*>(src) + done * eb;
-            GB_CUDA(cudaMemcpyAsync(h->d_ring + pos * eb, s, (size_t)run * eb, kind, h->stream));
+            GB_CUDA(cudaMemcpyAsync(h->d_ring + pos * eb, s, (size_t)run * eb, kind, stream));
             if (pos < mb)  // mirror the part that falls in [0, max_block) behind the end of the ring
                 {
                     const int64_t m = std::min<int64_t>(run, mb - pos);
-                    GB_CUDA(cudaMemcpyAsync(h->d_ring + (cap + pos) * eb, s, (size_t)m * eb, kind, h->stream));
+                    GB_CUDA(cudaMemcpyAsync(h->d_ring + (cap + pos) * eb, s, (size_t)m * eb, kind, stream));
                 }
             done += run;
         }
     return GB200_OK;
 }
 
-static int push_impl(gb200_trk* h, const void* src, int64_t n, uint64_t* first_index, cudaMemcpyKind kind)
+static int push_impl(gb200_trk* h, const void* src, int64_t n, uint64_t* first_index, cudaMemcpyKind kind, cudaStream_t stream = nullptr)
 {
     if (!h || (!src && n > 0)) return set_error(GB200_EINVAL, "null argument");
     if (n < 0 || n > h->cfg.ring_samples) return set_error(GB200_EINVAL, "push of %lld samples exceeds the ring (%lld)", (long long)n, (long long)h->cfg.ring_samples);
     GB_CUDA(cudaSetDevice(h->cfg.device));
     if (first_index) *first_index = h->head;
-    const int rc = write_at(h, h->head, src, n, kind);
+    const int rc = write_at(h, h->head, src, n, kind, stream);
     if (rc) return rc;
     h->head += (uint64_t)n;
     return GB200_OK;

@@ -245,6 +245,23 @@ class TrackingLoop:
         k = min(n.value, len(self._rec))
         return self._rec[:k].copy() if copy else self._rec[:k]
 
+    def submit(self, iq=None):
+        """pipelined form: enqueue a step and return at once (`iq` must stay alive, and should be page-locked, until collected)"""
+        if iq is None:
+            ptr, ns = None, 0
+        else:
+            iq = np.ascontiguousarray(iq)
+            ns = iq.size if self.engine.iq_dtype == IQ_CF32 else iq.size // 2
+            ptr = iq.ctypes.data
+        check(self._lib.gb200_loop_submit(self._h, ptr, ns))
+
+    def collect(self, copy=True):
+        """records of the oldest submitted step"""
+        n = C.c_int()
+        check(self._lib.gb200_loop_collect(self._h, self._rec.ctypes.data, len(self._rec), C.byref(n)))
+        k = min(n.value, len(self._rec))
+        return self._rec[:k].copy() if copy else self._rec[:k]
+
     def channel(self, ch):
         s = LoopChannelState()
         check(self._lib.gb200_loop_channel(self._h, ch, C.byref(s)))

@@ -260,6 +260,11 @@ int gb200_loop_stop(gb200_loop* l, int ch);
 /* One step.  Appends n_samples of the engine's item type from host memory (NULL / 0: none), runs every round that is due and
  * copies the records emitted during this step to `records` (at most max_records; *n_records receives how many were emitted). */
 int gb200_loop_step(gb200_loop* l, const void* iq_host, int64_t n_samples, gb200_loop_record* records, int max_records, int* n_records);
+/* Pipelined form: gb200_loop_submit enqueues the upload, the rounds and the counters' download and returns at once; gb200_loop_collect waits
+ * for the OLDEST submitted step and hands its records over.  Up to two steps may be in flight (the host reads step k while the device runs
+ * step k + 1); at most 7 code periods of samples per submit.  `iq_host` must stay valid — and should be page-locked — until collected. */
+int gb200_loop_submit(gb200_loop* l, const void* iq_host, int64_t n_samples);
+int gb200_loop_collect(gb200_loop* l, gb200_loop_record* records, int max_records, int* n_records);
 int gb200_loop_channel(gb200_loop* l, int ch, gb200_loop_channel_state* out);
 /* correlator outputs of the last correlated round of channel ch: n_correlators complex values (out[t] = tap t) */
 int gb200_loop_read_taps(gb200_loop* l, int ch, gb200_cf32* out);
