@@ -606,65 +606,77 @@ __global__ void __launch_bounds__(128) trk_loop_kernel(const LoopConf* __restric
     }
     __syncthreads();
     const int ch = blockIdx.x * blockDim.x + threadIdx.x;
-    if (ch >= n_channels) return;
-    LoopState s = states[ch];
-    if (s.planned)
+    const bool valid = ch < n_channels;
+    bool planned_now = false, ready_again = false, bad = false;
+    if (valid)
         {
-            float2 taps[GB200_MAX_TAPS];
-            const float2* o = reinterpret_cast<const float2*>(outs) + (size_t)ch * TRK_OUT_STRIDE;
-            for (int t = 0; t < k.n_taps; t++) taps[t] = o[t];
-            loop_finish(k, s, ch, taps, records, max_records, cnt);
-            s.nitems_read += (unsigned long long)s.current_prn_length_samples;  // consume_each(d_current_prn_length_samples), :2092
-            s.planned = 0;
-        }
-    const unsigned long long need = 2ull * (unsigned long long)k.c.vector_length;  // forecast(): 2 * vector_length items (:607-614)
-    for (int it = 0; it < 2; it++)
-        {
-            if (s.state == 0)
+            LoopState& s = states[ch];  // worked on in place: a thread touches a fraction of its 900-byte state per round (a local copy
+                                        // cost more in local-memory traffic than the whole loop closure)
+            if (s.planned)
                 {
-                    s.nitems_read = head;  // standby consumes whatever arrives (:1746-1752)
+                    float2 taps[GB200_MAX_TAPS];
+                    const float2* o = reinterpret_cast<const float2*>(outs) + (size_t)ch * TRK_OUT_STRIDE;
+                    for (int t = 0; t < k.n_taps; t++) taps[t] = o[t];
+                    loop_finish(k, s, ch, taps, records, max_records, cnt);
+                    s.nitems_read += (unsigned long long)s.current_prn_length_samples;  // consume_each(d_current_prn_length_samples), :2092
+                    s.planned = 0;
+                }
+            const unsigned long long need = 2ull * (unsigned long long)k.c.vector_length;  // forecast(): 2 * vector_length items (:607-614)
+            for (int it = 0; it < 2; it++)
+                {
+                    if (s.state == 0)
+                        {
+                            s.nitems_read = head;  // standby consumes whatever arrives (:1746-1752)
+                            break;
+                        }
+                    if (s.nitems_read + need > head) break;
+                    if (s.pull_in_transitory && (unsigned long long)k.c.pull_in_time_s < (s.nitems_read - s.acq_sample_stamp) / (unsigned long long)(int)k.c.fs_in)
+                        {
+                            s.pull_in_transitory = 0;  // :1738-1747
+                            s.carrier_lock_fail_counter = 0;
+                            s.code_lock_fail_counter = 0;
+                        }
+                    if (s.state == 1)
+                        {
+                            // pull-in: skip samples until the incoming code is aligned with the local replica (:1757-1788)
+                            const long long acq_trk_diff_samples = (long long)s.nitems_read - (long long)s.acq_sample_stamp;
+                            const double delta_trk_to_acq_prn_start_samples = (double)acq_trk_diff_samples - s.acq_code_phase_samples;
+                            s.code_freq_chips = k.c.code_chip_rate;
+                            s.code_phase_step_chips = s.code_freq_chips / k.c.fs_in;
+                            const double T_prn_mod_samples = (1.0 / s.code_freq_chips) * (double)k.c.code_length_chips * k.c.fs_in;
+                            s.acq_code_phase_samples = T_prn_mod_samples - fmod(delta_trk_to_acq_prn_start_samples, T_prn_mod_samples);
+                            s.current_prn_length_samples = (int)round(T_prn_mod_samples);
+                            const int samples_offset = (int)round(s.acq_code_phase_samples);
+                            s.acc_carrier_phase_rad -= s.carrier_phase_step_rad * (double)samples_offset;
+                            s.state = 2;
+                            loop_smoother_reset(s.cn0_smoother);
+                            loop_smoother_reset(s.lock_smoother);
+                            s.nitems_read += (unsigned long long)samples_offset;
+                            continue;
+                        }
+                    TrkDevCmd d;
+                    loop_write_cmd(k, s, ch, d);
+                    if (k.max_code_step_run > 0.0F && !(d.code_step <= k.max_code_step_run && d.code_step >= 1e-3F))
+                        {
+                            s.error = 1;  // outside what the selected correlator kernel serves: reported by gb200_loop_step, never silently mis-correlated
+                            bad = true;
+                            break;
+                        }
+                    cmds[ch] = d;
+                    s.planned = 1;
+                    planned_now = true;
+                    ready_again = head - s.nitems_read >= need + (unsigned long long)k.c.vector_length;
                     break;
                 }
-            if (s.nitems_read + need > head) break;
-            if (s.pull_in_transitory && (unsigned long long)k.c.pull_in_time_s < (s.nitems_read - s.acq_sample_stamp) / (unsigned long long)(int)k.c.fs_in)
-                {
-                    s.pull_in_transitory = 0;  // :1738-1747
-                    s.carrier_lock_fail_counter = 0;
-                    s.code_lock_fail_counter = 0;
-                }
-            if (s.state == 1)
-                {
-                    // pull-in: skip samples until the incoming code is aligned with the local replica (:1757-1788)
-                    const long long acq_trk_diff_samples = (long long)s.nitems_read - (long long)s.acq_sample_stamp;
-                    const double delta_trk_to_acq_prn_start_samples = (double)acq_trk_diff_samples - s.acq_code_phase_samples;
-                    s.code_freq_chips = k.c.code_chip_rate;
-                    s.code_phase_step_chips = s.code_freq_chips / k.c.fs_in;
-                    const double T_prn_mod_samples = (1.0 / s.code_freq_chips) * (double)k.c.code_length_chips * k.c.fs_in;
-                    s.acq_code_phase_samples = T_prn_mod_samples - fmod(delta_trk_to_acq_prn_start_samples, T_prn_mod_samples);
-                    s.current_prn_length_samples = (int)round(T_prn_mod_samples);
-                    const int samples_offset = (int)round(s.acq_code_phase_samples);
-                    s.acc_carrier_phase_rad -= s.carrier_phase_step_rad * (double)samples_offset;
-                    s.state = 2;
-                    loop_smoother_reset(s.cn0_smoother);
-                    loop_smoother_reset(s.lock_smoother);
-                    s.nitems_read += (unsigned long long)samples_offset;
-                    continue;
-                }
-            TrkDevCmd d;
-            loop_write_cmd(k, s, ch, d);
-            if (k.max_code_step_run > 0.0F && !(d.code_step <= k.max_code_step_run && d.code_step >= 1e-3F))
-                {
-                    s.error = 1;  // outside what the selected correlator kernel serves: reported by gb200_loop_step, never silently mis-correlated
-                    atomicAdd(&cnt->n_errors, 1u);
-                    break;
-                }
-            cmds[ch] = d;
-            s.planned = 1;
-            atomicAdd(&cnt->n_planned, 1u);
-            if (head - s.nitems_read >= need + (unsigned long long)k.c.vector_length) atomicAdd(&cnt->n_ready_again, 1u);
-            break;
+            if (!s.planned) cmds[ch].n = 0;
         }
-    if (!s.planned) cmds[ch].n = 0;
-    states[ch] = s;
+    // counters: one atomic per warp (10^4 single atomics on one address cost more than the loop closure itself)
+    const unsigned m_planned = __ballot_sync(0xffffffffu, planned_now), m_again = __ballot_sync(0xffffffffu, ready_again), m_bad = __ballot_sync(0xffffffffu, bad);
+    if ((threadIdx.x & 31) == 0)
+        {
+            if (m_planned) atomicAdd(&cnt->n_planned, (unsigned)__popc(m_planned));
+            if (m_again) atomicAdd(&cnt->n_ready_again, (unsigned)__popc(m_again));
+            if (m_bad) atomicAdd(&cnt->n_errors, (unsigned)__popc(m_bad));
+        }
 }
 }  // namespace gb200
