@@ -59,6 +59,12 @@ constexpr int trk_run_len(int iq, bool long_run)
 {
     return iq == GB200_IQ_CF32 ? (long_run ? 18 : 10) : iq == GB200_IQ_CS16 ? (long_run ? 20 : 12) : (long_run ? 24 : 8);
 }
+// extra-long variant (cf32 only: 22 samples = 11 chunks; the next odd chunk count of the integer types is already past one table entry
+// per run at every rate where their long variant applies).  Measured at 10 240 channels x 25 000 samples x 11 taps: 0.295 against
+// 0.306 ms per step (fewer runs per sample: the per-run boundary search and the tap phase are amortised over 22 samples)
+constexpr int TRK_RUN_XLONG = 22;
+// one table boundary per run at most: the law's argument grows by (R - 1) * step over a run, kept below 1 with room for its fp32 rounding
+inline bool trk_run_xlong_fits(int iq, double max_step) { return iq == GB200_IQ_CF32 && max_step * (TRK_RUN_XLONG - 1) <= 0.92; }
 
 // fraction of a turn in [0,1) -> 64-bit fixed point
 inline unsigned long long turns_to_fix(double turns)
@@ -122,6 +128,7 @@ cudaError_t launch_run_RG(gb200_trk* h)
 {
     constexpr int CH_LONG = IQ == GB200_IQ_CF32 ? 9 : IQ == GB200_IQ_CS16 ? 5 : 3;
     constexpr int CH_SHORT = IQ == GB200_IQ_CF32 ? 5 : IQ == GB200_IQ_CS16 ? 3 : 1;
+    if (IQ == GB200_IQ_CF32 && h->last_R == TRK_RUN_XLONG) return launch_run_one<T, GB200_IQ_CF32, 11>(h);
     return h->last_R == trk_run_len(IQ, true) ? launch_run_one<T, IQ, CH_LONG>(h) : launch_run_one<T, IQ, CH_SHORT>(h);
 }
 
@@ -212,10 +219,13 @@ int gb200_trk_create(const gb200_trk_config* cfg, gb200_trk** out)
     if (cfg->iq_dtype < GB200_IQ_CF32 || cfg->iq_dtype > GB200_IQ_CS8) return set_error(GB200_EINVAL, "unknown iq_dtype %d", cfg->iq_dtype);
     if (cfg->ring_samples < 2LL * cfg->max_block) return set_error(GB200_EINVAL, "ring_samples must be >= 2*max_block");
     if (cfg->max_block > (1 << 22)) return set_error(GB200_EINVAL, "max_block above 2^22 samples is not supported");
+    if (cfg->max_cmds > 65535) return set_error(GB200_EINVAL, "max_cmds %d above 65535 (one launch indexes its commands with gridDim.y)", cfg->max_cmds);
     int rc = select_device(cfg->device);
     if (rc) return rc;
     gb200_trk* h = new (std::nothrow) gb200_trk;
     if (!h) return set_error(GB200_ENOMEM, "out of host memory");
+    // every allocation below goes through one failure path: a handle that could not be completed is torn down, never leaked
+    rc = [&]() -> int {
     h->cfg = *cfg;
     h->elem_bytes = cfg->iq_dtype == GB200_IQ_CF32 ? 8 : cfg->iq_dtype == GB200_IQ_CS16 ? 4 : 2;
     cudaDeviceProp p;
@@ -241,6 +251,13 @@ int gb200_trk_create(const gb200_trk_config* cfg, gb200_trk** out)
     GB_CUDA(cudaMalloc(&h->d_counters, (size_t)cfg->max_cmds * sizeof(unsigned)));
     GB_CUDA(cudaMemsetAsync(h->d_counters, 0, (size_t)cfg->max_cmds * sizeof(unsigned), h->stream));
     GB_CUDA(cudaStreamSynchronize(h->stream));
+    return GB200_OK;
+    }();
+    if (rc)
+        {
+            gb200_trk_destroy(h);
+            return rc;
+        }
     *out = h;
     return GB200_OK;
 }
@@ -249,7 +266,7 @@ int gb200_trk_destroy(gb200_trk* h)
 {
     if (!h) return GB200_OK;
     cudaSetDevice(h->cfg.device);
-    cudaStreamSynchronize(h->stream);
+    if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->d_ring);
     cudaFree(h->d_raw);
     cudaFree(h->d_codes);
@@ -259,9 +276,10 @@ int gb200_trk_destroy(gb200_trk* h)
     cudaFreeHost(h->h_out);
     cudaFree(h->d_partials);
     cudaFree(h->d_counters);
-    cudaEventDestroy(h->ev0);
-    cudaEventDestroy(h->ev1);
-    cudaStreamDestroy(h->stream);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    (void)cudaGetLastError();
     delete h;
     return GB200_OK;
 }

@@ -1,5 +1,6 @@
 // Tracking multicorrelator, run-based kernel (K1b) for sm_100a — used when the code advances by less than one table entry
-// over a run of R samples (R * code_step <= 0.9: e.g. GPS L1 at >= 12 MS/s, Galileo E1 at >= 25 MS/s).
+// over a run of R samples (R * code_step <= 0.9, or 21 * code_step <= 0.92 for the 22-sample cf32 tier: e.g. GPS L1 at >= 12 MS/s,
+// Galileo E1 at >= 25 MS/s).
 //
 // Same contract as trk_kernel.cuh (Cpu_Multicorrelator_Real_Codes::Carrier_wipeoff_multicorrelator_resampler,
 // src/algorithms/tracking/libs/cpu_multicorrelator_real_codes.cc:103-126), different work decomposition:
@@ -8,7 +9,7 @@
 //     (cp.async.bulk + the warp's mbarrier); a lane pulls its run into registers, and as soon as the warp's runs are consumed
 //     (after the wipe-off) lane 0 issues the copy of the NEXT tile into the same buffer, so the transfer overlaps the tap phase
 //     and the next tile's set-up: registers are the second buffer, and there is no block-wide barrier inside the tile loop.
-//     R is chosen so that a run is an ODD number of 16-byte chunks (cf32: 18 or 10 samples, int16: 20 or 12, int8: 24 or 8):
+//     R is chosen so that a run is an ODD number of 16-byte chunks (cf32: 22, 18 or 10 samples, int16: 20 or 12, int8: 24 or 8):
 //     the lanes' 128-bit reads of the plain contiguous rows are then conflict-free without padding;
 //   * a lane owns one run: it wipes the carrier off once, keeps the R prefix sums of the wiped samples, and for every
 //     tap finds the single chip boundary inside the run, so a tap costs O(1) per run instead of O(R):

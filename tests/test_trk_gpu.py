@@ -196,10 +196,14 @@ def test_ring_wraparound_and_errors():
 
 
 @pytest.mark.parametrize("fs,L,chip_rate,nt,spacing,iq_dtype,nch", [
-    (25e6, 1023, 1.023e6, 11, 0.1, 0, 1536),     # C3 GPS L1: R = 16, groups of 4
-    (25e6, 8184, 2.046e6, 5, 0.3, 0, 640),        # C3 Galileo E1 (2 entries per chip): R = 8
+    (25e6, 1023, 1.023e6, 11, 0.1, 0, 1536),     # C3 GPS L1: runs of 22 samples (extra-long tier)
+    (25e6, 1023, 1.023e6, 3, 0.5, 0, 700),        # the same rate with the plain E/P/L taps: R = 22, T = 3
+    (25e6, 1023, 1.023e6, 5, 0.15, 0, 700),       # ... and the VE/E/P/L/VL set: R = 22, T = 5
+    (23.4e6, 1023, 1.023e6, 11, 0.1, 0, 600),     # code step 0.0437: the last rate the extra-long tier accepts (21 * step <= 0.92)
+    (20e6, 1023, 1.023e6, 11, 0.1, 0, 600),       # R = 18
+    (25e6, 8184, 2.046e6, 5, 0.3, 0, 640),        # C3 Galileo E1 (2 entries per chip): R = 10
     (100e6, 1023, 1.023e6, 11, 0.05, 2, 1280),    # C5: int8 IQ at 100 MS/s
-    (25e6, 1023, 1.023e6, 3, 0.5, 1, 400),        # int16, windows too far apart to share tiles: G = 1
+    (25e6, 1023, 1.023e6, 3, 0.5, 1, 400),        # int16, windows far apart
 ])
 def test_run_based_kernel_many_channels(fs, L, chip_rate, nt, spacing, iq_dtype, nch):
     """Enough channels for the run-based kernel (trk_run_kernel): every channel against the fp32 oracle, a sample of them
