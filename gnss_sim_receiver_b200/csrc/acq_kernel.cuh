@@ -81,31 +81,39 @@ __device__ __forceinline__ float2 acq_wiped_sample(const void* iq, int n, int co
 }
 
 // fp32 phase accumulation of the reference: tab[bin][n] = phase before sample n, accumulated by repeated fp32 addition (the order of
-// volk_gnsssdr_s32f_sincos_32fc_generic, so the values are the reference's bit for bit).  The recurrence is serial per bin: a lane owns
-// a bin; every 32 samples the warp transposes its 32 x 32 tile through shared memory so that the rows go out as coalesced 128-byte
-// stores (one thread per bin with strided 4-byte stores took as long as a whole sweep).
-constexpr int ACQ_PT_WARPS = 4;
-__global__ void __launch_bounds__(32 * ACQ_PT_WARPS) acq_phase_table_kernel(const float* __restrict__ inc, int n_bins, int n, float* __restrict__ tab)
+// volk_gnsssdr_s32f_sincos_32fc_generic, so the values are the reference's bit for bit).  The recurrence is serial per bin (25 000
+// dependent additions: ~50 us of FADD latency whatever the layout), so the kernel is laid out for the store side: one warp per CTA owns
+// ACQ_PT_BINS bins (80 bins -> 10 SMs instead of one), lanes 0..ACQ_PT_BINS-1 run the recurrences over a chunk of ACQ_PT_CHUNK samples
+// into shared memory, then all 32 lanes write the chunk's rows as coalesced 128-byte stores.
+constexpr int ACQ_PT_BINS = 8;
+constexpr int ACQ_PT_CHUNK = 128;
+__global__ void __launch_bounds__(32) acq_phase_table_kernel(const float* __restrict__ inc, int n_bins, int n, float* __restrict__ tab)
 {
-    __shared__ float tile[ACQ_PT_WARPS][32][33];
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int bin0 = (blockIdx.x * ACQ_PT_WARPS + w) * 32;
-    if (bin0 >= n_bins) return;
-    const int bin = bin0 + lane;
-    const float d = bin < n_bins ? inc[bin] : 0.0f;
-    const int rows = min(32, n_bins - bin0);
+    __shared__ float tile[ACQ_PT_BINS][ACQ_PT_CHUNK + 1];
+    const int lane = threadIdx.x;
+    const int bin0 = blockIdx.x * ACQ_PT_BINS;
+    const int rows = min(ACQ_PT_BINS, n_bins - bin0);
+    const float d = lane < rows ? inc[bin0 + lane] : 0.0f;
     float ph = 0.0f;
-    for (int i0 = 0; i0 < n; i0 += 32)
+    for (int i0 = 0; i0 < n; i0 += ACQ_PT_CHUNK)
         {
-#pragma unroll
-            for (int k = 0; k < 32; k++)
+            if (lane < rows)
                 {
-                    tile[w][lane][k] = ph;
-                    ph = __fadd_rn(ph, d);
+#pragma unroll 16
+                    for (int k = 0; k < ACQ_PT_CHUNK; k++)
+                        {
+                            tile[lane][k] = ph;
+                            ph = __fadd_rn(ph, d);
+                        }
                 }
             __syncwarp();
-            if (i0 + lane < n)
-                for (int r = 0; r < rows; r++) tab[(size_t)(bin0 + r) * n + i0 + lane] = tile[w][r][lane];
+            for (int r = 0; r < rows; r++)
+                {
+                    float* row = tab + (size_t)(bin0 + r) * n + i0;
+#pragma unroll
+                    for (int j = 0; j < ACQ_PT_CHUNK; j += 32)
+                        if (i0 + j + lane < n) row[j + lane] = tile[r][j + lane];
+                }
             __syncwarp();
         }
 }

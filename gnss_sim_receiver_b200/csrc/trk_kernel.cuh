@@ -104,6 +104,7 @@ __global__ void __launch_bounds__(TRK_THREADS) trk_correlate_kernel(const TrkDev
     extern __shared__ __align__(16) float s_tab[];
     __shared__ float s_red[TRK_THREADS / 32][2 * T];
     __shared__ int s_last;
+    __shared__ unsigned s_adj;
 
     const TrkDevCmd& c = cmds[blockIdx.y];
     const int tid = threadIdx.x;
@@ -127,6 +128,7 @@ __global__ void __launch_bounds__(TRK_THREADS) trk_correlate_kernel(const TrkDev
             const int idx_lo = trk_raw_index(step, (float)n0, c.shift_min, rem);
             const int idx_hi = trk_raw_index(step, (float)(n1 - 1), c.shift_max, rem);
             const int span = idx_hi - idx_lo + 1;
+            if (tid == 0) s_adj = smem_u32(s_tab) - (unsigned)(0x4B400000 + idx_lo) * (CPLX ? 8u : 4u);
             {
                 int k = math_mod(idx_lo + tid, L);
                 const int adv = TRK_THREADS % L;
@@ -150,7 +152,8 @@ __global__ void __launch_bounds__(TRK_THREADS) trk_correlate_kernel(const TrkDev
             const f32x2 MG = pk2(MAGIC, MAGIC), REM = pk2(rem, rem);
             // shared address of table entry j = bits(RD(x + MAGIC)) - bias:  tab_adj + ESZ * bits  (one multiply-add per tap)
             constexpr unsigned ESZ = CPLX ? 8u : 4u;
-            const unsigned tab_adj = smem_u32(s_tab) - (unsigned)(0x4B400000 + idx_lo) * ESZ;
+            // (read back through shared memory: given the constant, ptxas splits it off again and spends a LEA and an IADD3 per tap)
+            const unsigned tab_adj = *reinterpret_cast<volatile unsigned*>(&s_adj);
             const unsigned long long u0 = c.u0, du = c.du;
             const void* iq = c.iq;
             const float2 stp = trk_phasor(du * (unsigned long long)TRK_THREADS);

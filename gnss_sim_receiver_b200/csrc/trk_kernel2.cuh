@@ -163,6 +163,7 @@ __global__ void __launch_bounds__(TRK2_THREADS, trk2_min_blocks<IQ, CH>()) trk_r
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(8) uint64_t s_bar[TRK2_WARPS];
     __shared__ float s_red[TRK2_WARPS][2 * T];
+    __shared__ unsigned s_hide[TRK2_WARPS][2];
 
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     unsigned char* my_rows = smem + w * WROW_BYTES;
@@ -192,9 +193,15 @@ __global__ void __launch_bounds__(TRK2_THREADS, trk2_min_blocks<IQ, CH>()) trk_r
         {
             mbar_init(&s_bar[w], 1);
             fence_barrier_init();
+            s_hide[w][0] = 0u - (unsigned)MAGICBITS;
+            s_hide[w][1] = 0u;
         }
     my_pref[lane] = make_float2(0.0f, 0.0f);  // P[0]
     __syncwarp();
+    // -bits(MAGIC) and a zero, read back through shared memory so that ptxas cannot see them: knowing the constant, it splits the biased
+    // table and prefix addresses below into (variable part) + constant again, and without the XOR it re-associates tab_adj + 8 * bits into
+    // (bits + variable) * 8 + base — either way an extra IADD3 per tap
+    const unsigned hide = *reinterpret_cast<volatile unsigned*>(&s_hide[w][0]), zero = *reinterpret_cast<volatile unsigned*>(&s_hide[w][1]);
     const unsigned char* src = ring + ((size_t)tile0 + (size_t)w * WROW) * EB;
     if (lane == 0)
         {
@@ -247,7 +254,7 @@ __global__ void __launch_bounds__(TRK2_THREADS, trk2_min_blocks<IQ, CH>()) trk_r
             const int n0w = lead + tile * TILE + w * WROW;  // sample index of the warp's first staged sample
             const int nr = n0w + lane * R;                  // ... and of this lane's run
             // ---- install the window fetched during the previous tile
-            const unsigned tab_adj = tab_a - (unsigned)(MAGICBITS + win_lo) * 8u;  // address of entry j = tab_adj + 8 * bits(RD(x + MAGIC))
+            const unsigned tab_adj = (tab_a + (hide - (unsigned)win_lo) * 8u) ^ zero;  // address of entry j = tab_adj + 8 * bits(RD(x + MAGIC))
             {
                 if (lane < win_span) st_shared_f2(tab_a + 8u * lane, pre_c - pre_c1, pre_c1);
                 if (win_span > 32)  // wide tap spans only: the rest of the window, fetched here
@@ -319,7 +326,7 @@ __global__ void __launch_bounds__(TRK2_THREADS, trk2_min_blocks<IQ, CH>()) trk_r
                     const float a0 = __fmul_rn(step, nf);
                     const f32x2 A0 = pk2(a0, a0), REM = pk2(rem, rem), INV = pk2(inv_step, inv_step), MG = pk2(MAGIC, MAGIC), NFM = pk2(nfm, nfm);
                     const float kq_max = MAGIC + (float)R;
-                    const unsigned pref_adj = pref_addr + 256u - (unsigned)MAGICBITS * 256u;  // address of P[k] = pref_adj + 256 * (bits(MAGIC + k) - 1)
+                    const unsigned pref_adj = (pref_addr + 256u + hide * 256u) ^ zero;  // address of P[k] = pref_adj + 256 * (bits(MAGIC + k) - 1)
 #pragma unroll
                     for (int p = 0; p < TP; p++)
                         {
