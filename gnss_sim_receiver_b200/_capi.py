@@ -88,6 +88,7 @@ SYMBOLS = {
     "gb200_trk_read_iq": (C.c_int, [_vp, C.c_uint64, _vp, C.c_int64]),
     "gb200_trk_head": (C.c_uint64, [_vp]),
     "gb200_trk_correlate": (C.c_int, [_vp, _vp, C.c_int, _vp]),
+    "gb200_trk_correlate_noalloc": (C.c_int, [C.c_int, _vp, C.c_int64, _vp, C.c_int, C.c_int, _vp, C.c_int, _vp, _vp]),
     "gb200_trk_enqueue": (C.c_int, [_vp, _vp, C.c_int]),
     "gb200_trk_collect": (C.c_int, [_vp, _vp]),
     "gb200_trk_replay": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),

@@ -377,3 +377,4 @@ uint64_t gb200_trk_head(const gb200_trk* h) { return h ? h->head : 0; }
 #include "ingest.inc"
 #include "trk_submit.inc"
 #include "trk_loop.inc"
+#include "trk_noalloc.inc"

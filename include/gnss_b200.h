@@ -175,6 +175,30 @@ int gb200_trk_collect(gb200_trk* h, gb200_cf32* out);
 /* Re-launch the most recently enqueued command set `iters` times with inputs and commands
  * resident on the device; *ms_per_iter = CUDA-event time / iters on the engine's stream. */
 int gb200_trk_replay(gb200_trk* h, int iters, float* ms_per_iter);
+/* Allocation-free correlate.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Same arithmetic as gb200_trk_correlate's general kernel (trk_correlate_kernel: real codes, gr_complex IQ), but with no engine
+ * handle: the caller passes DEVICE pointers for the inputs and the output, and everything the kernel needs besides them (the device
+ * copy of the commands, the per-chunk partial sums and the per-command arrival counters) lives in ONE file-scope
+ * `static __device__` array of GB200_NOALLOC_SCRATCH_BYTES inside the library, held by every GPU that loads the library until exit.
+ * The call performs no cudaMalloc / cudaFree / cudaHostAlloc and no other allocating library routine.
+ *   iq_dev     n_iq gr_complex samples in device memory; cmds[i].sample_offset indexes it from 0 (window must lie inside [0, n_iq))
+ *   codes_dev  n_codes tables of code_len floats each, device memory, table c at codes_dev + c * code_len; cmds[i].ch selects
+ *   cmds       HOST array, same fields and meaning as for gb200_trk_correlate (GB200_TRK_HIGH_DYN is rejected)
+ *   out_dev    device memory for n_cmds * GB200_MAX_TAPS gb200_cf32; out_dev[i * GB200_MAX_TAPS + t], t < padded tap count
+ *              (1, 2, 3, 5, 8, 11 or 16 — the next size up from the largest n_taps), is written, the rest of a slot is left untouched
+ *   stream     a cudaStream_t passed as void* (NULL = the legacy default stream); the work is queued on it and the call returns
+ *              after synchronising that stream, i.e. with out_dev complete
+ * Limits (GB200_EINVAL with a message beyond them): n_cmds <= GB200_NOALLOC_MAX_CMDS, n_samples <= GB200_NOALLOC_MAX_SAMPLES.
+ * All calls on a device share the one scratch array, which keeps the previous call's contents; the entry point clears what must
+ * start at zero (the arrival counters) on every call.  Calls that OVERLAP on the same GPU (two host threads, or two streams) race on
+ * it and produce garbage: serialise them.  A process that never calls this pays only the array's device memory. */
+#define GB200_NOALLOC_MAX_CMDS 64
+#define GB200_NOALLOC_MAX_CHUNKS 64
+#define GB200_NOALLOC_MAX_SAMPLES (GB200_NOALLOC_MAX_CHUNKS * 16384)
+#define GB200_NOALLOC_SCRATCH_BYTES (GB200_NOALLOC_MAX_CMDS * 256 + GB200_NOALLOC_MAX_CMDS * 4 + GB200_NOALLOC_MAX_CMDS * GB200_NOALLOC_MAX_CHUNKS * 2 * GB200_MAX_TAPS * 4)
+int gb200_trk_correlate_noalloc(int device, const gb200_cf32* iq_dev, int64_t n_iq, const float* codes_dev, int code_len, int n_codes,
+    const gb200_trk_cmd* cmds, int n_cmds, gb200_cf32* out_dev, void* stream);
 /* name of the kernel variant the last enqueue selected (diagnostics / bench reporting), e.g.
  * "trk_correlate_kernel<T=11,chunks=2>" or "trk_run_kernel<T=11,R=16,G=4>" */
 const char* gb200_trk_last_kernel(const gb200_trk* h);
