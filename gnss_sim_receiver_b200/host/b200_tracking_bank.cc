@@ -64,8 +64,8 @@ int B200TrackingBank::step(std::vector<Output>* out)
                         }
                 }
             if (cmds_.empty()) return launches;
-            // one launch for the whole round; main and data commands differ in tap count, so they go in separate calls
-            // only when both kinds are present (a launch is specialised on the padded tap count)
+            // one launch for the whole round: main and data commands go in the same call (a launch is specialised on the padded tap
+            // count of the widest command, narrower ones are padded); split only by the engine's command capacity
             res_.resize(cmds_.size() * GB200_MAX_TAPS);
             const int cap = engine_->config().max_channels;
             for (size_t b = 0; b < cmds_.size(); b += cap)
