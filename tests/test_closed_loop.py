@@ -481,3 +481,149 @@ def test_device_loop_many_channels_run_kernel():
     assert launches <= 2 * periods + 2 * 40, launches  # correlate + loop kernel per period, a few catch-up rounds
     loop.close()
     eng.close()
+
+
+# ------------------------------------------------------------------------------------------------ device loop on the other served signals
+def _compare_device_with_ref(loop, loops, got, ref, nsat, truth_doppler, label, min_records, data_field="prompt_i"):
+    for k in range(nsat):
+        g, r = np.concatenate(got[k]), np.concatenate(ref[k])
+        gs, rs = loop.channel(k), loops[k].state()
+        assert rs["state"] == 4 and gs["state"] == 4, (label, k, gs, rs)
+        m = min(len(g), len(r))
+        assert m > min_records and len(r) - len(g) <= 6, (label, k, len(g), len(r))
+        g, r = g[:m], r[:m]
+        d_cnt = np.abs(g["tracking_sample_counter"].astype(np.int64) - r["tracking_sample_counter"].astype(np.int64))
+        assert d_cnt.max() <= 1, (label, k, d_cnt.max())
+        assert np.array_equal(g["correlation_length_ms"], r["correlation_length_ms"]), (label, k)
+        # telemetry symbols: identical signs on the data-bearing arm (with d_interchange_iq the record's Prompt_Q; the other arm is noise
+        # around zero), and both arms close in value
+        assert np.array_equal(np.sign(g[data_field]), np.sign(r[data_field])), (label, k)
+        amp = np.median(np.abs(r[data_field]))
+        for f in ("prompt_i", "prompt_q"):
+            assert np.max(np.abs(g[f][m // 4:] - r[f][m // 4:])) < 0.05 * amp, (label, k, f)
+        half = m // 2
+        d_cn0 = np.max(np.abs(g["cn0_db_hz"][half:] - r["cn0_db_hz"][half:]))
+        d_dop = np.sqrt(np.mean((g["carrier_doppler_hz"][half:] - r["carrier_doppler_hz"][half:]) ** 2))
+        print(f"[device loop {label}] ch {k}: records {m}, CN0 diff {d_cn0:.4f} dB, Doppler diff {d_dop:.4f} Hz rms")
+        assert d_cn0 < 0.1, (label, k, d_cn0)
+        assert d_dop < 0.5, (label, k, d_dop)
+        assert abs(np.mean(g["carrier_doppler_hz"][half:]) - truth_doppler[k]) < 2.0, (label, k)
+
+
+@pytest.mark.gpu
+@needs_ref
+def test_device_loop_galileo_e1b_vs_reference_objects():
+    """The device loop on Galileo E1B (data component, track_pilot=false: dll_pll_veml_tracking.cc:264-292): 4 ms codes of 8184 table
+    entries, the five-tap VEML correlator and discriminator, no secondary code, one symbol per code — against loops made of the
+    reference's own objects on the E1 open-service stream (E1-B minus E1-C), same gates as for GPS L1."""
+    from gnss_sim_receiver_b200.tracking import TrackingEngine, TrackingLoop, loop_config
+    nsat = 4
+    sc = e1_scenario(nsat, seed=23)
+    eng = TrackingEngine(max_channels=nsat, max_code_len=8184, ring_samples=4 * CHUNK, max_block=2 * 16000, max_cmds=nsat)
+    cfg = loop_config("1B", FS, pll_bw_hz=15.0, dll_bw_hz=0.75, pll_bw_narrow_hz=5.0, dll_bw_narrow_hz=0.2, early_late_space_chips=0.25,
+                      very_early_late_space_chips=0.5, early_late_space_narrow_chips=0.15, very_early_late_space_narrow_chips=0.5,
+                      pull_in_time_s=1, cn0_samples=20, cn0_min=25, max_code_lock_fail=50, max_carrier_lock_fail=5000, carrier_lock_th=0.5)
+    p = e1_ref_params()
+    p.track_pilot, p.secondary, p.secondary_code_length = 0, 0, 0
+    p.secondary_code = b""
+    cfg.slope, cfg.y_intercept = _e1_slope_intercept(0.25)
+    loops = []
+    for k in range(nsat):
+        eng.set_code(k, sc["data_code"][k])
+    loop = TrackingLoop(eng, cfg, nsat)
+    for k in range(nsat):
+        a = (int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+        loop.start(k, *a)
+        loops.append(O.RefLoop(p, sc["data_code"][k], None, *a))
+    got, ref = [[] for _ in range(nsat)], [[] for _ in range(nsat)]
+    for _, x in e1_chunks(sc, E1_SECONDS):
+        r = loop.step(x)
+        for k in range(nsat):
+            got[k].append(r[r["channel"] == k])
+            ref[k].append(loops[k].feed(x))
+    _compare_device_with_ref(loop, loops, got, ref, nsat, sc["doppler"], "E1B", 500)
+    for lp in loops:
+        lp.close()
+    loop.close()
+    eng.close()
+
+
+def _e1_slope_intercept(spc):
+    """slope / y_intercept the reference derives from SinBocCorrelationFunction<1,1> (dll_pll_veml_tracking.cc:275-277, tracking_discriminators.h):
+    taken from the host library's configuration reader, which is bit-checked against the reference's in tests/test_host_cpu.py"""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    lib = H.lib()
+    return float(np.float32(-lib.gb200h_sinboc_slope_abs(float(spc)))), float(np.float32(lib.gb200h_sinboc_yintercept_abs(float(spc))))
+
+
+L5_FS = 12.5e6
+L5_SECONDS = float(os.environ.get("GB200_LOOP_SECONDS_L5", "8"))
+# signal, secondary code (dll_pll_veml_tracking.cc:213-246 GPS_L5I_NH_CODE_STR; :296-330 GALILEO_E5A_I_SECONDARY_CODE), symbols per bit, d_interchange_iq
+L5_BAND = {"L5": ("0000110101", 10, 1), "5X": ("10000100001011101001", 20, 0)}
+
+
+def _l5_band_code(signal, prn):
+    import _signals as S
+    if signal == "L5":
+        return S.l5_table(prn)
+    return np.ascontiguousarray(S.e5a_primary(prn, "5I").real, dtype=np.float32)  # E5a-I primary code (the data component's table)
+
+
+@pytest.mark.gpu
+@needs_ref
+@pytest.mark.parametrize("signal", ["L5", "5X"])
+def test_device_loop_l5_band_vs_reference_objects(signal):
+    """The device loop on GPS L5I and Galileo E5aI (data components, dll_pll_veml_tracking.cc:213-246, :296-330): 10 230-chip codes at
+    10.23 Mcps (code step 0.82 entries per sample at 12.5 MS/s: the general correlator kernel), the secondary code (10-bit Neuman-Hofman /
+    20-bit CS20) synchronised and removed, extended integration over the symbols of a bit, Prompt_I / Prompt_Q interchanged for L5I —
+    against loops made of the reference's own objects."""
+    from gnss_sim_receiver_b200.tracking import TrackingEngine, TrackingLoop, loop_config
+    sec_str, spb, interchange = L5_BAND[signal]
+    nsat, fs = 3, L5_FS
+    chunk = int(fs * 0.1)
+    rng = np.random.default_rng(31 + spb)
+    prns = rng.choice(np.arange(1, 33), nsat, replace=False)
+    doppler, delay, phase = rng.uniform(-3000, 3000, nsat), rng.uniform(0, 10230, nsat), rng.uniform(0, 2 * np.pi, nsat)
+    cn0, acq_err = rng.uniform(44, 49, nsat), rng.uniform(-10, 10, nsat)
+    codes = np.stack([_l5_band_code(signal, int(p)) for p in prns])
+    sec = np.array([1 if c == "0" else -1 for c in sec_str], dtype=np.int8)
+    n_bits = 12000 // spb
+    bits = rng.choice(np.array([-1, 1], dtype=np.int8), (nsat, n_bits))
+    sym = (np.repeat(bits, spb, axis=1) * np.tile(sec, n_bits)[None, :]).astype(np.int8)  # one entry per 1 ms code period
+    f_chip = 10.23e6 * (1 + doppler / 1176.45e6)
+    acq_delay = np.mod(delay / f_chip * fs, fs / 1000.0)
+    kw = dict(pll_bw_hz=20.0, dll_bw_hz=1.5, pll_bw_narrow_hz=5.0, dll_bw_narrow_hz=0.5, early_late_space_chips=0.5, early_late_space_narrow_chips=0.25,
+              pull_in_time_s=1, cn0_samples=20, cn0_min=25, max_code_lock_fail=50, max_carrier_lock_fail=5000, carrier_lock_th=0.5)
+    cfg = loop_config(signal, fs, **kw)
+    assert (cfg.secondary_code.decode(), cfg.symbols_per_bit, cfg.interchange_iq) == (sec_str, spb, interchange)
+    p = ref_params(0)
+    p.fs_in, p.code_period, p.chip_rate, p.carrier_freq = fs, 0.001, 10.23e6, 1176.45e6
+    p.pll_bw, p.dll_bw, p.pll_bw_narrow, p.dll_bw_narrow, p.el, p.el_narrow = 20.0, 1.5, 5.0, 0.5, 0.5, 0.25
+    p.vector_length, p.veml, p.secondary, p.track_pilot, p.symbols_per_bit, p.samples_per_chip, p.code_length_chips = int(fs / 1000), 0, 1, 0, spb, 1, 10230
+    p.interchange_iq = interchange
+    p.secondary_code_length, p.data_secondary_code_length = len(sec_str), 0
+    p.secondary_code = sec_str.encode()
+    eng = TrackingEngine(max_channels=nsat, max_code_len=10230, ring_samples=4 * chunk, max_block=2 * int(fs / 1000), max_cmds=nsat)
+    for k in range(nsat):
+        eng.set_code(k, codes[k])
+    loop = TrackingLoop(eng, cfg, nsat)
+    loops = []
+    for k in range(nsat):
+        a = (int(prns[k]), float(acq_delay[k]), float(doppler[k] + acq_err[k]), 0, 0)
+        loop.start(k, *a)
+        loops.append(O.RefLoop(p, codes[k], None, *a))
+    got, ref = [[] for _ in range(nsat)], [[] for _ in range(nsat)]
+    n_total = int(L5_SECONDS * fs)
+    for first in range(0, n_total, chunk):
+        n = min(chunk, n_total - first)
+        x = O.gen_if(n, first, fs, codes, doppler, delay, phase, cn0, nav_bits=sym, periods_per_bit=1, f_chip=10.23e6, f_carrier=1176.45e6, seed=79)
+        r = loop.step(x)
+        for k in range(nsat):
+            got[k].append(r[r["channel"] == k])
+            ref[k].append(loops[k].feed(x))
+    assert loop.kernel.startswith("trk_correlate_kernel"), loop.kernel
+    _compare_device_with_ref(loop, loops, got, ref, nsat, doppler, signal, 250, data_field="prompt_q" if interchange else "prompt_i")
+    for lp in loops:
+        lp.close()
+    loop.close()
+    eng.close()
