@@ -6,6 +6,7 @@
 // restatement) and to generate tests/golden/*. Lives in oracle/_ref/libgnssref.so.
 #include "cpu_multicorrelator.h"
 #include "cpu_multicorrelator_16sc.h"
+#include "tracking_dump_reader.h"
 #include "cpu_multicorrelator_real_codes.h"
 #include "exponential_smoother.h"
 #include "galileo_e1_signal_replica.h"
@@ -205,6 +206,25 @@ void ref_exponential_smoother_run(float alpha, int init_samples, float min_value
     s.set_min_value(min_value);
     s.set_offset(offset);
     for (int i = 0; i < n; i++) out[i] = s.smooth(in[i]);
+}
+
+// ---- the reference's own reader of the tracking dump (src/tests/unit-tests/signal-processing-blocks/libs/tracking_dump_reader.cc) ----
+// out[e][10] per epoch: abs_E, abs_P, abs_L, prompt_I, prompt_Q, PRN_start_sample_count, carrier_doppler_hz, CN0_SNV_dB_Hz, carrier_lock_test, PRN
+long ref_trk_dump_read(const char* path, double* out, long max_epochs)
+{
+    Tracking_Dump_Reader r;
+    if (!r.open_obs_file(std::string(path))) return -1;
+    const long n = static_cast<long>(r.num_epochs());
+    long e = 0;
+    for (; e < n && e < max_epochs; e++)
+        {
+            if (!r.read_binary_obs()) break;
+            double* o = out + 10 * e;
+            o[0] = r.abs_E, o[1] = r.abs_P, o[2] = r.abs_L, o[3] = r.prompt_I, o[4] = r.prompt_Q;
+            o[5] = static_cast<double>(r.PRN_start_sample_count), o[6] = r.carrier_doppler_hz, o[7] = r.CN0_SNV_dB_Hz, o[8] = r.carrier_lock_test;
+            o[9] = static_cast<double>(r.PRN);
+        }
+    return n == e ? n : -2 - e;
 }
 
 }  // extern "C"

@@ -627,3 +627,53 @@ def test_device_loop_l5_band_vs_reference_objects(signal):
         lp.close()
     loop.close()
     eng.close()
+
+
+# ------------------------------------------------------------------------------------------------ tracking dump through the reference's reader
+@pytest.mark.gpu
+@needs_ref
+def test_tracking_dump_is_read_by_the_reference_reader(tmp_path):
+    """Tracking_XX.dump=true (dll_pll_veml_tracking.cc:1376-1470 log_data, :1675-1705 file naming): the per-channel .dat files the block
+    writes are read back with the reference's OWN reader (src/tests/unit-tests/signal-processing-blocks/libs/tracking_dump_reader.cc,
+    compiled into oracle/_ref) — whole epochs, and the fields agree with the Gnss_Synchro records of the same run."""
+    from gnss_sim_receiver_b200 import _hostapi as H
+    nsat, seconds = 3, 4.0
+    sc = scenario(nsat, seed=19)
+    base = str(tmp_path / "trk_dump_ch_")
+    bank = H.TrackingBank(CONF + f"Tracking_1C.dump=true\nTracking_1C.dump_filename={base}\n", "Tracking_1C", nsat)
+    for k in range(nsat):
+        bank.start(k, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+    got = [[] for _ in range(nsat)]
+    for _, x in stream_chunks(sc, seconds):
+        bank.push(x)
+        r = bank.step()
+        for k in range(nsat):
+            got[k].append(r[r["channel"] == k])
+    bank.close()  # closes the dump files
+    rd = O.ref().ref_trk_dump_read
+    rd.restype = O.C.c_long
+    rd.argtypes = [O.C.c_char_p, O.C.c_void_p, O.C.c_long]
+    for k in range(nsat):
+        path = base + f"{k}.dat"
+        assert os.path.exists(path), os.listdir(tmp_path)
+        assert os.path.getsize(path) % (8 + 8 + 19 * 4 + 4) == 0  # whole epochs of the reference's record (tracking_dump_reader.cc:74-79)
+        buf = np.zeros((8192, 10), dtype=np.float64)
+        n = rd(path.encode(), buf.ctypes.data, len(buf))
+        assert n > 1500, (k, n)
+        d = buf[:n]
+        g = np.concatenate(got[k])
+        assert np.all(d[:, 9] == sc["prn"][k])
+        # one dump epoch per code period once the loop runs (the first periods of pull-in included); Gnss_Synchro records are emitted for
+        # the same periods from tracking on: match them on the PRN start sample stamp
+        stamp = d[:, 5].astype(np.uint64)
+        assert np.all(np.diff(stamp.astype(np.int64)) > 0)
+        idx = np.searchsorted(stamp, g["tracking_sample_counter"])
+        ok = (idx < n) & (stamp[np.minimum(idx, n - 1)] == g["tracking_sample_counter"])
+        assert np.count_nonzero(ok) > 0.95 * len(g), (k, np.count_nonzero(ok), len(g))
+        e, gg = d[idx[ok]], g[ok]
+        # (the dump's prompt is that of the last code period, d_Prompt, :1397-1400; the record's is accumulated over the symbols of a bit,
+        # :1952-1958 — not comparable; Doppler and CN0 are the same variables in both)
+        assert np.allclose(e[:, 6], gg["carrier_doppler_hz"].astype(np.float32), rtol=1e-6, atol=1e-3)
+        assert np.allclose(e[:, 7], gg["cn0_db_hz"].astype(np.float32), rtol=1e-6, atol=1e-4)
+        assert np.all(d[-500:, 1] > d[-500:, 0]) and np.all(d[-500:, 1] > d[-500:, 2])  # locked: |P| above |E| and |L|
+        assert np.all(np.hypot(d[-500:, 3], d[-500:, 4]) > 0.0)
