@@ -4,6 +4,7 @@ The rules are the reference's unpack_2bit_samples (gnuradio_blocks/unpack_2bit_s
 2-bit fields per byte, least significant first, each mapped s -> 2 s + 1.
 """
 import numpy as np
+import pytest
 
 import _oracle as O
 
@@ -72,3 +73,23 @@ def test_labsat_known_answers():
         re = lvl[(w >> (15 - 4 * k)) & 1, (w >> (13 - 4 * k)) & 1]
         im = lvl[(w >> (14 - 4 * k)) & 1, (w >> (12 - 4 * k)) & 1]
         assert np.array_equal(four[:, k], (re + 1j * im).astype(np.complex64))
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("item_size", [1, 2, 4])
+@pytest.mark.parametrize("big_endian_items", [False, True])
+@pytest.mark.parametrize("big_endian_bytes", [False, True])
+@pytest.mark.parametrize("reverse_interleaving", [False, True])
+def test_two_bit_oracle_is_pinned_to_the_reference_block(item_size, big_endian_items, big_endian_bytes, reverse_interleaving):
+    """The oracle's 2-bit unpacker against the reference's OWN unpack_2bit_samples::work (gnuradio_blocks/unpack_2bit_samples.cc:121-208,
+    compiled unmodified into oracle/_ref against stub declarations of gr::sync_interpolator): every byte value, every option combination,
+    bit for bit — the GPU ingest kernel is tested bit-exact against this oracle in tests/test_ingest_gpu.py."""
+    rng = np.random.default_rng(item_size + 2 * big_endian_items + 4 * big_endian_bytes + 8 * reverse_interleaving)
+    raw = np.concatenate([np.arange(256, dtype=np.uint8), rng.integers(0, 256, 4096 - 256, dtype=np.uint8)])
+    want = np.zeros(4 * len(raw), np.int8)
+    f = O.ref().ref_unpack_2bit
+    f.restype = O.C.c_int
+    f.argtypes = [O.C.c_void_p, O.C.c_long, O.C.c_int, O.C.c_int, O.C.c_int, O.C.c_int, O.C.c_void_p]
+    assert f(raw.ctypes.data, len(raw), item_size, int(big_endian_items), int(big_endian_bytes), int(reverse_interleaving), want.ctypes.data) == 4 * len(raw)
+    got = O.unpack_2bit(raw, item_size=item_size, big_endian_items=big_endian_items, big_endian_bytes=big_endian_bytes, reverse_interleaving=reverse_interleaving)
+    assert np.array_equal(got, want)
