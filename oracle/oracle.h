@@ -12,9 +12,13 @@
  * and against golden vectors generated from it (tests/golden/).  The
  * acquisition side restates pcps_acquisition.cc, whose FFT (FFTW via GNU
  * Radio) and element-wise kernels (upstream VOLK) are NOT in the reference
- * tree and cannot be built here: its index outputs are "parity unpinned"
- * by the reference's own tests, cross-checked instead between
- * this fp32 FFT, a float64 FFT and numpy/scipy pocketfft.
+ * tree.  Round 1: "parity unpinned".  Since round 2 the reference's own
+ * pcps_acquisition.cc + acq_conf.cc are compiled UNMODIFIED into oracle/_ref
+ * against stand-in declarations (oracle/shim/acq, oracle/ref_acq.cc) with this
+ * file's FFT behind gr::fft: the restatement's grids equal the reference
+ * block's bit for bit and the frozen vectors are reproduced by the reference
+ * block (tests/test_acq_refblock_cpu.py).  FFTW's own rounding stays
+ * unpinned: index assertions must hold with the fp32 and the float64 FFT.
  */
 #ifndef GNSS_ORACLE_H
 #define GNSS_ORACLE_H

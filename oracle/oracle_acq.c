@@ -6,7 +6,9 @@
  *   volk_32fc_magnitude_squared_32f -> re*re + im*im
  *   volk_32f_x2_add_32f             -> a + b
  * compiled with -ffp-contract=off (exactly rounded; VOLK's SIMD protokernels give the same bits except where a
- * build fuses multiply-add).  "parity unpinned" against the reference itself: see oracle.h / DESIGN.md. */
+ * build fuses multiply-add).  Pinned since round 2 against the reference's own pcps_acquisition.cc compiled unmodified into oracle/_ref
+ * (oracle/ref_acq.cc; only the DFT library behind gr::fft is a stand-in): tests/test_acq_refblock_cpu.py — frozen vectors reproduced by
+ * the reference block, search grids equal bit for bit.  See oracle.h / DESIGN.md section 2. */
 #include "oracle.h"
 #include <math.h>
 #include <stdlib.h>

@@ -1,8 +1,9 @@
 // TEST INFRASTRUCTURE — CPU restatement of the raw-sample conversions in front of the hot paths.
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may use anything under oracle/.
 //
-// Parity unpinned against a reference binary: unpack_2bit_samples is a GNU Radio block (gr::sync_interpolator) and cannot be
-// compiled here.  The restatement keeps the reference's formulation — a bit-field view of each byte, laid out by THIS
+// Pinned (2-bit unpacker): the reference's unpack_2bit_samples.cc compiles unmodified into oracle/_ref against three stub declarations
+// (oracle/shim/gr_block) and tests/test_ingest_cpu.py compares its work() with this file bit for bit over every option combination.
+// The LabSat decoder stays on hand-worked known answers.  The restatement keeps the reference's formulation — a bit-field view of each byte, laid out by THIS
 // compiler exactly as it lays out the reference's byte_2bit_struct — while the CUDA kernel uses shifts and masks, so the two
 // sides of the parity test are independent formulations.  Known answers in tests/test_ingest_cpu.py.
 #include "oracle.h"

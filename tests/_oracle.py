@@ -358,3 +358,87 @@ def items_to_complex(raw, kind):
     f.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
     f(raw.ctypes.data, n, kind, out.ctypes.data)
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------------- the reference's own acquisition block
+class RefAcqStatus(C.Structure):
+    _fields_ = [("state", C.c_int32), ("active", C.c_int32), ("positive_acq", C.c_int32), ("n_events", C.c_int32), ("events", C.c_int32 * 8),
+                ("fsm_events", C.c_int32 * 8), ("n_fsm_events", C.c_int32),
+                ("fft_size", C.c_uint32), ("consumed_samples", C.c_uint32), ("num_doppler_bins", C.c_uint32), ("dwells_counter", C.c_uint32), ("samples_per_chip", C.c_uint32),
+                ("threshold", C.c_float), ("mag", C.c_float), ("input_power", C.c_float), ("test_statistics", C.c_float), ("samples_per_code", C.c_float),
+                ("samples_per_ms", C.c_float), ("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double),
+                ("acq_samplestamp_samples", C.c_uint64), ("sample_counter", C.c_uint64), ("consumed_total", C.c_int64),
+                ("doppler_step", C.c_int32), ("doppler_max", C.c_int32), ("use_cfar", C.c_int32), ("bit_transition", C.c_int32), ("it_size", C.c_int32)]
+
+
+class RefAcq:
+    """pcps_acquisition of the reference (oracle/ref_acq.cc: the reference's own pcps_acquisition.cc + acq_conf.cc compiled unmodified into
+    oracle/_ref against the stand-ins of oracle/shim/acq), driven like Channel and the adapters drive it."""
+
+    def __init__(self, conf_text, role, ms_per_code, chip_rate, opt_freq, prn, system, signal, fft_f64=False):
+        r = ref()
+        r.ref_acq_new.restype = C.c_void_p
+        r.ref_acq_new.argtypes = [C.c_char_p, C.c_char_p, C.c_uint, C.c_double, C.c_double, C.c_uint, C.c_char_p, C.c_char_p]
+        r.ref_acq_free.argtypes = [C.c_void_p]
+        r.ref_acq_init.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_float]
+        r.ref_acq_set_threshold.argtypes = [C.c_void_p, C.c_float]
+        r.ref_acq_set_doppler_center.argtypes = [C.c_void_p, C.c_int]
+        r.ref_acq_set_local_code.argtypes = [C.c_void_p, C.c_void_p]
+        r.ref_acq_arm.argtypes = [C.c_void_p]
+        r.ref_acq_work.restype = C.c_long
+        r.ref_acq_work.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        r.ref_acq_get_status.argtypes = [C.c_void_p, C.POINTER(RefAcqStatus)]
+        r.ref_acq_read_grid.restype = C.c_int
+        r.ref_acq_read_grid.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        r.ref_acq_fft_precision.argtypes = [C.c_int]
+        self._r = r
+        r.ref_acq_fft_precision(int(fft_f64))
+        self._h = r.ref_acq_new(conf_text.encode(), role.encode(), ms_per_code, chip_rate, opt_freq, prn, system.encode(), signal.encode())
+
+    def close(self):
+        if self._h:
+            self._r.ref_acq_free(self._h)
+            self._h = None
+
+    def init(self, doppler_max, doppler_step, threshold=0.0):
+        self._r.ref_acq_init(self._h, int(doppler_max), int(doppler_step), float(threshold))
+
+    def set_threshold(self, t):
+        self._r.ref_acq_set_threshold(self._h, float(t))
+
+    def set_local_code(self, code):
+        """code: complex64, at least vector_length samples (what the adapter's code_ buffer holds)"""
+        self._code = np.ascontiguousarray(code, dtype=np.complex64)
+        self._r.ref_acq_set_local_code(self._h, self._code.ctypes.data)
+
+    def arm(self):
+        self._r.ref_acq_arm(self._h)
+
+    def status(self):
+        s = RefAcqStatus()
+        self._r.ref_acq_get_status(self._h, C.byref(s))
+        return s
+
+    def work(self, items, scalars_per_item):
+        """general_work over a stream of items until the block stops (positive / negative acquisition) or the stream ends; returns items consumed"""
+        items = np.ascontiguousarray(items)
+        n_items, isz = len(items) // scalars_per_item, items.itemsize * scalars_per_item
+        pos, idle = 0, 0
+        for _ in range(100000):
+            st = self.status()
+            if st.state == 0 and not st.active:
+                break
+            # (the block switches from buffering to searching on the call AFTER the one that filled its buffer, :985-989, so a call with
+            # no new items is part of the sequence; two calls in a row without any effect end the loop)
+            c = self._r.ref_acq_work(self._h, items.ctypes.data + pos * isz, n_items - pos)
+            pos += c
+            st2 = self.status()
+            idle = idle + 1 if (c == 0 and st2.state == st.state and st2.active == st.active) else 0
+            if idle >= 2:
+                break
+        return pos
+
+    def grid(self, bins, neff):
+        g = np.zeros((bins, neff), dtype=np.float32)
+        n = self._r.ref_acq_read_grid(self._h, g.ctypes.data, bins, neff)
+        return g[:n]

@@ -40,6 +40,33 @@ def _oracle(fs, consumed, fft_size, spc, spchip, local, sigs, bit_transition=Fal
     return conf, O.acq_statistic(conf, grid, len(sigs))
 
 
+def _ref_block(conf_text, role, ms_per_code, chip_rate, opt, prn, system, signal, local, x, dmax=5000, dstep=250):
+    """the same .conf, replica and stream through the reference's OWN pcps_acquisition (oracle/ref_acq.cc): consumed items and status"""
+    if not O.ref_available():
+        return None
+    b = O.RefAcq(conf_text.replace("_B200", ""), role, ms_per_code, chip_rate, opt, prn, system, signal)
+    b.init(dmax, dstep, 0.0)
+    code = np.zeros(b.status().fft_size, np.complex64)
+    code[:len(local)] = local
+    b.set_local_code(code)
+    b.arm()
+    consumed = b.work(np.ascontiguousarray(x, np.complex64), 1)
+    st = b.status()
+    b.close()
+    return consumed, st
+
+
+def _check_vs_ref_block(s, consumed, ref):
+    """the product's block against the reference's block: same items consumed (same number of dwells), same event, same Gnss_Synchro"""
+    if ref is None:
+        return
+    rc, rs = ref
+    assert consumed == rc, (consumed, rc)
+    assert list(rs.fsm_events[:rs.n_fsm_events]) == [1] and s.last_event == 1
+    assert (s.acq_delay_samples, s.acq_doppler_hz, s.acq_samplestamp_samples) == (rs.acq_delay_samples, rs.acq_doppler_hz, rs.acq_samplestamp_samples)
+    assert abs(s.threshold - rs.threshold) <= 1e-5 * rs.threshold and abs(s.test_statistics - rs.test_statistics) <= 1e-3 * rs.test_statistics
+
+
 def _check(s, ro, consumed):
     assert s.last_event == 1 and s.active == 0 and s.state == 0, (s.last_event, s.active, s.state, s.test_statistics, s.threshold)
     assert (s.indext, s.doppler_index) == (ro.indext, ro.doppler_index)
@@ -54,7 +81,8 @@ def test_galileo_e1_adapter_from_conf(pilot, cboc):
     extra = "Acquisition_1B.coherent_integration_time_ms=4\nAcquisition_1B.pfa=0.001\n"
     extra += "Acquisition_1B.acquire_pilot=true\n" if pilot else ""
     extra += "Acquisition0.cboc=true\n" if cboc else ""   # read as "Acquisition<channel>.cboc" by the reference (:151-152)
-    a = H.AcquisitionBlock(_conf(fs, "Acquisition_1B", "Galileo_E1_PCPS_Ambiguous_Acquisition_B200", extra), "Acquisition_1B", prn, system="E", signal="1B")
+    conf_text = _conf(fs, "Acquisition_1B", "Galileo_E1_PCPS_Ambiguous_Acquisition_B200", extra)
+    a = H.AcquisitionBlock(conf_text, "Acquisition_1B", prn, system="E", signal="1B")
     a.arm()
     local = a.local_code()
     sig = "1C" if pilot else "1B"
@@ -70,6 +98,7 @@ def test_galileo_e1_adapter_from_conf(pilot, cboc):
     conf, ro = _oracle(fs, 16000, 16000, float(np.float32(np.float32(fs) * np.float32(0.001)) * 4), 4, local, [x[:16000]])
     _check(s, ro, consumed)
     assert consumed == 16000 and s.acq_samplestamp_samples == 16000
+    _check_vs_ref_block(s, consumed, _ref_block(conf_text, "Acquisition_1B", 4, 1.023e6, 4e6, prn, "E", "1B", local, x))
     assert abs(s.threshold - O.acq_threshold(conf, 0.001)) <= 1e-5 * s.threshold
     assert abs(s.acq_delay_samples - delay / 2.046e6 * fs) <= 2 and abs(s.acq_doppler_hz - doppler) <= 125
     a.close()
@@ -79,7 +108,8 @@ def test_gps_l5i_adapter_from_conf_with_dwells():
     from gnss_sim_receiver_b200 import _hostapi as H
     fs, prn, doppler, delay = 20e6, 7, -1820.0, 6111.7
     extra = "Acquisition_L5.max_dwells=3\nAcquisition_L5.pfa=0.0001\n"
-    a = H.AcquisitionBlock(_conf(fs, "Acquisition_L5", "GPS_L5i_PCPS_Acquisition_B200", extra), "Acquisition_L5", prn, system="G", signal="L5")
+    conf_text = _conf(fs, "Acquisition_L5", "GPS_L5i_PCPS_Acquisition_B200", extra)
+    a = H.AcquisitionBlock(conf_text, "Acquisition_L5", prn, system="G", signal="L5")
     a.arm()
     local = a.local_code()
     assert len(local) == 20000
@@ -99,6 +129,7 @@ def test_gps_l5i_adapter_from_conf_with_dwells():
     conf, ro = _oracle(fs, 20000, 20000, float(np.float32(np.float32(fs) * np.float32(0.001))), 2, local, [x[d * 20000:(d + 1) * 20000] for d in range(n_dwells)], max_dwells=3)
     _check(s, ro, consumed)
     assert abs(((s.acq_delay_samples - delay / 10.23e6 * fs + 10000) % 20000) - 10000) <= 2 and abs(s.acq_doppler_hz - doppler) <= 250  # either bin next to the truth
+    _check_vs_ref_block(s, consumed, _ref_block(conf_text, "Acquisition_L5", 1, 10.23e6, 10e6, prn, "G", "L5", local, x))  # the same number of dwells
     a.close()
 
 
@@ -106,7 +137,8 @@ def test_gps_l5i_adapter_from_conf_with_dwells():
 def test_galileo_e5a_adapter_from_conf(opts, sig):
     from gnss_sim_receiver_b200 import _hostapi as H
     fs, prn, doppler, delay = 20e6, 19, 2630.0, 901.2
-    a = H.AcquisitionBlock(_conf(fs, "Acquisition_5X", "Galileo_E5a_Pcps_Acquisition_B200", "Acquisition_5X.pfa=0.001\n" + opts), "Acquisition_5X", prn, system="E", signal="5X")
+    conf_text = _conf(fs, "Acquisition_5X", "Galileo_E5a_Pcps_Acquisition_B200", "Acquisition_5X.pfa=0.001\n" + opts)
+    a = H.AcquisitionBlock(conf_text, "Acquisition_5X", prn, system="E", signal="5X")
     a.arm()
     local = a.local_code()
     assert len(local) == 20000
@@ -120,4 +152,5 @@ def test_galileo_e5a_adapter_from_conf(opts, sig):
     conf, ro = _oracle(fs, 20000, 20000, float(np.float32(np.float32(fs) * np.float32(0.001))), 2, local, [x[:20000]])
     _check(s, ro, consumed)
     assert abs(((s.acq_delay_samples - delay / 10.23e6 * fs + 10000) % 20000) - 10000) <= 2 and abs(s.acq_doppler_hz - doppler) <= 250  # either bin next to the truth
+    _check_vs_ref_block(s, consumed, _ref_block(conf_text, "Acquisition_5X", 1, 10.23e6, 10e6, prn, "E", "5X", local, x))
     a.close()

@@ -1,8 +1,9 @@
 """Pins the acquisition oracle (oracle/oracle_acq.c) on the frozen scenarios of tests/_signals.py: it must keep reproducing
 tests/golden/acq_vectors.json — produced by tests/golden/make_acq_golden.py — with BOTH FFT precisions agreeing on every index.
 
-What this pin is and is not: the reference's pcps_acquisition needs GNU Radio / FFTW / VOLK / Boost, none of which exist here, so no
-vector comes from the reference binary ("parity unpinned").  The vectors freeze the restatement (which follows
+What this pin is and is not: the reference's pcps_acquisition needs GNU Radio / FFTW / VOLK / Boost, none of which exist here, so the
+vectors were frozen from the restatement; tests/test_acq_refblock_cpu.py then has the reference's OWN pcps_acquisition.cc (compiled
+unmodified into oracle/_ref, with a stand-in DFT behind gr::fft) reproduce them.  The vectors freeze the restatement (which follows
 pcps_acquisition.cc:175-208,496-697 and uses the reference's own sincos / index_max kernels where they compile) against regressions,
 require the fp32-FFT and float64-FFT evaluations to name the same (code phase, Doppler bin) — so no frozen index hangs on FFT rounding —
 and give the GPU tests an oracle-free target (tests/test_acq_golden_gpu.py).
