@@ -6,6 +6,9 @@
 // Acq_Conf::SetFromConfiguration from "key=value" text, set_gnss_synchro / set_channel_fsm / set_doppler_max / set_doppler_step /
 // set_threshold, init(), set_local_code(), set_state(1), set_active(true), general_work() over the input stream.
 #include <algorithm>
+#include <any>
+#include <deque>
+#include <functional>
 #include <complex>
 #include <cstdint>
 #include <cstring>

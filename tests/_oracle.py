@@ -442,3 +442,44 @@ class RefAcq:
         g = np.zeros((bins, neff), dtype=np.float32)
         n = self._r.ref_acq_read_grid(self._h, g.ctypes.data, bins, neff)
         return g[:n]
+
+
+# ---------------------------------------------------------------------------------------------------------------- the reference's own tracking block
+class RefTrkBlock:
+    """dll_pll_veml_tracking of the reference (oracle/ref_trkblk.cc: the reference's own dll_pll_veml_tracking.cc + dll_pll_conf.cc compiled
+    unmodified into oracle/_ref, the door playing the GNU Radio scheduler).  Same feed() / state() as RefLoop; the block generates its own
+    code tables from (system, signal, PRN) in start_tracking."""
+    SIGNALS = {"1C": ("G", "1C", 1.023e6, 1023.0), "1B": ("E", "1B", 1.023e6, 1023.0), "L5": ("G", "L5", 10.23e6, 10230.0), "5X": ("E", "5X", 10.23e6, 10230.0)}
+
+    def __init__(self, conf_text, role, signal, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp=0):
+        r = ref()
+        r.ref_trkblk_new.restype = C.c_void_p
+        r.ref_trkblk_new.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_double, C.c_double, C.c_uint, C.c_double, C.c_double, C.c_uint64]
+        r.ref_trkblk_feed.restype = C.c_int
+        r.ref_trkblk_feed.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int]
+        r.ref_trkblk_state.argtypes = [C.c_void_p, C.c_void_p]
+        r.ref_trkblk_free.argtypes = [C.c_void_p]
+        self._r = r
+        system, sig, chip_rate, code_len = self.SIGNALS[signal]
+        # vector_length = round(fs / (chip_rate / code_length)): 1 ms for GPS L1 / L5 / E5a; the E1 adapter uses the 4 ms code (4092 chips)
+        if signal == "1B":
+            code_len = 4092.0
+        self._h = r.ref_trkblk_new(conf_text.encode(), role.encode(), system.encode(), sig.encode(), chip_rate, code_len, int(prn), float(acq_delay_samples),
+                                   float(acq_doppler_hz), int(acq_samplestamp))
+        self._rec = np.zeros(8192, dtype=REF_LOOP_REC)
+
+    def feed(self, sig):
+        sig = np.ascontiguousarray(sig, dtype=np.complex64)
+        n = self._r.ref_trkblk_feed(self._h, sig.ctypes.data, len(sig), self._rec.ctypes.data, len(self._rec))
+        return self._rec[:n].copy()
+
+    def state(self):
+        out = np.zeros(6, dtype=np.float64)
+        self._r.ref_trkblk_state(self._h, out.ctypes.data)
+        return dict(state=int(out[0]), cn0_db_hz=float(out[1]), carrier_doppler_hz=float(out[2]), code_freq_chips=float(out[3]), carrier_lock_test=float(out[4]),
+                    last_event=int(out[5]))
+
+    def close(self):
+        if self._h:
+            self._r.ref_trkblk_free(self._h)
+            self._h = None

@@ -3,7 +3,9 @@
 Product: B200TrackingBank (host C++ loop closure, gnss_sim_receiver_b200/host/) over the GPU multicorrelator, selected through
 the `.conf` implementation string.  Oracle: one loop per channel made of the reference's OWN objects (oracle/ref_loop.cc in
 oracle/_ref: Cpu_Multicorrelator_Real_Codes over the volk_gnsssdr protokernels, Tracking_loop_filter, Tracking_FLL_PLL_filter,
-discriminators, lock detectors, Exponential_Smoother), glue restated from dll_pll_veml_tracking.cc.
+discriminators, lock detectors, Exponential_Smoother), glue restated from dll_pll_veml_tracking.cc — and that restatement is itself pinned:
+tests/test_trk_refblock_cpu.py has the reference's OWN dll_pll_veml_tracking.cc (compiled unmodified into oracle/_ref) emit bit-identical
+records on the same streams, for every signal and mode used here.
 
 Gates: every channel the oracle keeps locked stays locked in the product, same PRN set, same number of
 telemetry symbols with identical signs, CN0 (M2M4) within 0.1 dB, Doppler within 0.5 Hz RMS.
