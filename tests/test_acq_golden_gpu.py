@@ -36,3 +36,39 @@ def test_engine_reproduces_the_frozen_vectors(key):
         assert r.acq_delay_samples == want["acq_delay_samples"]
         assert abs(r.test_statistics - want["test_statistics"]) <= 1e-3 * want["test_statistics"], (key, p)
         assert abs(r.peak - want["peak"]) <= 1e-3 * want["peak"]
+
+
+@pytest.mark.parametrize("name,seed", [("c1_gps_4msps", 3), ("c2_e1c_bit_transition_cshort", 1), ("c3_gps_25msps", 2), ("c4_l5i_4_dwells", 2)])
+def test_engine_indices_equal_the_reference_blocks(name, seed):
+    """north_star's gate, literally: acquisition code-phase and Doppler-bin results against the reference's pcps_acquisition — here the
+    reference's OWN pcps_acquisition.cc, compiled unmodified into oracle/_ref (oracle/ref_acq.cc; the DFT library behind gr::fft is the one
+    stand-in) and run live on the same block as the engine — for EVERY PRN searched, satellites in the air and noise-only alike."""
+    import numpy as np
+
+    import _oracle as O
+    import test_acq_refblock_cpu as R
+    if not O.ref_available():
+        pytest.skip("oracle/_ref not built")
+    from gnss_sim_receiver_b200.acquisition import AcquisitionEngine
+    c = S.acq_case(name, seed)
+    eng = AcquisitionEngine(fs_in=c["fs"], fft_size=c["fft_size"], consumed_samples=c["consumed"], samples_per_code=c["spc"], samples_per_chip=c["spchip"],
+                            bit_transition=c["bit_transition"], use_cfar=c["use_cfar"], max_dwells=c["max_dwells"], max_prns=len(c["prns"]), iq_dtype=c["iq_dtype"])
+    eng.set_doppler_grid(c["dmax"], c["dstep"])
+    for i, p in enumerate(c["prns"]):
+        eng.set_local_code(i, c["locals_"][p])
+    res = None
+    for d, items in enumerate(c["items"]):
+        res = eng.run(items, dwell_index=d)
+    eng.close()
+    stream = np.concatenate(c["items"])
+    k = 1 if S.ACQ_CASES[name][8] == "gr_complex" else 2
+    for i, p in enumerate(c["prns"]):
+        b = R._block(name, c, p, False, 0.001)
+        b.set_threshold(3e38)  # take every dwell
+        b.arm()
+        b.work(stream, k)
+        st = b.status()
+        b.close()
+        r = res[i]
+        assert (r.acq_delay_samples, float(r.doppler_hz)) == (st.acq_delay_samples, st.acq_doppler_hz), (name, p, p in c["present"])
+        assert abs(r.test_statistics - st.test_statistics) <= 1e-3 * st.test_statistics, (name, p)
