@@ -18,6 +18,11 @@ struct gb200_acq
     int threads{1024};
     size_t smem{0};
     int n_bins{0}, neff{0}, out_offset{0}, n_parts{1};
+    // transform length: cfg.fft_size, or — for sizes the mixed-radix plan cannot factor (a prime factor above 61) — a smooth length
+    // >= 2 * fft_size - 1 on which the same circular correlation is computed exactly (zero-padded input, wrapped replica, search over
+    // the first fft_size lags only): FFTW takes any size, this is how the engine does
+    int tlen{0};
+    bool padded{false};
     bool cluster_inv{false};  // split transforms: the blocks of a cell run as a thread-block cluster (acq_inv_kernel<3>) instead of staging in global memory
     int doppler_max{0}, doppler_step{0}, doppler_center{0};
     int keep_grid{0}, user_keep{0};
@@ -207,7 +212,7 @@ int plan_threads(const FftPlan& pl)
 
 int make_plan(gb200_acq* h, int max_smem)
 {
-    const int N = h->cfg.fft_size;
+    const int N = h->tlen;
     FftPlan& pl = h->plan;
     if (N < 8) return set_error(GB200_EINVAL, "fft_size %d: at least 8 points", N);
     pl.n = N;

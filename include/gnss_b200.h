@@ -313,7 +313,7 @@ typedef struct
 {
     int32_t device;
     int32_t iq_dtype;         /* GB200_IQ_*: acq_parameters.it_size / item_type (acq_conf.cc:24-31) */
-    int32_t fft_size;         /* d_fft_size           pcps_acquisition.cc:84-93  (prime factors up to 61; larger ones are refused with GB200_EINVAL) */
+    int32_t fft_size;         /* d_fft_size           pcps_acquisition.cc:84-93  (any size, like FFTW behind gr::fft: sizes with a prime factor above 61 run on a padded transform that gives the same circular correlation) */
     int32_t consumed_samples; /* d_consumed_samples   pcps_acquisition.cc:84-91  (input zero-padded to fft_size, :612-619) */
     int32_t bit_transition;   /* acq_parameters.bit_transition_flag */
     int32_t use_cfar;         /* d_use_CFAR_algorithm_flag (pfa > 0), pcps_acquisition.cc:81 */

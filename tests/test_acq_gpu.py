@@ -182,7 +182,11 @@ def test_split_transform_sizes(fs, periods):
 def test_errors_are_loud():
     from gnss_sim_receiver_b200._capi import GB200Error
     with pytest.raises(GB200Error):
-        _engine(fs_in=4e6, fft_size=2222)  # 2 * 11 * 101: prime factors outside 2,3,5,7
+        _engine(fs_in=4e6, fft_size=4000, consumed_samples=4001)  # more samples than the transform holds
+    with pytest.raises(GB200Error):
+        _engine(fs_in=4e6, fft_size=4001, bit_transition=True)     # bit_transition needs an even block
+    e = _engine(fs_in=4e6, fft_size=2222)  # 2 * 11 * 101: not factorable by the plan — served by a padded transform (tests/test_acq_anysize_gpu.py)
+    e.close()
     eng = _engine(fs_in=4e6, fft_size=4000, max_prns=2)
     with pytest.raises(GB200Error):
         eng.run(np.zeros(4000, np.complex64))  # no doppler grid
