@@ -47,7 +47,8 @@ class LoopConfig(C.Structure):
                 ("enable_fll_pull_in", C.c_int32), ("enable_fll_steady_state", C.c_int32), ("carrier_aiding", C.c_int32),
                 ("cn0_samples", C.c_int32), ("cn0_min", C.c_int32), ("max_code_lock_fail", C.c_int32), ("max_carrier_lock_fail", C.c_int32),
                 ("cn0_smoother_samples", C.c_int32), ("carrier_lock_test_smoother_samples", C.c_int32),
-                ("pull_in_time_s", C.c_uint32), ("bit_synchronization_time_limit_s", C.c_uint32), ("n_correlators", C.c_int32), ("reserved_", C.c_int32)]
+                ("pull_in_time_s", C.c_uint32), ("bit_synchronization_time_limit_s", C.c_uint32), ("n_correlators", C.c_int32), ("track_pilot", C.c_int32),
+                ("data_secondary_code_length", C.c_int32), ("data_secondary_code", C.c_char * 36)]
 
 
 class LoopChannelState(C.Structure):

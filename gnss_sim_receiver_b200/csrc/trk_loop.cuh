@@ -8,7 +8,8 @@
 // gb200_trk_enqueue does per command (csrc/trk_submit.inc: prepare_cmd) — so that a step of a closed loop over 10^4 channels is
 //   correlate kernel -> this kernel -> correlate kernel -> ...
 // with nothing but the new IQ block going to the device and the emitted Gnss_Synchro records coming back.
-// Scope: real-code channels whose data and tracked component coincide (track_pilot=false), high_dyn=false; the host block
+// Scope: real-code channels, high_dyn=false: data-component tracking, and pilot tracking (track_pilot) with a second one-tap correlator
+// on the data code when the pilot's secondary code does not depend on the satellite (E1C / E1B, L5Q / L5I); the host block
 // (host/b200_dll_pll_veml_tracking.cc, bit-exact scalar pieces) remains the path for the rest and the parity reference of this one.
 // The scalar pieces restate tracking_discriminators.cc:68-149, tracking_loop_filter.cc:58-200, tracking_FLL_PLL_filter.cc:23-99,
 // lock_detectors.cc:90-148, exponential_smoother.cc with the reference's operand types (float / double), like host/b200_tracking_libs.cc.
@@ -43,6 +44,8 @@ struct LoopConf
 {
     gb200_loop_config c;
     unsigned sec_zero[LOOP_MAX_SEC / 32];  // bit i set: chip i of the secondary code / sync pattern is '0'
+    unsigned data_sec_zero[2];             // the same for the data component's secondary code (track_pilot)
+    int n_channels;                        // data command / data code slot of channel i: n_channels + i (track_pilot)
     float shifts_wide[GB200_MAX_TAPS], shifts_narrow[GB200_MAX_TAPS];
     int n_taps, idx_ve, idx_e, idx_p, idx_l, idx_vl;
     int enable_extended;
@@ -356,8 +359,8 @@ __device__ void loop_update_tracking_vars(const LoopConf& k, LoopState& s)
     s.rem_code_phase_chips = s.code_freq_chips * s.rem_code_phase_samples / k.c.fs_in;
 }
 
-// :1263-1373 (track_pilot = false)
-__device__ void loop_save_correlation_results(const LoopConf& k, LoopState& s, const float2* taps)
+// :1263-1373.  dprompt: the data correlator's prompt (track_pilot), else unused
+__device__ void loop_save_correlation_results(const LoopConf& k, LoopState& s, const float2* taps, float2 dprompt)
 {
     const bool flip = k.c.secondary && !((k.sec_zero[s.current_symbol >> 5] >> (s.current_symbol & 31)) & 1u);
     const float sign = flip ? -1.0F : 1.0F;
@@ -375,16 +378,28 @@ __device__ void loop_save_correlation_results(const LoopConf& k, LoopState& s, c
     s.L.x += sign * taps[k.idx_l].x;
     s.L.y += sign * taps[k.idx_l].y;
     if (k.c.secondary) s.current_symbol = (s.current_symbol + 1) % k.c.secondary_code_length;
-    const float2 dp = taps[k.idx_p];
+    // the symbol comes from the data component's own correlator when the pilot is tracked (:1305-1362)
+    const float2 dp = k.c.track_pilot ? dprompt : taps[k.idx_p];
     if (k.c.symbols_per_bit > 1)
         {
-            s.P_data.x += dp.x;  // (a data secondary code exists only with track_pilot)
-            s.P_data.y += dp.y;
-            s.current_data_symbol = (s.current_data_symbol + 1) % k.c.symbols_per_bit;
+            if (k.c.data_secondary_code_length > 0)
+                {
+                    const bool zero = (k.data_sec_zero[s.current_data_symbol >> 5] >> (s.current_data_symbol & 31)) & 1u;
+                    const float ds = zero ? 1.0F : -1.0F;
+                    s.P_data.x += ds * dp.x;
+                    s.P_data.y += ds * dp.y;
+                    s.current_data_symbol = (s.current_data_symbol + 1) % k.c.data_secondary_code_length;
+                }
+            else
+                {
+                    s.P_data.x += dp.x;
+                    s.P_data.y += dp.y;
+                    s.current_data_symbol = (s.current_data_symbol + 1) % k.c.symbols_per_bit;
+                }
         }
     else
         s.P_data = dp;
-    s.cloop = 1;
+    s.cloop = k.c.track_pilot ? 0 : 1;  // tracking the pilot: no Costas loop (:1364-1372)
 }
 
 __device__ void loop_clear_tracking_vars(LoopState& s)
@@ -452,7 +467,7 @@ __device__ void loop_emit(const LoopConf& k, const LoopState& s, int ch, bool va
 }
 
 // second half of general_work (:1791-2094) for a channel whose command was correlated
-__device__ void loop_finish(const LoopConf& k, LoopState& s, int ch, const float2* taps, gb200_loop_record* records, unsigned max_records, LoopCounters* cnt)
+__device__ void loop_finish(const LoopConf& k, LoopState& s, int ch, const float2* taps, float2 dprompt, gb200_loop_record* records, unsigned max_records, LoopCounters* cnt)
 {
     bool emit = false, loss = false, reset_acc = false;
     switch (s.state)
@@ -508,7 +523,7 @@ __device__ void loop_finish(const LoopConf& k, LoopState& s, int ch, const float
             }
         case 3:
             {
-                loop_save_correlation_results(k, s, taps);
+                loop_save_correlation_results(k, s, taps, dprompt);
                 loop_update_tracking_vars(k, s);
                 if (s.current_data_symbol == 0) emit = true;
                 s.extend_count++;
@@ -521,7 +536,7 @@ __device__ void loop_finish(const LoopConf& k, LoopState& s, int ch, const float
             }
         case 4:
             {
-                loop_save_correlation_results(k, s, taps);
+                loop_save_correlation_results(k, s, taps, dprompt);
                 if (!loop_cn0_and_lock(k, s, k.c.code_period_s * (double)k.c.extend_correlation_symbols))
                     {
                         loop_clear_tracking_vars(s);
@@ -617,7 +632,8 @@ __global__ void __launch_bounds__(128) trk_loop_kernel(const LoopConf* __restric
                     float2 taps[GB200_MAX_TAPS];
                     const float2* o = reinterpret_cast<const float2*>(outs) + (size_t)ch * TRK_OUT_STRIDE;
                     for (int t = 0; t < k.n_taps; t++) taps[t] = o[t];
-                    loop_finish(k, s, ch, taps, records, max_records, cnt);
+                    const float2 dprompt = k.c.track_pilot ? reinterpret_cast<const float2*>(outs)[(size_t)(k.n_channels + ch) * TRK_OUT_STRIDE] : make_float2(0.0F, 0.0F);
+                    loop_finish(k, s, ch, taps, dprompt, records, max_records, cnt);
                     s.nitems_read += (unsigned long long)s.current_prn_length_samples;  // consume_each(d_current_prn_length_samples), :2092
                     s.planned = 0;
                 }
@@ -663,12 +679,27 @@ __global__ void __launch_bounds__(128) trk_loop_kernel(const LoopConf* __restric
                             break;
                         }
                     cmds[ch] = d;
+                    if (k.c.track_pilot)
+                        {
+                            // the data correlator: same window, carrier and code NCO, the data code, one tap at the prompt shift
+                            // (do_correlation_step :1051-1062; d_prompt_data_shift :498,510)
+                            const float ps = d.shifts[k.idx_p];
+                            d.code = reinterpret_cast<const void*>(k.code_base + (unsigned long long)(k.n_channels + ch) * k.max_code_len * 2ull * sizeof(float));
+                            d.ntaps = 1;
+                            for (int t = 0; t < GB200_MAX_TAPS; t++) d.shifts[t] = ps;
+                            d.shift_min = d.shift_max = ps;
+                            cmds[k.n_channels + ch] = d;
+                        }
                     s.planned = 1;
                     planned_now = true;
                     ready_again = head - s.nitems_read >= need + (unsigned long long)k.c.vector_length;
                     break;
                 }
-            if (!s.planned) cmds[ch].n = 0;
+            if (!s.planned)
+                {
+                    cmds[ch].n = 0;
+                    if (k.c.track_pilot) cmds[k.n_channels + ch].n = 0;
+                }
         }
     // counters: one atomic per warp (10^4 single atomics on one address cost more than the loop closure itself)
     const unsigned m_planned = __ballot_sync(0xffffffffu, planned_now), m_again = __ballot_sync(0xffffffffu, ready_again), m_bad = __ballot_sync(0xffffffffu, bad);

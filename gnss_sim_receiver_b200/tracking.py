@@ -178,10 +178,23 @@ _SIGNALS = {
 }
 
 
+# pilot tracking (track_pilot = true, dll_pll_veml_tracking.cc:227-237, :278-284): the tracked component's secondary code, and the data component's
+_PILOT = {
+    "1B": dict(secondary=1, secondary_code="0011100000001010110110010", data_secondary_code="", interchange_iq=0),       # GALILEO_E1_C_SECONDARY_CODE
+    "L5": dict(secondary=1, secondary_code="00000100110101001110", data_secondary_code="0000110101", interchange_iq=0),  # GPS_L5Q_NH_CODE_STR / GPS_L5I_NH_CODE_STR
+}
+
+
 def loop_config(signal, fs_in, **overrides):
     """gb200_loop_config of one signal with the reference's Dll_Pll_Conf defaults (src/algorithms/tracking/libs/dll_pll_conf.cc:36-125,
     gnss_sdr_flags.cc:48-57); keyword arguments override fields by name."""
     sig = dict(_SIGNALS[signal])
+    data_code = ""
+    if overrides.get("track_pilot"):
+        if signal not in _PILOT:
+            raise ValueError(f"track_pilot is served on the device for {sorted(_PILOT)}; {signal!r} goes through the host block")
+        sig.update(_PILOT[signal])
+        data_code = sig.pop("data_secondary_code")
     code = sig.pop("secondary_code")
     c = LoopConfig()
     c.fs_in = float(fs_in)
@@ -189,13 +202,15 @@ def loop_config(signal, fs_in, **overrides):
         setattr(c, k, v)
     c.secondary_code = code.encode()
     c.secondary_code_length = len(code)
+    c.data_secondary_code = data_code.encode()
+    c.data_secondary_code_length = len(data_code)
     c.vector_length = int(round(fs_in / (c.code_chip_rate / c.code_length_chips)))
     d = dict(pll_bw_hz=35.0, dll_bw_hz=2.0, fll_bw_hz=35.0, pll_bw_narrow_hz=5.0, dll_bw_narrow_hz=0.75, early_late_space_chips=0.25 if signal != "1B" else 0.25,
              very_early_late_space_chips=0.5, early_late_space_narrow_chips=0.15, very_early_late_space_narrow_chips=0.5, slope=1.0, y_intercept=1.0,
              carrier_lock_th=0.7, cn0_smoother_alpha=0.002, carrier_lock_test_smoother_alpha=0.002, pll_filter_order=3, dll_filter_order=2,
              extend_correlation_symbols=1, enable_fll_pull_in=0, enable_fll_steady_state=0, carrier_aiding=1, cn0_samples=20, cn0_min=25,
              max_code_lock_fail=50, max_carrier_lock_fail=5000, cn0_smoother_samples=200, carrier_lock_test_smoother_samples=25, pull_in_time_s=10,
-             bit_synchronization_time_limit_s=20, n_correlators=0)
+             bit_synchronization_time_limit_s=20, n_correlators=0, track_pilot=0)
     d.update(overrides)
     for k, v in d.items():
         if not hasattr(c, k):

@@ -213,8 +213,13 @@ const char* gb200_trk_last_kernel(const gb200_trk* h);
  * (0 standby, 1 pull-in, 2 wide tracking + symbol synchronisation, 3 extended integration, 4 narrow tracking), with the channel
  * state resident in HBM: one gb200_loop_step = upload the new IQ block, [correlate kernel -> loop kernel] for every channel whose
  * next window is in the ring, download the Gnss_Synchro records emitted in this step.  No per-channel host work.
- * Served: real-code channels with track_pilot = false and high_dyn = false (GPS L1 C/A, GPS L5I, Galileo E1B, Galileo E5aI); the
- * host block (gnss_sim_receiver_b200/host/b200_dll_pll_veml_tracking.cc) serves the rest.
+ * Served: real-code channels with high_dyn = false — data-component tracking (GPS L1 C/A, GPS L5I, Galileo E1B, Galileo E5aI) and, with
+ * track_pilot = 1, pilot tracking whose secondary code is the same for every satellite (Galileo E1C with E1B as data component, GPS L5Q
+ * with L5I): the pilot's taps close the loop, a second one-tap correlator on the data code at the prompt shift supplies the symbols
+ * (d_correlator_data_cpu, :526-531,1051-1062; save_correlation_results :1305-1372).  The host block
+ * (gnss_sim_receiver_b200/host/b200_dll_pll_veml_tracking.cc) serves the rest (high_dyn, Galileo E5aQ's per-satellite secondary codes).
+ * With track_pilot the engine needs max_channels and max_cmds >= 2 * n_channels: channel i's tracking code is the engine's code slot
+ * i, its data code slot n_channels + i.
  * ====================================================================== */
 typedef struct gb200_loop gb200_loop;
 
@@ -249,7 +254,9 @@ typedef struct
      * the loop narrows): E is the first, P the middle, L the last; the others are correlated in the same launch and stay readable on
      * the device through gb200_loop_read_taps (multipath / signal-quality monitors). */
     int32_t n_correlators;
-    int32_t reserved_;
+    int32_t track_pilot;         /* Dll_Pll_Conf::track_pilot (see "Served" above) */
+    int32_t data_secondary_code_length; /* d_data_secondary_code_length: secondary code of the DATA component, removed from its prompt (track_pilot only) */
+    char data_secondary_code[36];       /* d_data_secondary_code_string: '0' / '1' */
 } gb200_loop_config;
 
 /* one emitted Gnss_Synchro (what general_work writes to its output, :2063-2090), or a loss of lock (flag_valid_symbol_output = 0) */

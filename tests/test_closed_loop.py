@@ -679,3 +679,120 @@ def test_tracking_dump_is_read_by_the_reference_reader(tmp_path):
         assert np.allclose(e[:, 7], gg["cn0_db_hz"].astype(np.float32), rtol=1e-6, atol=1e-4)
         assert np.all(d[-500:, 1] > d[-500:, 0]) and np.all(d[-500:, 1] > d[-500:, 2])  # locked: |P| above |E| and |L|
         assert np.all(np.hypot(d[-500:, 3], d[-500:, 4]) > 0.0)
+
+
+# ------------------------------------------------------------------------------------------------ device loop, pilot tracking
+def _conf_text(role, fs, **kw):
+    lines = [f"GNSS-SDR.internal_fs_sps={int(fs)}", f"{role}.item_type=gr_complex"]
+    for k, v in kw.items():
+        lines.append(f"{role}.{k}={'true' if v is True else 'false' if v is False else v}")
+    return "\n".join(lines) + "\n"
+
+
+def _device_vs_block_pilot(label, loop, blocks, chunks, nsat, truth_doppler, min_records):
+    got, ref = [[] for _ in range(nsat)], [[] for _ in range(nsat)]
+    for x in chunks:
+        r = loop.step(x)
+        for k in range(nsat):
+            got[k].append(r[r["channel"] == k])
+            ref[k].append(blocks[k].feed(x))
+    for k in range(nsat):
+        g, r = np.concatenate(got[k]), np.concatenate(ref[k])
+        gs, rs = loop.channel(k), blocks[k].state()
+        assert rs["state"] == 4 and gs["state"] == 4, (label, k, gs, rs)
+        m = min(len(g), len(r))
+        assert m > min_records and len(r) - len(g) <= 6, (label, k, len(g), len(r))
+        g, r = g[:m], r[:m]
+        d_cnt = np.abs(g["tracking_sample_counter"].astype(np.int64) - r["tracking_sample_counter"].astype(np.int64))
+        assert d_cnt.max() <= 1, (label, k, d_cnt.max())
+        assert np.array_equal(g["correlation_length_ms"], r["correlation_length_ms"]), (label, k)
+        # the symbols sit on the arm that carries the data component's energy (in phase with the pilot for E1, in quadrature for L5)
+        f = "prompt_i" if np.median(np.abs(r["prompt_i"])) >= np.median(np.abs(r["prompt_q"])) else "prompt_q"
+        assert np.array_equal(np.sign(g[f]), np.sign(r[f])), (label, k, f)
+        amp = np.median(np.abs(r[f]))
+        for ff in ("prompt_i", "prompt_q"):  # (auxiliary: both arms close in value; the gates are the signs above and CN0 / Doppler below)
+            assert np.max(np.abs(g[ff][m // 4:] - r[ff][m // 4:])) < 0.1 * amp, (label, k, ff)
+        half = m // 2
+        d_cn0 = np.max(np.abs(g["cn0_db_hz"][half:] - r["cn0_db_hz"][half:]))
+        d_dop = np.sqrt(np.mean((g["carrier_doppler_hz"][half:] - r["carrier_doppler_hz"][half:]) ** 2))
+        print(f"[device loop {label}] ch {k}: records {m}, symbols on {f}, CN0 diff {d_cn0:.4f} dB, Doppler diff {d_dop:.4f} Hz rms")
+        assert d_cn0 < 0.1 and d_dop < 0.5, (label, k, d_cn0, d_dop)
+        assert abs(np.mean(g["carrier_doppler_hz"][half:]) - truth_doppler[k]) < 2.0, (label, k)
+
+
+@pytest.mark.gpu
+@needs_ref
+def test_device_loop_galileo_e1_pilot_vs_the_reference_block():
+    """track_pilot=true on the device: E1-C tracked by the five-tap VEML correlator (25-chip secondary code synchronised and wiped), the
+    E1-B symbols from a second one-tap correlator in the same launch, no Costas loop — against the reference's OWN dll_pll_veml_tracking
+    block (oracle/ref_trkblk.cc) on the E1 open-service stream."""
+    from gnss_sim_receiver_b200.tracking import TrackingEngine, TrackingLoop, loop_config
+    nsat = 4
+    sc = e1_scenario(nsat, seed=37)
+    kw = dict(pll_bw_hz=15.0, dll_bw_hz=0.75, pll_bw_narrow_hz=5.0, dll_bw_narrow_hz=0.2, early_late_space_chips=0.25, very_early_late_space_chips=0.5,
+              early_late_space_narrow_chips=0.15, very_early_late_space_narrow_chips=0.5, extend_correlation_symbols=1, pull_in_time_s=1, cn0_samples=20, cn0_min=25,
+              carrier_lock_th=0.5)
+    eng = TrackingEngine(max_channels=2 * nsat, max_code_len=8184, ring_samples=4 * CHUNK, max_block=2 * 16000, max_cmds=2 * nsat)
+    cfg = loop_config("1B", FS, track_pilot=True, max_code_lock_fail=50, max_carrier_lock_fail=5000, **kw)
+    cfg.slope, cfg.y_intercept = _e1_slope_intercept(0.25)
+    for k in range(nsat):
+        eng.set_code(k, sc["pilot_code"][k])         # tracking code: slot i
+        eng.set_code(nsat + k, sc["data_code"][k])   # data code: slot n_channels + i
+    loop = TrackingLoop(eng, cfg, nsat)
+    blocks = []
+    for k in range(nsat):
+        a = (int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]))
+        loop.start(k, *a, 0, 0)
+        blocks.append(O.RefTrkBlock(_conf_text("Tracking_1B", FS, track_pilot=True, max_lock_fail=50, max_carrier_lock_fail=5000, **kw), "Tracking_1B", "1B", *a))
+    _device_vs_block_pilot("E1 pilot", loop, blocks, (x for _, x in e1_chunks(sc, E1_SECONDS)), nsat, sc["doppler"], 500)
+    for b in blocks:
+        b.close()
+    loop.close()
+    eng.close()
+
+
+@pytest.mark.gpu
+@needs_ref
+def test_device_loop_gps_l5_pilot_vs_the_reference_block():
+    """track_pilot=true for GPS L5: L5Q tracked (20-bit Neuman-Hofman code synchronised and wiped), the L5I symbols from the data correlator with
+    their own 10-bit Neuman-Hofman code removed (d_data_secondary_code_string, :227-237, :1305-1335) — against the reference's own block."""
+    import _signals as S
+    from gnss_sim_receiver_b200.tracking import TrackingEngine, TrackingLoop, loop_config
+    nsat, fs = 3, L5_FS
+    chunk = int(fs * 0.1)
+    rng = np.random.default_rng(53)
+    prns = rng.choice(np.arange(1, 33), nsat, replace=False)
+    doppler, delay, phase = rng.uniform(-3000, 3000, nsat), rng.uniform(0, 10230, nsat), rng.uniform(0, 2 * np.pi, nsat)
+    cn0, acq_err = rng.uniform(45, 49, nsat), rng.uniform(-10, 10, nsat)
+    ci = np.stack([S.l5_table(int(p)) for p in prns])
+    cq = np.stack([S.l5_table(int(p), q=True) for p in prns])
+    nh10 = np.array([1 if c == "0" else -1 for c in "0000110101"], dtype=np.int8)
+    nh20 = np.array([1 if c == "0" else -1 for c in "00000100110101001110"], dtype=np.int8)
+    bits = rng.choice(np.array([-1, 1], dtype=np.int8), (nsat, 1200))
+    sym_i = (np.repeat(bits, 10, axis=1) * np.tile(nh10, 1200)[None, :]).astype(np.int8)
+    sym_q = np.tile(nh20, (nsat, 600)).astype(np.int8)
+    two = lambda a: np.concatenate([a, a])
+    gen_codes, gen_sym = np.concatenate([ci, cq]), np.concatenate([sym_i, sym_q])
+    gen_phase = np.concatenate([phase, phase + np.pi / 2])  # the pilot in quadrature with the data component
+    acq_delay = np.mod(delay / (10.23e6 * (1 + doppler / 1176.45e6)) * fs, fs / 1000.0)
+    kw = dict(pll_bw_hz=20.0, dll_bw_hz=1.5, pll_bw_narrow_hz=5.0, dll_bw_narrow_hz=0.5, early_late_space_chips=0.5, early_late_space_narrow_chips=0.25,
+              pull_in_time_s=1, cn0_samples=20, cn0_min=25, carrier_lock_th=0.5)
+    eng = TrackingEngine(max_channels=2 * nsat, max_code_len=10230, ring_samples=4 * chunk, max_block=2 * int(fs / 1000), max_cmds=2 * nsat)
+    cfg = loop_config("L5", fs, track_pilot=True, max_code_lock_fail=50, max_carrier_lock_fail=5000, **kw)
+    for k in range(nsat):
+        eng.set_code(k, cq[k])
+        eng.set_code(nsat + k, ci[k])
+    loop = TrackingLoop(eng, cfg, nsat)
+    blocks = []
+    for k in range(nsat):
+        a = (int(prns[k]), float(acq_delay[k]), float(doppler[k] + acq_err[k]))
+        loop.start(k, *a, 0, 0)
+        blocks.append(O.RefTrkBlock(_conf_text("Tracking_L5", fs, track_pilot=True, max_lock_fail=50, max_carrier_lock_fail=5000, **kw), "Tracking_L5", "L5", *a))
+    n_total = int(L5_SECONDS * fs)
+    chunks = (O.gen_if(min(chunk, n_total - first), first, fs, gen_codes, two(doppler), two(delay), gen_phase, two(cn0) - 3.0103, nav_bits=gen_sym, periods_per_bit=1,
+                       f_chip=10.23e6, f_carrier=1176.45e6, seed=89) for first in range(0, n_total, chunk))
+    _device_vs_block_pilot("L5 pilot", loop, blocks, chunks, nsat, doppler, 250)
+    for b in blocks:
+        b.close()
+    loop.close()
+    eng.close()
