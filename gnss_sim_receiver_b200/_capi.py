@@ -98,6 +98,7 @@ SYMBOLS = {
     "gb200_loop_destroy": (C.c_int, [_vp]),
     "gb200_loop_start": (C.c_int, [_vp, C.c_int, C.c_uint32, C.c_double, C.c_double, C.c_uint64, C.c_uint64]),
     "gb200_loop_stop": (C.c_int, [_vp, C.c_int]),
+    "gb200_loop_set_secondary_code": (C.c_int, [_vp, C.c_int, C.c_char_p, C.c_int]),
     "gb200_loop_step": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int, C.POINTER(C.c_int)]),
     "gb200_loop_submit": (C.c_int, [_vp, _vp, C.c_int64]),
     "gb200_loop_collect": (C.c_int, [_vp, _vp, C.c_int, C.POINTER(C.c_int)]),

@@ -56,6 +56,7 @@ SYMBOLS = {
     "gb200h_fll_diff_atan": (_d, [_f, _f, _f, _f, _d, _d]),
     "gb200h_dll_nc_e_minus_l_normalized": (_d, [_f] * 7),
     "gb200h_dll_nc_vemlp_normalized": (_d, [_f] * 8),
+    "gb200h_e5a_q_secondary_code": (C.c_int, [C.c_uint, C.c_char_p]),
     "gb200h_sinboc_slope_abs": (_d, [_d]),
     "gb200h_sinboc_yintercept_abs": (_d, [_d]),
     "gb200h_cn0_m2m4_estimator": (_f, [_vp, _i, _f]),

@@ -78,6 +78,8 @@ struct LoopState
     float2 prompt_buffer[LOOP_MAX_CN0];
     unsigned sign_bits[LOOP_MAX_SEC / 32];  // prompt sign history, oldest at bit 0
     int sign_count;
+    int own_secondary;         // the channel carries its own secondary code (per-satellite codes: Galileo E5a-Q)
+    unsigned own_sec_zero[LOOP_MAX_SEC / 32];
     LoopFilterDll dll;
     LoopFilterPll pll;
     LoopSmoother cn0_smoother, lock_smoother;
@@ -362,7 +364,8 @@ __device__ void loop_update_tracking_vars(const LoopConf& k, LoopState& s)
 // :1263-1373.  dprompt: the data correlator's prompt (track_pilot), else unused
 __device__ void loop_save_correlation_results(const LoopConf& k, LoopState& s, const float2* taps, float2 dprompt)
 {
-    const bool flip = k.c.secondary && !((k.sec_zero[s.current_symbol >> 5] >> (s.current_symbol & 31)) & 1u);
+    const unsigned* sec_zero = s.own_secondary ? s.own_sec_zero : k.sec_zero;
+    const bool flip = k.c.secondary && !((sec_zero[s.current_symbol >> 5] >> (s.current_symbol & 31)) & 1u);
     const float sign = flip ? -1.0F : 1.0F;
     if (k.c.veml)
         {
@@ -436,7 +439,7 @@ __device__ bool loop_push_and_acquire_secondary(const LoopConf& k, LoopState& s,
             const int lo = i * 32;
             if (lo >= len) break;
             const unsigned mask = (len - lo >= 32) ? 0xffffffffu : ((1u << (len - lo)) - 1u);
-            matches += __popc(~(s.sign_bits[i] ^ k.sec_zero[i]) & mask);  // negative == zero_chip
+            matches += __popc(~(s.sign_bits[i] ^ (s.own_secondary ? s.own_sec_zero[i] : k.sec_zero[i])) & mask);  // negative == zero_chip
         }
     if (matches == len || matches == 0)
         {

@@ -164,6 +164,14 @@ double gb200h_dll_nc_vemlp_normalized(float ver, float vei, float er, float ei, 
 {
     return dll_nc_vemlp_normalized(c(ver, vei), c(er, ei), c(lr, li), c(vlr, vli));
 }
+int gb200h_e5a_q_secondary_code(unsigned prn, char* out)
+{
+    if (!out || prn < 1 || prn > 50) return 0;
+    const std::string s = gb200h::galileo_e5a_q_secondary_code(prn);
+    std::memcpy(out, s.c_str(), s.size() + 1);
+    return static_cast<int>(s.size());
+}
+
 double gb200h_sinboc_slope_abs(double x) { return sinboc11_slope_abs(x); }
 double gb200h_sinboc_yintercept_abs(double x) { return sinboc11_y_intercept_abs(x); }
 float gb200h_cn0_m2m4_estimator(const float* p, int length, float T) { return cn0_m2m4_estimator(reinterpret_cast<const cf32*>(p), length, T); }

@@ -27,6 +27,8 @@ double gb200h_fll_four_quadrant_atan(float r1, float i1, float r2, float i2, dou
 double gb200h_fll_diff_atan(float r1, float i1, float r2, float i2, double t1, double t2);
 double gb200h_dll_nc_e_minus_l_normalized(float er, float ei, float lr, float li, float spc, float slope, float y_intercept);
 double gb200h_dll_nc_vemlp_normalized(float ver, float vei, float er, float ei, float lr, float li, float vlr, float vli);
+/* GALILEO_E5A_Q_SECONDARY_CODE[prn - 1] as 100 '0' / '1' characters + NUL into out[101]; returns 100, or 0 for a PRN outside 1..50 */
+int gb200h_e5a_q_secondary_code(unsigned prn, char* out);
 double gb200h_sinboc_slope_abs(double x);
 double gb200h_sinboc_yintercept_abs(double x);
 float gb200h_cn0_m2m4_estimator(const float* prompt_ri, int length, float T);

@@ -182,6 +182,8 @@ _SIGNALS = {
 _PILOT = {
     "1B": dict(secondary=1, secondary_code="0011100000001010110110010", data_secondary_code="", interchange_iq=0),       # GALILEO_E1_C_SECONDARY_CODE
     "L5": dict(secondary=1, secondary_code="00000100110101001110", data_secondary_code="0000110101", interchange_iq=0),  # GPS_L5Q_NH_CODE_STR / GPS_L5I_NH_CODE_STR
+    # Galileo E5a-Q: 100-chip secondary code PER SATELLITE (TrackingLoop.set_secondary_code), the data component's CS20 removed, I / Q interchanged (:305-314)
+    "5X": dict(secondary=1, secondary_code="0" * 100, data_secondary_code="10000100001011101001", interchange_iq=1),
 }
 
 
@@ -246,6 +248,10 @@ class TrackingLoop:
 
     def stop(self, ch):
         check(self._lib.gb200_loop_stop(self._h, ch))
+
+    def set_secondary_code(self, ch, code):
+        """per-satellite secondary code of the tracked component ('0' / '1' string; Galileo E5a-Q), before start()"""
+        check(self._lib.gb200_loop_set_secondary_code(self._h, ch, code.encode(), len(code)))
 
     def step(self, iq=None, copy=True):
         """Append `iq` (host samples of the engine's item type) and run the rounds that are due; returns the records emitted."""

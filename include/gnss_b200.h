@@ -214,10 +214,10 @@ const char* gb200_trk_last_kernel(const gb200_trk* h);
  * state resident in HBM: one gb200_loop_step = upload the new IQ block, [correlate kernel -> loop kernel] for every channel whose
  * next window is in the ring, download the Gnss_Synchro records emitted in this step.  No per-channel host work.
  * Served: real-code channels with high_dyn = false — data-component tracking (GPS L1 C/A, GPS L5I, Galileo E1B, Galileo E5aI) and, with
- * track_pilot = 1, pilot tracking whose secondary code is the same for every satellite (Galileo E1C with E1B as data component, GPS L5Q
- * with L5I): the pilot's taps close the loop, a second one-tap correlator on the data code at the prompt shift supplies the symbols
+ * track_pilot = 1, pilot tracking (Galileo E1C with E1B as data component, GPS L5Q with L5I, Galileo E5aQ with E5aI): the pilot's taps close the loop, a second one-tap correlator on the data code at the prompt shift supplies the symbols
  * (d_correlator_data_cpu, :526-531,1051-1062; save_correlation_results :1305-1372).  The host block
- * (gnss_sim_receiver_b200/host/b200_dll_pll_veml_tracking.cc) serves the rest (high_dyn, Galileo E5aQ's per-satellite secondary codes).
+ * (gnss_sim_receiver_b200/host/b200_dll_pll_veml_tracking.cc) serves the rest (high_dyn).  Galileo E5a-Q, whose secondary code depends on the
+ * satellite, takes it per channel through gb200_loop_set_secondary_code.
  * With track_pilot the engine needs max_channels and max_cmds >= 2 * n_channels: channel i's tracking code is the engine's code slot
  * i, its data code slot n_channels + i.
  * ====================================================================== */
@@ -288,6 +288,10 @@ int gb200_loop_destroy(gb200_loop* l);
 int gb200_loop_start(gb200_loop* l, int ch, uint32_t prn, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp_samples, uint64_t nitems_read);
 /* stop_tracking(): back to standby */
 int gb200_loop_stop(gb200_loop* l, int ch);
+/* A secondary code of the TRACKED component that depends on the satellite (Galileo E5a-Q: GALILEO_E5A_Q_SECONDARY_CODE[prn - 1],
+ * dll_pll_veml_tracking.cc:733-735 d_secondary_code_string = &GALILEO_E5A_Q_SECONDARY_CODE[PRN - 1]): '0' / '1' characters, as long as
+ * gb200_loop_config::secondary_code_length; call before gb200_loop_start of that channel.  Channels without one use the configuration's. */
+int gb200_loop_set_secondary_code(gb200_loop* l, int ch, const char* code, int length);
 /* One step.  Appends n_samples of the engine's item type from host memory (NULL / 0: none), runs every round that is due and
  * copies the records emitted during this step to `records` (at most max_records; *n_records receives how many were emitted). */
 int gb200_loop_step(gb200_loop* l, const void* iq_host, int64_t n_samples, gb200_loop_record* records, int max_records, int* n_records);

@@ -753,24 +753,41 @@ def test_device_loop_galileo_e1_pilot_vs_the_reference_block():
 
 @pytest.mark.gpu
 @needs_ref
-def test_device_loop_gps_l5_pilot_vs_the_reference_block():
-    """track_pilot=true for GPS L5: L5Q tracked (20-bit Neuman-Hofman code synchronised and wiped), the L5I symbols from the data correlator with
-    their own 10-bit Neuman-Hofman code removed (d_data_secondary_code_string, :227-237, :1305-1335) — against the reference's own block."""
+@pytest.mark.parametrize("signal", ["L5", "5X"])
+def test_device_loop_l5_band_pilot_vs_the_reference_block(signal):
+    """track_pilot=true in the L5 band, against the reference's own block:
+    GPS L5 — L5Q tracked (20-bit Neuman-Hofman code synchronised and wiped), the L5I symbols from the data correlator with their own 10-bit
+    code removed (d_data_secondary_code_string, :227-237, :1305-1335);
+    Galileo E5a — E5a-Q tracked with the 100-chip secondary code OF THE SATELLITE (gb200_loop_set_secondary_code; :733-735), the E5a-I
+    symbols with CS20 removed, Prompt_I / Prompt_Q interchanged (:305-314)."""
     import _signals as S
+    from gnss_sim_receiver_b200 import _hostapi as H
     from gnss_sim_receiver_b200.tracking import TrackingEngine, TrackingLoop, loop_config
     nsat, fs = 3, L5_FS
     chunk = int(fs * 0.1)
-    rng = np.random.default_rng(53)
+    rng = np.random.default_rng(53 if signal == "L5" else 59)
     prns = rng.choice(np.arange(1, 33), nsat, replace=False)
     doppler, delay, phase = rng.uniform(-3000, 3000, nsat), rng.uniform(0, 10230, nsat), rng.uniform(0, 2 * np.pi, nsat)
     cn0, acq_err = rng.uniform(45, 49, nsat), rng.uniform(-10, 10, nsat)
-    ci = np.stack([S.l5_table(int(p)) for p in prns])
-    cq = np.stack([S.l5_table(int(p), q=True) for p in prns])
-    nh10 = np.array([1 if c == "0" else -1 for c in "0000110101"], dtype=np.int8)
-    nh20 = np.array([1 if c == "0" else -1 for c in "00000100110101001110"], dtype=np.int8)
-    bits = rng.choice(np.array([-1, 1], dtype=np.int8), (nsat, 1200))
-    sym_i = (np.repeat(bits, 10, axis=1) * np.tile(nh10, 1200)[None, :]).astype(np.int8)
-    sym_q = np.tile(nh20, (nsat, 600)).astype(np.int8)
+    signs = lambda code: np.array([1 if c == "0" else -1 for c in code], dtype=np.int8)
+    if signal == "L5":
+        ci = np.stack([S.l5_table(int(p)) for p in prns])
+        cq = np.stack([S.l5_table(int(p), q=True) for p in prns])
+        data_sec, spb, role = "0000110101", 10, "Tracking_L5"
+        pilot_sec = ["00000100110101001110"] * nsat
+    else:
+        ci = np.stack([np.ascontiguousarray(S.e5a_primary(int(p), "5I").real, dtype=np.float32) for p in prns])
+        cq = np.stack([np.ascontiguousarray(S.e5a_primary(int(p), "5Q").real, dtype=np.float32) for p in prns])
+        data_sec, spb, role = "10000100001011101001", 20, "Tracking_5X"
+        pilot_sec = []
+        for p in prns:
+            buf = C_create_string_buffer(101)
+            assert H.lib().gb200h_e5a_q_secondary_code(int(p), buf) == 100
+            pilot_sec.append(buf.value.decode())
+    n_bits = 12000 // spb
+    bits = rng.choice(np.array([-1, 1], dtype=np.int8), (nsat, n_bits))
+    sym_i = (np.repeat(bits, spb, axis=1) * np.tile(signs(data_sec), n_bits)[None, :]).astype(np.int8)
+    sym_q = np.stack([np.tile(signs(c), 12000 // len(c)) for c in pilot_sec]).astype(np.int8)
     two = lambda a: np.concatenate([a, a])
     gen_codes, gen_sym = np.concatenate([ci, cq]), np.concatenate([sym_i, sym_q])
     gen_phase = np.concatenate([phase, phase + np.pi / 2])  # the pilot in quadrature with the data component
@@ -778,7 +795,7 @@ def test_device_loop_gps_l5_pilot_vs_the_reference_block():
     kw = dict(pll_bw_hz=20.0, dll_bw_hz=1.5, pll_bw_narrow_hz=5.0, dll_bw_narrow_hz=0.5, early_late_space_chips=0.5, early_late_space_narrow_chips=0.25,
               pull_in_time_s=1, cn0_samples=20, cn0_min=25, carrier_lock_th=0.5)
     eng = TrackingEngine(max_channels=2 * nsat, max_code_len=10230, ring_samples=4 * chunk, max_block=2 * int(fs / 1000), max_cmds=2 * nsat)
-    cfg = loop_config("L5", fs, track_pilot=True, max_code_lock_fail=50, max_carrier_lock_fail=5000, **kw)
+    cfg = loop_config(signal, fs, track_pilot=True, max_code_lock_fail=50, max_carrier_lock_fail=5000, **kw)
     for k in range(nsat):
         eng.set_code(k, cq[k])
         eng.set_code(nsat + k, ci[k])
@@ -786,13 +803,20 @@ def test_device_loop_gps_l5_pilot_vs_the_reference_block():
     blocks = []
     for k in range(nsat):
         a = (int(prns[k]), float(acq_delay[k]), float(doppler[k] + acq_err[k]))
+        if signal == "5X":
+            loop.set_secondary_code(k, pilot_sec[k])
         loop.start(k, *a, 0, 0)
-        blocks.append(O.RefTrkBlock(_conf_text("Tracking_L5", fs, track_pilot=True, max_lock_fail=50, max_carrier_lock_fail=5000, **kw), "Tracking_L5", "L5", *a))
+        blocks.append(O.RefTrkBlock(_conf_text(role, fs, track_pilot=True, max_lock_fail=50, max_carrier_lock_fail=5000, **kw), role, signal, *a))
     n_total = int(L5_SECONDS * fs)
     chunks = (O.gen_if(min(chunk, n_total - first), first, fs, gen_codes, two(doppler), two(delay), gen_phase, two(cn0) - 3.0103, nav_bits=gen_sym, periods_per_bit=1,
                        f_chip=10.23e6, f_carrier=1176.45e6, seed=89) for first in range(0, n_total, chunk))
-    _device_vs_block_pilot("L5 pilot", loop, blocks, chunks, nsat, doppler, 250)
+    _device_vs_block_pilot(f"{signal} pilot", loop, blocks, chunks, nsat, doppler, 120 if signal == "5X" else 250)
     for b in blocks:
         b.close()
     loop.close()
     eng.close()
+
+
+def C_create_string_buffer(n):
+    import ctypes
+    return ctypes.create_string_buffer(n)
