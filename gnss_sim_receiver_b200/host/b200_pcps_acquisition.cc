@@ -194,6 +194,13 @@ void b200_pcps_acquisition::acquisition_core(uint64_t samp_count)
             last_.acq_doppler_hz = static_cast<float>(last_.doppler_hz);
         }
     d_mag = last_.peak;
+    if (d_step_two && d_use_CFAR_algorithm_flag)
+        {
+            // :517-528: max_to_input_power_statistic estimates the input power on the coarse grid only; the fine step divides its own
+            // maximum by the power the first step left behind
+            last_.input_power = d_input_power;
+            last_.test_statistics = last_.peak / d_input_power;
+        }
     d_input_power = last_.input_power;
     d_test_statistics = last_.test_statistics;
     const Acq_Conf& p = d_acq_parameters;

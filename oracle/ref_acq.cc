@@ -100,6 +100,7 @@ struct ref_acq_status
     uint64_t acq_samplestamp_samples, sample_counter;
     int64_t consumed_total;
     int32_t doppler_step, doppler_max, use_cfar, bit_transition, it_size;
+    int32_t step_two, pad_;  // d_step_two: the coarse step was positive, the fine step (make_two_steps) starts with the next call
 };
 
 // conf_text: "role.key=value" lines as in a .conf; ms_per_code / chip_rate / opt_freq: what the adapter passes (e.g. 1, 1.023e6, 2e6)
@@ -178,6 +179,7 @@ void ref_acq_get_status(void* h, ref_acq_status* s)
     s->acq_samplestamp_samples = r->synchro.Acq_samplestamp_samples, s->sample_counter = b.d_sample_counter;
     s->consumed_total = b.shim_consumed;
     s->doppler_step = static_cast<int32_t>(b.d_doppler_step), s->doppler_max = b.d_acq_parameters.doppler_max;
+    s->step_two = b.d_step_two ? 1 : 0;
     s->use_cfar = b.d_use_CFAR_algorithm_flag, s->bit_transition = b.d_acq_parameters.bit_transition_flag, s->it_size = static_cast<int32_t>(b.d_acq_parameters.it_size);
 }
 // the magnitude grid of the last dwell: out[bin][neff]

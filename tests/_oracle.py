@@ -368,7 +368,8 @@ class RefAcqStatus(C.Structure):
                 ("threshold", C.c_float), ("mag", C.c_float), ("input_power", C.c_float), ("test_statistics", C.c_float), ("samples_per_code", C.c_float),
                 ("samples_per_ms", C.c_float), ("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double),
                 ("acq_samplestamp_samples", C.c_uint64), ("sample_counter", C.c_uint64), ("consumed_total", C.c_int64),
-                ("doppler_step", C.c_int32), ("doppler_max", C.c_int32), ("use_cfar", C.c_int32), ("bit_transition", C.c_int32), ("it_size", C.c_int32)]
+                ("doppler_step", C.c_int32), ("doppler_max", C.c_int32), ("use_cfar", C.c_int32), ("bit_transition", C.c_int32), ("it_size", C.c_int32),
+                ("step_two", C.c_int32), ("pad_", C.c_int32)]
 
 
 class RefAcq:
@@ -426,7 +427,7 @@ class RefAcq:
         pos, idle = 0, 0
         for _ in range(100000):
             st = self.status()
-            if st.state == 0 and not st.active:
+            if st.state == 0 and not st.active and not st.step_two:  # (between the two steps of make_two_steps the block is inactive for one call)
                 break
             # (the block switches from buffering to searching on the call AFTER the one that filled its buffer, :985-989, so a call with
             # no new items is part of the sequence; two calls in a row without any effect end the loop)

@@ -155,12 +155,30 @@ def test_two_step_acquisition_refines_doppler():
     assert (s.indext, s.doppler_index) == (r2.indext, r2.doppler_index)
     assert s.acq_doppler_hz == r2.acq_doppler_hz == 875.0          # nearest fine bin to 835 Hz
     assert s.acq_delay_samples == r2.acq_delay_samples
-    assert abs(s.test_statistics - r2.test_statistics) <= 1e-3 * r2.test_statistics
+    # max_to_input_power_statistic estimates the input power in the first step only (:517-522 sit under `if (!d_step_two)`): the fine step's
+    # statistic is the fine grid's maximum over the power the COARSE search left in d_input_power
+    want_stat = r2.peak / r1.input_power
+    assert abs(r2.test_statistics - want_stat) > 0.05 * want_stat  # (the two laws differ on this stream: the check below can tell them apart)
+    assert abs(s.test_statistics - want_stat) <= 1e-4 * want_stat and abs(s.input_power - r1.input_power) <= 1e-5 * r1.input_power
     # the fine step was judged against its own threshold (4 bins, pfa_second_step); once it has declared the acquisition the block
     # is back on the coarse step's threshold (calculate_threshold after d_step_two = false, :775-786)
     assert s.test_statistics > O.acq_threshold(conf2, 0.01)
     assert abs(s.threshold - O.acq_threshold(conf1, 0.01)) <= 1e-5 * s.threshold
     a.close()
+    # ... and the reference's OWN block (pcps_acquisition.cc compiled unmodified into oracle/_ref, oracle/ref_acq.cc) on the same .conf, replica
+    # and stream: it takes the same two buffers, raises the same event and reports the same fine-step result
+    if O.ref_available():
+        b = O.RefAcq(conf_text.replace("_B200", ""), "Acquisition_1C", 1, 1.023e6, 2e6, prn, "G", "1C")
+        b.init(10000, 250, 0.0)
+        b.set_local_code(O.gps_l1_ca_code_sampled(prn, int(FS), 4000))
+        b.arm()
+        rc = b.work(x, 1)
+        rs = b.status()
+        b.close()
+        assert rc == consumed and list(rs.fsm_events[:rs.n_fsm_events]) == [1]
+        assert (rs.acq_delay_samples, rs.acq_doppler_hz, rs.acq_samplestamp_samples) == (s.acq_delay_samples, s.acq_doppler_hz, s.acq_samplestamp_samples)
+        assert abs(rs.test_statistics - s.test_statistics) <= 1e-5 * rs.test_statistics and abs(rs.threshold - s.threshold) <= 1e-5 * rs.threshold
+        assert abs(rs.input_power - s.input_power) <= 1e-5 * rs.input_power
 
 
 @pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built")
