@@ -26,6 +26,14 @@ class AcqStatus(C.Structure):
                 ("state", C.c_int32), ("active", C.c_int32), ("last_event", C.c_int32), ("indext", C.c_uint32), ("doppler_index", C.c_int32)]
 
 
+class FineDopplerStatus(C.Structure):
+    """gb200h_acqfd_status"""
+    _fields_ = [("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double), ("acq_samplestamp_samples", C.c_uint64), ("sample_counter", C.c_uint64),
+                ("fine_index", C.c_int64), ("test_statistics", C.c_float), ("threshold", C.c_float), ("state", C.c_int32), ("active", C.c_int32),
+                ("last_event", C.c_int32), ("positive_acq", C.c_int32), ("num_doppler_points", C.c_int32), ("fft_size", C.c_int32),
+                ("acq_doppler_step", C.c_uint32), ("pad_", C.c_int32)]
+
+
 class Synchro(C.Structure):
     """gb200h_synchro: every field of the GnssSynchro message (docs/protobuf/gnss_synchro.proto of the reference)"""
     _fields_ = [("system", C.c_char), ("signal", C.c_char * 3), ("prn", C.c_uint32), ("channel_id", C.c_int32),
@@ -88,6 +96,11 @@ SYMBOLS = {
     "gb200h_acq_arm": (_i, [_vp, _f]),
     "gb200h_acq_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
     "gb200h_acq_get_status": (_i, [_vp, C.POINTER(AcqStatus)]),
+    "gb200h_acqfd_create": (_i, [C.c_char_p, C.c_char_p, C.c_uint, C.POINTER(_vp)]),
+    "gb200h_acqfd_destroy": (None, [_vp]),
+    "gb200h_acqfd_arm": (_i, [_vp, C.c_uint, C.c_uint, C.c_float]),
+    "gb200h_acqfd_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
+    "gb200h_acqfd_get_status": (_i, [_vp, C.POINTER(FineDopplerStatus)]),
     "gb200h_mat_write_sample": (_i, [_s, _vp, _i, _i, C.c_int32, C.c_uint32, C.c_uint64, _f]),
     "gb200h_rx_create": (_i, [_s, _s, _s, _i, C.POINTER(C.c_uint), _i, C.POINTER(_vp)]),
     "gb200h_rx_destroy": (None, [_vp]),
@@ -245,6 +258,38 @@ class AcquisitionBlock:
     def status(self):
         s = AcqStatus()
         check(self._lib.gb200h_acq_get_status(self._h, C.byref(s)))
+        return s
+
+
+class FineDopplerAcquisitionBlock:
+    """GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200 (host/b200_pcps_acquisition_fine_doppler.h) driven like a channel drives it"""
+
+    def __init__(self, conf_text, role, prn):
+        self._lib = lib()
+        self._h = _vp()
+        check(self._lib.gb200h_acqfd_create(conf_text.encode(), role.encode(), prn, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self._lib.gb200h_acqfd_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def arm(self, doppler_max, doppler_step, threshold):
+        check(self._lib.gb200h_acqfd_arm(self._h, int(doppler_max), int(doppler_step), float(threshold)))
+
+    def work(self, items, noutput_items):
+        items = np.ascontiguousarray(items, dtype=np.complex64)
+        return check(self._lib.gb200h_acqfd_work(self._h, items.ctypes.data, items.size, int(noutput_items)))
+
+    def status(self):
+        s = FineDopplerStatus()
+        check(self._lib.gb200h_acqfd_get_status(self._h, C.byref(s)))
         return s
 
 

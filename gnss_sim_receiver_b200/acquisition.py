@@ -116,3 +116,12 @@ class AcquisitionEngine:
         out = np.zeros_like(x)
         check(self._lib.gb200_acq_fft(self._h, x.ctypes.data, out.ctypes.data, int(inverse)))
         return out
+
+    def spectrum_peak(self, x, rep, pad_factor=8):
+        """estimate_Doppler's search (pcps_acquisition_fine_doppler_cc.cc:338-374): (index of the first maximum, value) of
+        |FFT(x * rep repeated, zero-padded to pad_factor * len(x))|^2; len(x) a multiple of the engine's fft_size"""
+        x = np.ascontiguousarray(x, dtype=np.complex64)
+        rep = np.ascontiguousarray(rep, dtype=np.complex64)
+        idx, val = C.c_int64(0), C.c_float(0.0)
+        check(self._lib.gb200_acq_spectrum_peak(self._h, x.ctypes.data, len(x), rep.ctypes.data, len(rep), int(pad_factor), C.byref(idx), C.byref(val)))
+        return int(idx.value), float(val.value)

@@ -266,6 +266,82 @@ std::unique_ptr<TrackingInterface> GetB200TrkBlock(const ConfigurationInterface*
     return nullptr;
 }
 
+// adapters/gps_l1_ca_pcps_acquisition_fine_doppler.cc:30-100
+GpsL1CaPcpsAcquisitionFineDopplerB200::GpsL1CaPcpsAcquisitionFineDopplerB200(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
+    : role_(role),
+      item_size_(sizeof(gr_complex)),
+      doppler_max_(c->property(role + ".doppler_max", 5000)),
+      max_dwells_(c->property(role + ".max_dwells", 1)),
+      sampled_ms_(static_cast<unsigned int>(c->property(role + ".coherent_integration_time_ms", 1))),
+      dump_(c->property(role + ".dump", false))
+{
+    Acq_Conf acq_parameters = Acq_Conf();
+    item_type_ = c->property(role_ + ".item_type", std::string("gr_complex"));
+    const int64_t fs_in_deprecated = c->property("GNSS-SDR.internal_fs_hz", static_cast<int64_t>(2048000));
+    fs_in_ = c->property("GNSS-SDR.internal_fs_sps", fs_in_deprecated);
+    acq_parameters.fs_in = fs_in_;
+    acq_parameters.samples_per_chip = static_cast<unsigned int>(std::ceil((1.0 / 1023000.0) * static_cast<float>(acq_parameters.fs_in)));  // GPS_L1_CA_CHIP_PERIOD_S
+    acq_parameters.dump = dump_;
+    dump_filename_ = c->property(role_ + ".dump_filename", std::string("./acquisition.mat"));
+    acq_parameters.dump_filename = dump_filename_;
+    acq_parameters.doppler_max = doppler_max_;
+    acq_parameters.sampled_ms = sampled_ms_;
+    acq_parameters.max_dwells = static_cast<uint32_t>(max_dwells_);
+    acq_parameters.blocking_on_standby = c->property(role + ".blocking_on_standby", false);
+    acq_parameters.device = c->property(role + ".device", 0);
+    vector_length_ = static_cast<unsigned int>(std::round(static_cast<double>(fs_in_) / (1023000.0 / 1023.0)));
+    acq_parameters.samples_per_ms = static_cast<float>(vector_length_);
+    code_ = std::vector<std::complex<float>>(vector_length_);
+    // the reference block takes gr_complex only; any other item type leaves it without a block (:76-85) — here that is an error at once
+    if (item_type_ != "gr_complex") throw std::invalid_argument(item_type_ + " unknown acquisition item type (GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200 takes gr_complex)");
+    acquisition_cc_ = std::make_shared<b200_pcps_acquisition_fine_doppler>(acq_parameters);
+    if (in > 1) std::cerr << "This implementation only supports one input stream\n";
+    if (out > 0) std::cerr << "This implementation does not provide an output stream\n";
+}
+void GpsL1CaPcpsAcquisitionFineDopplerB200::connect(gr::top_block_sptr top_block)
+{
+    if (top_block) { /* nothing to connect internally */ }
+}
+void GpsL1CaPcpsAcquisitionFineDopplerB200::disconnect(gr::top_block_sptr top_block)
+{
+    if (top_block) { /* nothing to disconnect */ }
+}
+void GpsL1CaPcpsAcquisitionFineDopplerB200::stop_acquisition()
+{
+    acquisition_cc_->set_state(0);
+    acquisition_cc_->set_active(false);
+}
+void GpsL1CaPcpsAcquisitionFineDopplerB200::set_threshold(float threshold)
+{
+    threshold_ = threshold;
+    acquisition_cc_->set_threshold(threshold_);
+}
+void GpsL1CaPcpsAcquisitionFineDopplerB200::set_doppler_max(unsigned int doppler_max)
+{
+    doppler_max_ = static_cast<int>(doppler_max);
+    acquisition_cc_->set_doppler_max(doppler_max);
+}
+void GpsL1CaPcpsAcquisitionFineDopplerB200::set_doppler_step(unsigned int doppler_step)
+{
+    doppler_step_ = doppler_step;
+    acquisition_cc_->set_doppler_step(doppler_step_);
+}
+void GpsL1CaPcpsAcquisitionFineDopplerB200::set_gnss_synchro(Gnss_Synchro* gnss_synchro)
+{
+    gnss_synchro_ = gnss_synchro;
+    acquisition_cc_->set_gnss_synchro(gnss_synchro_);
+}
+void GpsL1CaPcpsAcquisitionFineDopplerB200::set_channel(unsigned int channel)
+{
+    channel_ = channel;
+    acquisition_cc_->set_channel(channel_);
+}
+void GpsL1CaPcpsAcquisitionFineDopplerB200::set_local_code()
+{
+    gps_l1_ca_code_gen_complex_sampled(code_.data(), static_cast<int>(code_.size()), gnss_synchro_->PRN, static_cast<int32_t>(fs_in_), 0);
+    acquisition_cc_->set_local_code(code_.data());
+}
+
 std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
 {
     const std::string impl = c->property(role + ".implementation", std::string("Pass_Through"));
@@ -273,6 +349,7 @@ std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const ConfigurationInterfa
     if (impl == "Galileo_E1_PCPS_Ambiguous_Acquisition_B200") return std::make_unique<GalileoE1PcpsAmbiguousAcquisitionB200>(c, role, in, out);
     if (impl == "GPS_L5i_PCPS_Acquisition_B200") return std::make_unique<GpsL5iPcpsAcquisitionB200>(c, role, in, out);
     if (impl == "Galileo_E5a_Pcps_Acquisition_B200") return std::make_unique<GalileoE5aPcpsAcquisitionB200>(c, role, in, out);
+    if (impl == "GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200") return std::make_unique<GpsL1CaPcpsAcquisitionFineDopplerB200>(c, role, in, out);
     return nullptr;
 }
 

@@ -9,6 +9,7 @@
 
 #include "b200_dll_pll_veml_tracking.h"
 #include "b200_pcps_acquisition.h"
+#include "b200_pcps_acquisition_fine_doppler.h"
 #include "gnss_sdr_compat.h"
 #include <memory>
 #include <string>
@@ -179,6 +180,49 @@ public:
 protected:
     void generate_code(std::complex<float>* code, int32_t fs) override;
     bool acq_pilot_, acq_iq_;
+};
+
+// adapters/gps_l1_ca_pcps_acquisition_fine_doppler.{h:46-170,cc:30-190}: `GPS_L1_CA_PCPS_Acquisition_Fine_Doppler`; gr_complex items only,
+// keys doppler_max (5000), max_dwells (1), coherent_integration_time_ms, blocking_on_standby, dump / dump_filename (the dump is not written here)
+class GpsL1CaPcpsAcquisitionFineDopplerB200 : public AcquisitionInterface
+{
+public:
+    GpsL1CaPcpsAcquisitionFineDopplerB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+    std::string role() override { return role_; }
+    std::string implementation() override { return "GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200"; }
+    size_t item_size() override { return item_size_; }
+    void connect(gr::top_block_sptr top_block) override;
+    void disconnect(gr::top_block_sptr top_block) override;
+    gr::basic_block_sptr get_left_block() override { return acquisition_cc_; }
+    gr::basic_block_sptr get_right_block() override { return acquisition_cc_; }
+    void set_gnss_synchro(Gnss_Synchro* p_gnss_synchro) override;
+    void set_channel(unsigned int channel) override;
+    void set_channel_fsm(std::weak_ptr<ChannelFsm> channel_fsm) override { channel_fsm_ = std::move(channel_fsm); }
+    void set_threshold(float threshold) override;
+    void set_doppler_max(unsigned int doppler_max) override;
+    void set_doppler_step(unsigned int doppler_step) override;
+    void init() override { acquisition_cc_->init(); }
+    void set_local_code() override;
+    void set_state(int state) override { acquisition_cc_->set_state(state); }
+    signed int mag() override { return static_cast<signed int>(acquisition_cc_->mag()); }
+    void reset() override { acquisition_cc_->set_active(true); }
+    void stop_acquisition() override;
+    void set_resampler_latency(uint32_t latency_samples __attribute__((unused))) override {}
+    std::shared_ptr<b200_pcps_acquisition_fine_doppler> block() { return acquisition_cc_; }
+    const std::vector<std::complex<float>>& local_code() const { return code_; }
+
+private:
+    std::shared_ptr<b200_pcps_acquisition_fine_doppler> acquisition_cc_;
+    std::weak_ptr<ChannelFsm> channel_fsm_;
+    std::vector<std::complex<float>> code_;
+    std::string role_, item_type_, dump_filename_;
+    Gnss_Synchro* gnss_synchro_{nullptr};
+    int64_t fs_in_;
+    size_t item_size_;
+    float threshold_{0.0F};
+    int doppler_max_, max_dwells_;
+    unsigned int vector_length_{0}, channel_{0}, doppler_step_{0}, sampled_ms_;
+    bool dump_;
 };
 
 // The `.implementation` strings this tree serves; nullptr for any other string (the caller falls through to the

@@ -579,7 +579,110 @@ struct gb200h_acq
     int last_event{0};
 };
 
+struct gb200h_acqfd
+{
+    B200Configuration cfg;
+    std::unique_ptr<GpsL1CaPcpsAcquisitionFineDopplerB200> adapter;
+    Gnss_Synchro synchro;
+    int last_event{0};
+};
+
 extern "C" {
+
+int gb200h_acqfd_create(const char* conf_text, const char* role, unsigned prn, gb200h_acqfd** out)
+{
+    try
+        {
+            auto a = std::make_unique<gb200h_acqfd>();
+            a->cfg.load_string(conf_text);
+            auto blk = GetB200AcqBlock(&a->cfg, role, 1, 0);
+            auto* fd = dynamic_cast<GpsL1CaPcpsAcquisitionFineDopplerB200*>(blk.get());
+            if (!fd) throw std::runtime_error(std::string(role) + ".implementation is not GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200");
+            blk.release();
+            a->adapter.reset(fd);
+            a->synchro.System = 'G';
+            std::memset(a->synchro.Signal, 0, 3);
+            a->synchro.Signal[0] = '1';
+            a->synchro.Signal[1] = 'C';
+            a->synchro.PRN = prn;
+            a->adapter->set_gnss_synchro(&a->synchro);
+            a->adapter->set_channel(0);
+            gb200h_acqfd* raw = a.get();
+            a->adapter->block()->set_event_sink([raw](int ev) { raw->last_event = ev; });
+            *out = a.release();
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+void gb200h_acqfd_destroy(gb200h_acqfd* a) { delete a; }
+
+int gb200h_acqfd_arm(gb200h_acqfd* a, unsigned doppler_max, unsigned doppler_step, float threshold)
+{
+    try
+        {
+            auto& ad = *a->adapter;
+            ad.set_doppler_max(doppler_max);
+            ad.set_doppler_step(doppler_step);
+            ad.set_threshold(threshold);
+            ad.init();
+            ad.set_local_code();
+            ad.block()->start();
+            a->last_event = 0;
+            ad.set_state(1);
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int64_t gb200h_acqfd_work(gb200h_acqfd* a, const void* items, int64_t n_items, int noutput_items)
+{
+    try
+        {
+            auto& blk = *a->adapter->block();
+            const auto* in = static_cast<const std::complex<float>*>(items);
+            const int64_t need = std::max(blk.fft_size(), noutput_items);
+            int64_t pos = 0;
+            while (n_items - pos >= need)
+                {
+                    pos += blk.general_work(noutput_items, in + pos, static_cast<int>(std::min<int64_t>(n_items - pos, 1 << 30)));
+                    if (blk.state() == 0 && !blk.active()) break;
+                }
+            return pos;
+        }
+    catch (const std::exception& e)
+        {
+            fail(e);
+            return -1;
+        }
+}
+
+int gb200h_acqfd_get_status(gb200h_acqfd* a, gb200h_acqfd_status* s)
+{
+    const auto& blk = *a->adapter->block();
+    std::memset(s, 0, sizeof(*s));
+    s->acq_delay_samples = a->synchro.Acq_delay_samples;
+    s->acq_doppler_hz = a->synchro.Acq_doppler_hz;
+    s->acq_samplestamp_samples = a->synchro.Acq_samplestamp_samples;
+    s->acq_doppler_step = a->synchro.Acq_doppler_step;
+    s->sample_counter = blk.sample_counter();
+    s->fine_index = blk.fine_index();
+    s->test_statistics = blk.test_statistics();
+    s->threshold = blk.threshold();
+    s->state = blk.state();
+    s->active = blk.active() ? 1 : 0;
+    s->last_event = a->last_event;
+    s->positive_acq = blk.positive_acq();
+    s->num_doppler_points = blk.num_doppler_points();
+    s->fft_size = blk.fft_size();
+    return 0;
+}
 
 int gb200h_acq_create(const char* conf_text, const char* role, unsigned prn, gb200h_acq** out) { return gb200h_acq_create2(conf_text, role, prn, 'G', "1C", out); }
 

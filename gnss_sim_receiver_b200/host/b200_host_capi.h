@@ -101,6 +101,27 @@ int gb200h_acq_arm(gb200h_acq* a, float threshold_if_no_pfa);
 int64_t gb200h_acq_work(gb200h_acq* a, const void* items, int64_t n_items, int chunk);
 int gb200h_acq_get_status(gb200h_acq* a, gb200h_acq_status* s);
 
+/* ---- fine-Doppler acquisition block (GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200; b200_pcps_acquisition_fine_doppler.h) */
+typedef struct gb200h_acqfd gb200h_acqfd;
+typedef struct
+{
+    double acq_delay_samples, acq_doppler_hz;
+    uint64_t acq_samplestamp_samples, sample_counter;
+    int64_t fine_index; /* index of the padded-spectrum maximum of the last estimate_Doppler, -1 before */
+    float test_statistics, threshold;
+    int32_t state, active, last_event, positive_acq, num_doppler_points, fft_size;
+    uint32_t acq_doppler_step;
+    int32_t pad_;
+} gb200h_acqfd_status;
+int gb200h_acqfd_create(const char* conf_text, const char* role, unsigned prn, gb200h_acqfd** out);
+void gb200h_acqfd_destroy(gb200h_acqfd* a);
+/* the adapter calls a channel makes: set_doppler_max, set_doppler_step, set_threshold, init, set_local_code, start, set_state(1) */
+int gb200h_acqfd_arm(gb200h_acqfd* a, unsigned doppler_max, unsigned doppler_step, float threshold);
+/* plays the scheduler over a host buffer of gr_complex items: general_work(noutput_items, ...) while at least max(fft_size, noutput_items)
+ * items are left, until the block has raised its event and gone idle; returns the items consumed, -1 on error */
+int64_t gb200h_acqfd_work(gb200h_acqfd* a, const void* items, int64_t n_items, int noutput_items);
+int gb200h_acqfd_get_status(gb200h_acqfd* a, gb200h_acqfd_status* s);
+
 /* MAT level-5 writer used by the acquisition dump (b200_mat_writer.h): one file with a single matrix and one scalar of each class */
 int gb200h_mat_write_sample(const char* filename, const float* grid, int rows, int cols, int32_t i32, uint32_t u32, uint64_t u64, float f32);
 

@@ -388,6 +388,14 @@ int gb200_acq_read_grid(gb200_acq* h, int slot, float* grid_host);
 int gb200_acq_read_cells(gb200_acq* h, int n_slots, float* vmax, int32_t* imax, float* sum);
 /* forward transform of one fft_size block through the engine's FFT (test hook: natural-order output) */
 int gb200_acq_fft(gb200_acq* h, const gb200_cf32* in_host, gb200_cf32* out_host, int inverse);
+/* Fine Doppler estimate — pcps_acquisition_fine_doppler_cc::estimate_Doppler (pcps_acquisition_fine_doppler_cc.cc:338-402): the n_x
+ * buffered samples x (10 code periods) times the delay-aligned replica rep (one period, repeated: :357-366), transformed zero-padded to
+ * pad_factor * n_x points (:340-345,:368), |.|^2 (:371), index of the FIRST maximum (volk_gnsssdr_32f_index_max_32u, :374) in
+ * [0, pad_factor * n_x) and its value.  The handle's fft_size must divide n_x (fold = n_x / fft_size <= 64): the padded transform is
+ * evaluated as pad_factor * fold transforms of fft_size points on the engine's own FFT (csrc/acq_peak.inc), nothing of the padded
+ * length is stored.  Host buffers in, blocking; the handle needs a Doppler grid (any) and a factorable fft_size. */
+int gb200_acq_spectrum_peak(gb200_acq* h, const gb200_cf32* x_host, int64_t n_x, const gb200_cf32* rep_host, int rep_len, int pad_factor,
+    int64_t* index_out, float* value_out);
 
 #ifdef __cplusplus
 }

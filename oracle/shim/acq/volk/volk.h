@@ -30,4 +30,11 @@ inline void volk_32f_x2_add_32f(float* c, const float* a, const float* b, unsign
 {
     for (unsigned int i = 0; i < n; i++) c[i] = a[i] + b[i];
 }
+// (pcps_acquisition_fine_doppler_cc::estimate_input_power only, which general_work never calls: VOLK's generic running sum)
+inline void volk_32f_accumulator_s32f(float* result, const float* a, unsigned int n)
+{
+    float acc = 0.0F;
+    for (unsigned int i = 0; i < n; i++) acc += a[i];
+    *result = acc;
+}
 #endif

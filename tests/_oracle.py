@@ -445,6 +445,50 @@ class RefAcq:
         return g[:n]
 
 
+class RefAcqFdStatus(C.Structure):
+    """ref_acqfd_status (oracle/ref_acqfd.cc)"""
+    _fields_ = [("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double), ("acq_samplestamp_samples", C.c_uint64), ("sample_counter", C.c_uint64),
+                ("consumed_total", C.c_int64), ("test_statistics", C.c_float), ("threshold", C.c_float), ("state", C.c_int32), ("active", C.c_int32),
+                ("positive_acq", C.c_int32), ("num_doppler_points", C.c_int32), ("fft_size", C.c_int32), ("well_count", C.c_int32), ("n_events", C.c_int32),
+                ("events", C.c_int32 * 8), ("acq_doppler_step", C.c_uint32)]
+
+
+class RefAcqFd:
+    """pcps_acquisition_fine_doppler_cc of the reference (oracle/ref_acqfd.cc: the reference's own block compiled unmodified into oracle/_ref),
+    filled and driven like adapters/gps_l1_ca_pcps_acquisition_fine_doppler.cc does"""
+
+    def __init__(self, fs_in, doppler_max, max_dwells, prn, blocking_on_standby=False):
+        r = ref()
+        r.ref_acqfd_new.restype = C.c_void_p
+        r.ref_acqfd_new.argtypes = [C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_uint]
+        r.ref_acqfd_free.argtypes = [C.c_void_p]
+        r.ref_acqfd_arm.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_float]
+        r.ref_acqfd_work.restype = C.c_longlong
+        r.ref_acqfd_work.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int]
+        r.ref_acqfd_get_status.argtypes = [C.c_void_p, C.POINTER(RefAcqFdStatus)]
+        self._r = r
+        r.ref_acq_fft_precision.argtypes = [C.c_int]
+        r.ref_acq_fft_precision(0)
+        self._h = r.ref_acqfd_new(int(fs_in), int(doppler_max), int(max_dwells), int(blocking_on_standby), int(prn))
+
+    def close(self):
+        if self._h:
+            self._r.ref_acqfd_free(self._h)
+            self._h = None
+
+    def arm(self, doppler_max, doppler_step, threshold):
+        self._r.ref_acqfd_arm(self._h, int(doppler_max), int(doppler_step), float(threshold))
+
+    def work(self, items, noutput_items):
+        items = np.ascontiguousarray(items, dtype=np.complex64)
+        return int(self._r.ref_acqfd_work(self._h, items.ctypes.data, items.size, int(noutput_items)))
+
+    def status(self):
+        s = RefAcqFdStatus()
+        self._r.ref_acqfd_get_status(self._h, C.byref(s))
+        return s
+
+
 # ---------------------------------------------------------------------------------------------------------------- the reference's own tracking block
 class RefTrkBlock:
     """dll_pll_veml_tracking of the reference (oracle/ref_trkblk.cc: the reference's own dll_pll_veml_tracking.cc + dll_pll_conf.cc compiled
