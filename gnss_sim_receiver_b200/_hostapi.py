@@ -34,6 +34,13 @@ class FineDopplerStatus(C.Structure):
                 ("acq_doppler_step", C.c_uint32), ("pad_", C.c_int32)]
 
 
+class CafStatus(C.Structure):
+    """gb200h_acqcaf_status"""
+    _fields_ = [("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double), ("acq_samplestamp_samples", C.c_uint64), ("sample_counter", C.c_uint64),
+                ("test_statistics", C.c_float), ("threshold", C.c_float), ("mag", C.c_float), ("input_power", C.c_float), ("state", C.c_int32), ("active", C.c_int32),
+                ("last_event", C.c_int32), ("num_doppler_bins", C.c_int32), ("fft_size", C.c_int32), ("well_count", C.c_int32), ("acq_doppler_step", C.c_uint32), ("pad_", C.c_int32)]
+
+
 class Synchro(C.Structure):
     """gb200h_synchro: every field of the GnssSynchro message (docs/protobuf/gnss_synchro.proto of the reference)"""
     _fields_ = [("system", C.c_char), ("signal", C.c_char * 3), ("prn", C.c_uint32), ("channel_id", C.c_int32),
@@ -96,6 +103,12 @@ SYMBOLS = {
     "gb200h_acq_arm": (_i, [_vp, _f]),
     "gb200h_acq_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
     "gb200h_acq_get_status": (_i, [_vp, C.POINTER(AcqStatus)]),
+    "gb200h_acqcaf_create": (_i, [C.c_char_p, C.c_char_p, C.c_uint, C.c_char_p, C.POINTER(_vp)]),
+    "gb200h_acqcaf_destroy": (None, [_vp]),
+    "gb200h_acqcaf_arm": (_i, [_vp, C.c_uint, C.c_uint, C.c_float]),
+    "gb200h_acqcaf_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
+    "gb200h_acqcaf_get_status": (_i, [_vp, C.POINTER(CafStatus)]),
+    "gb200h_acqcaf_caf_vector": (_i, [_vp, _vp, _i]),
     "gb200h_acqfd_create": (_i, [C.c_char_p, C.c_char_p, C.c_uint, C.POINTER(_vp)]),
     "gb200h_acqfd_destroy": (None, [_vp]),
     "gb200h_acqfd_arm": (_i, [_vp, C.c_uint, C.c_uint, C.c_float]),
@@ -291,6 +304,45 @@ class FineDopplerAcquisitionBlock:
         s = FineDopplerStatus()
         check(self._lib.gb200h_acqfd_get_status(self._h, C.byref(s)))
         return s
+
+
+class E5aCafAcquisitionBlock:
+    """Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200 (host/b200_e5a_noncoherent_iq_acquisition_caf.h) driven like a channel drives it"""
+
+    def __init__(self, conf_text, role, prn, signal="5X"):
+        self._lib = lib()
+        self._h = _vp()
+        check(self._lib.gb200h_acqcaf_create(conf_text.encode(), role.encode(), prn, signal.encode(), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self._lib.gb200h_acqcaf_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def arm(self, doppler_max, doppler_step, threshold):
+        check(self._lib.gb200h_acqcaf_arm(self._h, int(doppler_max), int(doppler_step), float(threshold)))
+
+    def work(self, items, chunk):
+        items = np.ascontiguousarray(items, dtype=np.complex64)
+        return check(self._lib.gb200h_acqcaf_work(self._h, items.ctypes.data, items.size, int(chunk)))
+
+    def status(self):
+        s = CafStatus()
+        check(self._lib.gb200h_acqcaf_get_status(self._h, C.byref(s)))
+        return s
+
+    def caf_vector(self):
+        n = self._lib.gb200h_acqcaf_caf_vector(self._h, None, 0)
+        out = np.zeros(n, np.float32)
+        if n:
+            self._lib.gb200h_acqcaf_caf_vector(self._h, out.ctypes.data, n)
+        return out
 
 
 class ChannelManager:

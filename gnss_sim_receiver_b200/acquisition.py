@@ -117,6 +117,21 @@ class AcquisitionEngine:
         check(self._lib.gb200_acq_fft(self._h, x.ctypes.data, out.ctypes.data, int(inverse)))
         return out
 
+    def grid_pair_max(self, slot_a, slot_b):
+        """per Doppler bin: maximum / first index of kept grid row slot_a[bin] + row slot_b[bin] (slot_b < 0: row slot_a alone)"""
+        a = np.ascontiguousarray(slot_a, dtype=np.int32)
+        b = np.ascontiguousarray(slot_b, dtype=np.int32)
+        assert len(a) == len(b) == self.num_doppler_bins
+        v, i = np.zeros(len(a), np.float32), np.zeros(len(a), np.int32)
+        check(self._lib.gb200_acq_grid_pair_max(self._h, a.ctypes.data, b.ctypes.data, v.ctypes.data, i.ctypes.data))
+        return v, i
+
+    def grid_probe(self, slot, bin_, index):
+        s, b, i = (np.ascontiguousarray(x, dtype=np.int32) for x in (slot, bin_, index))
+        out = np.zeros(len(s), np.float32)
+        check(self._lib.gb200_acq_grid_probe(self._h, len(s), s.ctypes.data, b.ctypes.data, i.ctypes.data, out.ctypes.data))
+        return out
+
     def spectrum_peak(self, x, rep, pad_factor=8):
         """estimate_Doppler's search (pcps_acquisition_fine_doppler_cc.cc:338-374): (index of the first maximum, value) of
         |FFT(x * rep repeated, zero-padded to pad_factor * len(x))|^2; len(x) a multiple of the engine's fft_size"""

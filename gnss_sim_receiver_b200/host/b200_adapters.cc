@@ -342,6 +342,116 @@ void GpsL1CaPcpsAcquisitionFineDopplerB200::set_local_code()
     acquisition_cc_->set_local_code(code_.data());
 }
 
+// adapters/galileo_e5a_noncoherent_iq_acquisition_caf.cc:40-128
+GalileoE5aNoncoherentIQAcquisitionCafB200::GalileoE5aNoncoherentIQAcquisitionCafB200(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
+    : configuration_(c),
+      role_(role),
+      item_size_(sizeof(gr_complex)),
+      Zero_padding(c->property(role + ".Zero_padding", 0)),
+      CAF_window_hz_(c->property(role + ".CAF_window_hz", 0)),
+      doppler_max_(static_cast<unsigned int>(c->property(role + ".doppler_max", 5000))),
+      sampled_ms_(static_cast<unsigned int>(c->property(role + ".coherent_integration_time_ms", 1))),
+      max_dwells_(static_cast<unsigned int>(c->property(role + ".max_dwells", 1))),
+      bit_transition_flag_(c->property(role + ".bit_transition_flag", false))
+{
+    item_type_ = c->property(role_ + ".item_type", std::string("gr_complex"));
+    const int64_t fs_in_deprecated = c->property("GNSS-SDR.internal_fs_hz", static_cast<int64_t>(32000000));
+    fs_in_ = c->property("GNSS-SDR.internal_fs_sps", fs_in_deprecated);
+    if (sampled_ms_ > 3)
+        {
+            sampled_ms_ = 3;
+            std::cout << "Too high coherent integration time. Changing to 3ms\n";
+        }
+    if (Zero_padding > 0)
+        {
+            sampled_ms_ = 2;
+            std::cout << "Zero padding activated. Changing to 1ms code + 1ms zero padding\n";
+        }
+    code_length_ = static_cast<int>(std::round(static_cast<double>(fs_in_) / 10230000.0 * 10230.0));  // GALILEO_E5A_CODE_CHIP_RATE_CPS, GALILEO_E5A_CODE_LENGTH_CHIPS
+    vector_length_ = static_cast<unsigned int>(code_length_) * sampled_ms_;
+    codeI_ = std::vector<std::complex<float>>(vector_length_);
+    codeQ_ = std::vector<std::complex<float>>(vector_length_);
+    const std::string sig_ = c->property("Channel.signal", std::string("5X"));
+    if (sig_.size() >= 2 && sig_.at(0) == '5' && sig_.at(1) == 'X') both_signal_components = true;
+    if (item_type_ != "gr_complex") throw std::invalid_argument(item_type_ + " unknown acquisition item type (Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200 takes gr_complex)");
+    acquisition_cc_ = std::make_shared<b200_e5a_noncoherent_iq_acquisition_caf>(sampled_ms_, max_dwells_, doppler_max_, fs_in_, code_length_, code_length_, bit_transition_flag_,
+        both_signal_components, CAF_window_hz_, Zero_padding, c->property(role + ".device", 0));
+    if (in > 1) std::cerr << "This implementation only supports one input stream\n";
+    if (out > 0) std::cerr << "This implementation does not provide an output stream\n";
+}
+void GalileoE5aNoncoherentIQAcquisitionCafB200::connect(gr::top_block_sptr top_block)
+{
+    if (top_block) { /* nothing to connect internally */ }
+}
+void GalileoE5aNoncoherentIQAcquisitionCafB200::disconnect(gr::top_block_sptr top_block)
+{
+    if (top_block) { /* nothing to disconnect */ }
+}
+void GalileoE5aNoncoherentIQAcquisitionCafB200::stop_acquisition()
+{
+    acquisition_cc_->set_state(0);
+    acquisition_cc_->set_active(false);
+}
+// :134-154
+void GalileoE5aNoncoherentIQAcquisitionCafB200::set_threshold(float threshold)
+{
+    float pfa = configuration_->property(role_ + std::to_string(channel_) + ".pfa", static_cast<float>(0.0));
+    if (pfa == 0.0) pfa = configuration_->property(role_ + ".pfa", static_cast<float>(0.0));
+    threshold_ = pfa == 0.0 ? threshold : calculate_threshold(pfa);
+    acquisition_cc_->set_threshold(threshold_);
+}
+// :272-289: the (1 - pfa)^(1 / cells) quantile of an exponential distribution of rate vector_length (Boost there: -log1p(-p) / lambda)
+float GalileoE5aNoncoherentIQAcquisitionCafB200::calculate_threshold(float pfa) const
+{
+    unsigned int frequency_bins = 0;
+    for (int doppler = static_cast<int>(-doppler_max_); doppler <= static_cast<int>(doppler_max_); doppler += static_cast<int>(doppler_step_)) frequency_bins++;
+    const unsigned int ncells = vector_length_ * frequency_bins;
+    const double exponent = 1 / static_cast<double>(ncells);
+    const double val = std::pow(1.0 - pfa, exponent);
+    const auto lambda = static_cast<double>(vector_length_);
+    return static_cast<float>(-std::log1p(-val) / lambda);
+}
+void GalileoE5aNoncoherentIQAcquisitionCafB200::set_doppler_max(unsigned int doppler_max)
+{
+    doppler_max_ = doppler_max;
+    acquisition_cc_->set_doppler_max(doppler_max_);
+}
+void GalileoE5aNoncoherentIQAcquisitionCafB200::set_doppler_step(unsigned int doppler_step)
+{
+    doppler_step_ = doppler_step;
+    acquisition_cc_->set_doppler_step(doppler_step_);
+}
+void GalileoE5aNoncoherentIQAcquisitionCafB200::set_gnss_synchro(Gnss_Synchro* gnss_synchro)
+{
+    gnss_synchro_ = gnss_synchro;
+    acquisition_cc_->set_gnss_synchro(gnss_synchro_);
+}
+void GalileoE5aNoncoherentIQAcquisitionCafB200::set_channel(unsigned int channel)
+{
+    channel_ = channel;
+    acquisition_cc_->set_channel(channel_);
+}
+// :211-261
+void GalileoE5aNoncoherentIQAcquisitionCafB200::set_local_code()
+{
+    std::vector<std::complex<float>> codeI(static_cast<size_t>(code_length_)), codeQ(static_cast<size_t>(code_length_));
+    const bool x = gnss_synchro_->Signal[0] == '5' && gnss_synchro_->Signal[1] == 'X';
+    if (x)
+        {
+            galileo_e5_a_code_gen_complex_sampled(codeI.data(), gnss_synchro_->PRN, "5I", static_cast<int32_t>(fs_in_), 0);
+            galileo_e5_a_code_gen_complex_sampled(codeQ.data(), gnss_synchro_->PRN, "5Q", static_cast<int32_t>(fs_in_), 0);
+        }
+    else
+        galileo_e5_a_code_gen_complex_sampled(codeI.data(), gnss_synchro_->PRN, "5X", static_cast<int32_t>(fs_in_), 0);
+    const unsigned int copies = Zero_padding == 0 ? sampled_ms_ : 1U;  // zero padding: 1 ms of code, the rest stays zero
+    for (unsigned int i = 0; i < copies; i++)
+        {
+            std::copy_n(codeI.data(), code_length_, codeI_.data() + static_cast<size_t>(i) * code_length_);
+            if (x) std::copy_n(codeQ.data(), code_length_, codeQ_.data() + static_cast<size_t>(i) * code_length_);
+        }
+    acquisition_cc_->set_local_code(codeI_.data(), codeQ_.data());
+}
+
 std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
 {
     const std::string impl = c->property(role + ".implementation", std::string("Pass_Through"));
@@ -349,6 +459,7 @@ std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const ConfigurationInterfa
     if (impl == "Galileo_E1_PCPS_Ambiguous_Acquisition_B200") return std::make_unique<GalileoE1PcpsAmbiguousAcquisitionB200>(c, role, in, out);
     if (impl == "GPS_L5i_PCPS_Acquisition_B200") return std::make_unique<GpsL5iPcpsAcquisitionB200>(c, role, in, out);
     if (impl == "Galileo_E5a_Pcps_Acquisition_B200") return std::make_unique<GalileoE5aPcpsAcquisitionB200>(c, role, in, out);
+    if (impl == "Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200") return std::make_unique<GalileoE5aNoncoherentIQAcquisitionCafB200>(c, role, in, out);
     if (impl == "GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200") return std::make_unique<GpsL1CaPcpsAcquisitionFineDopplerB200>(c, role, in, out);
     return nullptr;
 }

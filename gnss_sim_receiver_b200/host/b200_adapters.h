@@ -10,6 +10,7 @@
 #include "b200_dll_pll_veml_tracking.h"
 #include "b200_pcps_acquisition.h"
 #include "b200_pcps_acquisition_fine_doppler.h"
+#include "b200_e5a_noncoherent_iq_acquisition_caf.h"
 #include "gnss_sdr_compat.h"
 #include <memory>
 #include <string>
@@ -223,6 +224,52 @@ private:
     int doppler_max_, max_dwells_;
     unsigned int vector_length_{0}, channel_{0}, doppler_step_{0}, sampled_ms_;
     bool dump_;
+};
+
+// adapters/galileo_e5a_noncoherent_iq_acquisition_caf.{h:50-200,cc:40-326}: `Galileo_E5a_Noncoherent_IQ_Acquisition_CAF`; gr_complex items only;
+// keys doppler_max (5000), coherent_integration_time_ms (1, at most 3), max_dwells (1), bit_transition_flag, CAF_window_hz (0 = off),
+// Zero_padding (> 0: 1 ms of code + 1 ms of zeros), pfa, and `Channel.signal` ("5X": both components, the default)
+class GalileoE5aNoncoherentIQAcquisitionCafB200 : public AcquisitionInterface
+{
+public:
+    GalileoE5aNoncoherentIQAcquisitionCafB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+    std::string role() override { return role_; }
+    std::string implementation() override { return "Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200"; }
+    size_t item_size() override { return item_size_; }
+    void connect(gr::top_block_sptr top_block) override;
+    void disconnect(gr::top_block_sptr top_block) override;
+    gr::basic_block_sptr get_left_block() override { return acquisition_cc_; }
+    gr::basic_block_sptr get_right_block() override { return acquisition_cc_; }
+    void set_gnss_synchro(Gnss_Synchro* p_gnss_synchro) override;
+    void set_channel(unsigned int channel) override;
+    void set_channel_fsm(std::weak_ptr<ChannelFsm> channel_fsm) override { channel_fsm_ = std::move(channel_fsm); }
+    void set_threshold(float threshold) override;
+    void set_doppler_max(unsigned int doppler_max) override;
+    void set_doppler_step(unsigned int doppler_step) override;
+    void init() override { acquisition_cc_->init(); }
+    void set_local_code() override;
+    void set_state(int state) override { acquisition_cc_->set_state(state); }
+    signed int mag() override { return static_cast<signed int>(acquisition_cc_->mag()); }
+    void reset() override { acquisition_cc_->set_active(true); }
+    void stop_acquisition() override;
+    void set_resampler_latency(uint32_t latency_samples __attribute__((unused))) override {}
+    std::shared_ptr<b200_e5a_noncoherent_iq_acquisition_caf> block() { return acquisition_cc_; }
+    float threshold() const { return threshold_; }
+
+private:
+    float calculate_threshold(float pfa) const;
+    const ConfigurationInterface* configuration_;
+    std::shared_ptr<b200_e5a_noncoherent_iq_acquisition_caf> acquisition_cc_;
+    std::weak_ptr<ChannelFsm> channel_fsm_;
+    std::vector<std::complex<float>> codeI_, codeQ_;
+    std::string role_, item_type_;
+    Gnss_Synchro* gnss_synchro_{nullptr};
+    int64_t fs_in_;
+    size_t item_size_;
+    float threshold_{0.0F};
+    int Zero_padding, CAF_window_hz_, code_length_{0};
+    unsigned int vector_length_{0}, channel_{0}, doppler_max_, doppler_step_{0}, sampled_ms_, max_dwells_;
+    bool bit_transition_flag_, both_signal_components{false};
 };
 
 // The `.implementation` strings this tree serves; nullptr for any other string (the caller falls through to the

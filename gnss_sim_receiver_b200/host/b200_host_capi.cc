@@ -579,6 +579,14 @@ struct gb200h_acq
     int last_event{0};
 };
 
+struct gb200h_acqcaf
+{
+    B200Configuration cfg;
+    std::unique_ptr<GalileoE5aNoncoherentIQAcquisitionCafB200> adapter;
+    Gnss_Synchro synchro;
+    int last_event{0};
+};
+
 struct gb200h_acqfd
 {
     B200Configuration cfg;
@@ -588,6 +596,113 @@ struct gb200h_acqfd
 };
 
 extern "C" {
+
+int gb200h_acqcaf_create(const char* conf_text, const char* role, unsigned prn, const char* signal, gb200h_acqcaf** out)
+{
+    try
+        {
+            auto a = std::make_unique<gb200h_acqcaf>();
+            a->cfg.load_string(conf_text);
+            auto blk = GetB200AcqBlock(&a->cfg, role, 1, 0);
+            auto* caf = dynamic_cast<GalileoE5aNoncoherentIQAcquisitionCafB200*>(blk.get());
+            if (!caf) throw std::runtime_error(std::string(role) + ".implementation is not Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200");
+            blk.release();
+            a->adapter.reset(caf);
+            a->synchro.System = 'E';
+            std::memset(a->synchro.Signal, 0, 3);
+            a->synchro.Signal[0] = signal[0];
+            a->synchro.Signal[1] = signal[0] ? signal[1] : '\0';
+            a->synchro.PRN = prn;
+            a->adapter->set_gnss_synchro(&a->synchro);
+            a->adapter->set_channel(0);
+            gb200h_acqcaf* raw = a.get();
+            a->adapter->block()->set_event_sink([raw](int ev) { raw->last_event = ev; });
+            *out = a.release();
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+void gb200h_acqcaf_destroy(gb200h_acqcaf* a) { delete a; }
+
+int gb200h_acqcaf_arm(gb200h_acqcaf* a, unsigned doppler_max, unsigned doppler_step, float threshold)
+{
+    try
+        {
+            auto& ad = *a->adapter;
+            ad.set_doppler_max(doppler_max);
+            ad.set_doppler_step(doppler_step);
+            ad.set_threshold(threshold);
+            ad.init();
+            ad.set_local_code();
+            a->last_event = 0;
+            ad.set_state(1);
+            ad.reset();
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int64_t gb200h_acqcaf_work(gb200h_acqcaf* a, const void* items, int64_t n_items, int chunk)
+{
+    try
+        {
+            auto& blk = *a->adapter->block();
+            const auto* in = static_cast<const std::complex<float>*>(items);
+            int64_t pos = 0;
+            int idle = 0;
+            while (pos < n_items && idle < 3)
+                {
+                    const int before = blk.state();
+                    const int c = blk.general_work(in + pos, static_cast<int>(std::min<int64_t>(n_items - pos, chunk)));
+                    pos += c;
+                    if (blk.state() == 0 && !blk.active()) break;
+                    idle = (c == 0 && blk.state() == before) ? idle + 1 : 0;
+                }
+            return pos;
+        }
+    catch (const std::exception& e)
+        {
+            fail(e);
+            return -1;
+        }
+}
+
+int gb200h_acqcaf_get_status(gb200h_acqcaf* a, gb200h_acqcaf_status* s)
+{
+    const auto& blk = *a->adapter->block();
+    std::memset(s, 0, sizeof(*s));
+    s->acq_delay_samples = a->synchro.Acq_delay_samples;
+    s->acq_doppler_hz = a->synchro.Acq_doppler_hz;
+    s->acq_samplestamp_samples = a->synchro.Acq_samplestamp_samples;
+    s->acq_doppler_step = a->synchro.Acq_doppler_step;
+    s->sample_counter = blk.sample_counter();
+    s->test_statistics = blk.test_statistics();
+    s->threshold = blk.threshold();
+    s->mag = blk.mag_f();
+    s->input_power = blk.input_power();
+    s->state = blk.state();
+    s->active = blk.active() ? 1 : 0;
+    s->last_event = a->last_event;
+    s->num_doppler_bins = blk.num_doppler_bins();
+    s->fft_size = blk.fft_size();
+    s->well_count = blk.well_count();
+    return 0;
+}
+
+int gb200h_acqcaf_caf_vector(gb200h_acqcaf* a, float* dst, int max_bins)
+{
+    const auto& v = a->adapter->block()->caf_vector();
+    const int n = std::min<int>(max_bins, static_cast<int>(v.size()));
+    if (n > 0 && dst) std::copy(v.begin(), v.begin() + n, dst);
+    return static_cast<int>(v.size());
+}
 
 int gb200h_acqfd_create(const char* conf_text, const char* role, unsigned prn, gb200h_acqfd** out)
 {

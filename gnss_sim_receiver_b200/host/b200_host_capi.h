@@ -122,6 +122,29 @@ int gb200h_acqfd_arm(gb200h_acqfd* a, unsigned doppler_max, unsigned doppler_ste
 int64_t gb200h_acqfd_work(gb200h_acqfd* a, const void* items, int64_t n_items, int noutput_items);
 int gb200h_acqfd_get_status(gb200h_acqfd* a, gb200h_acqfd_status* s);
 
+/* ---- Galileo E5a non-coherent I/Q acquisition with CAF (Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200; b200_e5a_noncoherent_iq_acquisition_caf.h) */
+typedef struct gb200h_acqcaf gb200h_acqcaf;
+typedef struct
+{
+    double acq_delay_samples, acq_doppler_hz;
+    uint64_t acq_samplestamp_samples, sample_counter;
+    float test_statistics, threshold, mag, input_power;
+    int32_t state, active, last_event, num_doppler_bins, fft_size, well_count;
+    uint32_t acq_doppler_step;
+    int32_t pad_;
+} gb200h_acqcaf_status;
+/* signal: the channel's Gnss_Synchro signal ("5X": I and Q replicas, else one "5X"-composed replica, adapters/...caf.cc:218-233) */
+int gb200h_acqcaf_create(const char* conf_text, const char* role, unsigned prn, const char* signal, gb200h_acqcaf** out);
+void gb200h_acqcaf_destroy(gb200h_acqcaf* a);
+/* set_doppler_max, set_doppler_step, set_threshold (a configured pfa wins), init, set_local_code, set_state(1), set_active(true) */
+int gb200h_acqcaf_arm(gb200h_acqcaf* a, unsigned doppler_max, unsigned doppler_step, float threshold);
+/* plays the scheduler: general_work with at most `chunk` items per call until the block has raised its event and gone idle or the buffer
+ * is used up; returns the items consumed, -1 on error */
+int64_t gb200h_acqcaf_work(gb200h_acqcaf* a, const void* items, int64_t n_items, int chunk);
+int gb200h_acqcaf_get_status(gb200h_acqcaf* a, gb200h_acqcaf_status* s);
+/* the filtered CAF vector of the last search (num_doppler_bins floats; 0 returned when CAF_window_hz = 0) */
+int gb200h_acqcaf_caf_vector(gb200h_acqcaf* a, float* dst, int max_bins);
+
 /* MAT level-5 writer used by the acquisition dump (b200_mat_writer.h): one file with a single matrix and one scalar of each class */
 int gb200h_mat_write_sample(const char* filename, const float* grid, int rows, int cols, int32_t i32, uint32_t u32, uint64_t u64, float f32);
 

@@ -388,6 +388,14 @@ int gb200_acq_read_grid(gb200_acq* h, int slot, float* grid_host);
 int gb200_acq_read_cells(gb200_acq* h, int n_slots, float* vmax, int32_t* imax, float* sum);
 /* forward transform of one fft_size block through the engine's FFT (test hook: natural-order output) */
 int gb200_acq_fft(gb200_acq* h, const gb200_cf32* in_host, gb200_cf32* out_host, int inverse);
+/* Non-coherent combination of kept grid rows, per Doppler bin — galileo_e5a_noncoherentIQ_acquisition_caf_cc's "d_magnitudeIA[i] += d_magnitudeQA[i]"
+ * then volk_gnsssdr_32f_index_max_32u (galileo_e5a_noncoherent_iq_acquisition_caf_cc.cc:464-467,475-478,494-497,505-508,525-531): for every bin
+ * of the last run, row slot_a[bin] + row slot_b[bin] of the kept grid (slot_b[bin] < 0: row slot_a[bin] alone), its maximum and the first
+ * index of it.  slot_a / slot_b / vmax / imax: n_bins entries each, host memory.  Needs gb200_acq_keep_grid(h, 1). */
+int gb200_acq_grid_pair_max(gb200_acq* h, const int32_t* slot_a, const int32_t* slot_b, float* vmax, int32_t* imax);
+/* n single values of the kept grid: value_out[k] = grid[slot[k]][bin[k]][index[k]] (the CAF block reads d_magnitudeIB at the index of
+ * another component's maximum, :435) */
+int gb200_acq_grid_probe(gb200_acq* h, int n, const int32_t* slot, const int32_t* bin, const int32_t* index, float* value_out);
 /* Fine Doppler estimate — pcps_acquisition_fine_doppler_cc::estimate_Doppler (pcps_acquisition_fine_doppler_cc.cc:338-402): the n_x
  * buffered samples x (10 code periods) times the delay-aligned replica rep (one period, repeated: :357-366), transformed zero-padded to
  * pad_factor * n_x points (:340-345,:368), |.|^2 (:371), index of the FIRST maximum (volk_gnsssdr_32f_index_max_32u, :374) in

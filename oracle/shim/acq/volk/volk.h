@@ -30,6 +30,11 @@ inline void volk_32f_x2_add_32f(float* c, const float* a, const float* b, unsign
 {
     for (unsigned int i = 0; i < n; i++) c[i] = a[i] + b[i];
 }
+// (galileo_e5a_noncoherentIQ_acquisition_caf_cc::set_local_code: the sign flip of the B replicas; VOLK's generic loop, a full complex product)
+inline void volk_32fc_s32fc_multiply_32fc(lv_32fc_t* c, const lv_32fc_t* a, const lv_32fc_t s, unsigned int n)
+{
+    for (unsigned int i = 0; i < n; i++) c[i] = a[i] * s;
+}
 // (pcps_acquisition_fine_doppler_cc::estimate_input_power only, which general_work never calls: VOLK's generic running sum)
 inline void volk_32f_accumulator_s32f(float* result, const float* a, unsigned int n)
 {

@@ -489,6 +489,60 @@ class RefAcqFd:
         return s
 
 
+class RefAcqCafStatus(C.Structure):
+    """ref_acqcaf_status (oracle/ref_acqcaf.cc)"""
+    _fields_ = [("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double), ("acq_samplestamp_samples", C.c_uint64), ("sample_counter", C.c_uint64),
+                ("consumed_total", C.c_int64), ("test_statistics", C.c_float), ("threshold", C.c_float), ("mag", C.c_float), ("input_power", C.c_float),
+                ("state", C.c_int32), ("active", C.c_int32), ("num_doppler_bins", C.c_int32), ("fft_size", C.c_int32), ("well_count", C.c_int32), ("n_events", C.c_int32),
+                ("events", C.c_int32 * 8), ("acq_doppler_step", C.c_uint32)]
+
+
+class RefAcqCaf:
+    """galileo_e5a_noncoherentIQ_acquisition_caf_cc of the reference (oracle/ref_acqcaf.cc: the reference's own block compiled unmodified into
+    oracle/_ref), made and driven like adapters/galileo_e5a_noncoherent_iq_acquisition_caf.cc does"""
+
+    def __init__(self, fs_in, sampled_ms, max_dwells, doppler_max, prn, signal="5X", channel_signal="5X", bit_transition=False, caf_window_hz=0, zero_padding=0):
+        r = ref()
+        r.ref_acqcaf_new.restype = C.c_void_p
+        r.ref_acqcaf_new.argtypes = [C.c_longlong, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_uint, C.c_char_p, C.c_char_p]
+        r.ref_acqcaf_free.argtypes = [C.c_void_p]
+        r.ref_acqcaf_arm.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_float]
+        r.ref_acqcaf_work.restype = C.c_longlong
+        r.ref_acqcaf_work.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int]
+        r.ref_acqcaf_get_status.argtypes = [C.c_void_p, C.POINTER(RefAcqCafStatus)]
+        r.ref_acqcaf_caf_vector.restype = C.c_int
+        r.ref_acqcaf_caf_vector.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        self._r = r
+        r.ref_acq_fft_precision.argtypes = [C.c_int]
+        r.ref_acq_fft_precision(0)
+        self._h = r.ref_acqcaf_new(int(fs_in), int(sampled_ms), int(max_dwells), int(doppler_max), int(bit_transition), int(caf_window_hz), int(zero_padding), int(prn),
+                                   signal.encode(), channel_signal.encode())
+
+    def close(self):
+        if self._h:
+            self._r.ref_acqcaf_free(self._h)
+            self._h = None
+
+    def arm(self, doppler_max, doppler_step, threshold):
+        self._r.ref_acqcaf_arm(self._h, int(doppler_max), int(doppler_step), float(threshold))
+
+    def work(self, items, chunk):
+        items = np.ascontiguousarray(items, dtype=np.complex64)
+        return int(self._r.ref_acqcaf_work(self._h, items.ctypes.data, items.size, int(chunk)))
+
+    def status(self):
+        s = RefAcqCafStatus()
+        self._r.ref_acqcaf_get_status(self._h, C.byref(s))
+        return s
+
+    def caf_vector(self):
+        n = self._r.ref_acqcaf_caf_vector(self._h, None, 0)
+        out = np.zeros(n, np.float32)
+        if n:
+            self._r.ref_acqcaf_caf_vector(self._h, out.ctypes.data, n)
+        return out
+
+
 # ---------------------------------------------------------------------------------------------------------------- the reference's own tracking block
 class RefTrkBlock:
     """dll_pll_veml_tracking of the reference (oracle/ref_trkblk.cc: the reference's own dll_pll_veml_tracking.cc + dll_pll_conf.cc compiled
