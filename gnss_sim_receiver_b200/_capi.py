@@ -122,6 +122,8 @@ SYMBOLS = {
     "gb200_acq_read_grid": (C.c_int, [_vp, C.c_int, _vp]),
     "gb200_acq_read_cells": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp]),
     "gb200_acq_fft": (C.c_int, [_vp, _vp, _vp, C.c_int]),
+    "gb200_acq_set_input_folding": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "gb200_acq_folded_candidates": (C.c_int, [_vp, C.c_int, C.c_int, _vp, C.c_int, C.c_int, _vp]),
     "gb200_acq_grid_pair_max": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "gb200_acq_grid_probe": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp]),
     "gb200_acq_spectrum_peak": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int, C.c_int, _vp, _vp]),

@@ -41,6 +41,14 @@ class CafStatus(C.Structure):
                 ("last_event", C.c_int32), ("num_doppler_bins", C.c_int32), ("fft_size", C.c_int32), ("well_count", C.c_int32), ("acq_doppler_step", C.c_uint32), ("pad_", C.c_int32)]
 
 
+class QuickSyncStatus(C.Structure):
+    """gb200h_acqqs_status"""
+    _fields_ = [("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double), ("acq_samplestamp_samples", C.c_uint64), ("sample_counter", C.c_uint64),
+                ("test_statistics", C.c_float), ("threshold", C.c_float), ("mag", C.c_float), ("input_power", C.c_float), ("state", C.c_int32), ("active", C.c_int32),
+                ("last_event", C.c_int32), ("num_doppler_bins", C.c_int32), ("fft_size", C.c_int32), ("well_count", C.c_int32), ("item_length", C.c_int32),
+                ("folding_factor", C.c_int32), ("sampled_ms", C.c_int32), ("acq_doppler_step", C.c_uint32)]
+
+
 class Synchro(C.Structure):
     """gb200h_synchro: every field of the GnssSynchro message (docs/protobuf/gnss_synchro.proto of the reference)"""
     _fields_ = [("system", C.c_char), ("signal", C.c_char * 3), ("prn", C.c_uint32), ("channel_id", C.c_int32),
@@ -109,6 +117,11 @@ SYMBOLS = {
     "gb200h_acqcaf_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
     "gb200h_acqcaf_get_status": (_i, [_vp, C.POINTER(CafStatus)]),
     "gb200h_acqcaf_caf_vector": (_i, [_vp, _vp, _i]),
+    "gb200h_acqqs_create": (_i, [C.c_char_p, C.c_char_p, C.c_uint, C.POINTER(_vp)]),
+    "gb200h_acqqs_destroy": (None, [_vp]),
+    "gb200h_acqqs_arm": (_i, [_vp, C.c_uint, C.c_uint, C.c_float]),
+    "gb200h_acqqs_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
+    "gb200h_acqqs_get_status": (_i, [_vp, C.POINTER(QuickSyncStatus)]),
     "gb200h_acqfd_create": (_i, [C.c_char_p, C.c_char_p, C.c_uint, C.POINTER(_vp)]),
     "gb200h_acqfd_destroy": (None, [_vp]),
     "gb200h_acqfd_arm": (_i, [_vp, C.c_uint, C.c_uint, C.c_float]),
@@ -343,6 +356,39 @@ class E5aCafAcquisitionBlock:
         if n:
             self._lib.gb200h_acqcaf_caf_vector(self._h, out.ctypes.data, n)
         return out
+
+
+class QuickSyncAcquisitionBlock:
+    """GPS_L1_CA_PCPS_QuickSync_Acquisition_B200 (host/b200_pcps_quicksync_acquisition.h) driven like a channel drives it"""
+
+    def __init__(self, conf_text, role, prn):
+        self._lib = lib()
+        self._h = _vp()
+        check(self._lib.gb200h_acqqs_create(conf_text.encode(), role.encode(), prn, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self._lib.gb200h_acqqs_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def arm(self, doppler_max, doppler_step, threshold):
+        check(self._lib.gb200h_acqqs_arm(self._h, int(doppler_max), int(doppler_step), float(threshold)))
+
+    def work(self, samples, max_items):
+        """returns the vector ITEMS consumed"""
+        samples = np.ascontiguousarray(samples, dtype=np.complex64)
+        return check(self._lib.gb200h_acqqs_work(self._h, samples.ctypes.data, samples.size, int(max_items)))
+
+    def status(self):
+        s = QuickSyncStatus()
+        check(self._lib.gb200h_acqqs_get_status(self._h, C.byref(s)))
+        return s
 
 
 class ChannelManager:

@@ -117,6 +117,17 @@ class AcquisitionEngine:
         check(self._lib.gb200_acq_fft(self._h, x.ctypes.data, out.ctypes.data, int(inverse)))
         return out
 
+    def set_input_folding(self, chunks, block_len):
+        """QuickSync's folded input: every run reads block_len samples, wipes them off over the whole block and adds the first `chunks` pieces of
+        fft_size samples into one transform input per Doppler bin (0 chunks: off)"""
+        check(self._lib.gb200_acq_set_input_folding(self._h, int(chunks), int(block_len)))
+
+    def folded_candidates(self, bin_, index, code, n_candidates):
+        code = np.ascontiguousarray(code, dtype=np.complex64)
+        out = np.zeros(n_candidates, np.complex64)
+        check(self._lib.gb200_acq_folded_candidates(self._h, int(bin_), int(index), code.ctypes.data, len(code), int(n_candidates), out.ctypes.data))
+        return out
+
     def grid_pair_max(self, slot_a, slot_b):
         """per Doppler bin: maximum / first index of kept grid row slot_a[bin] + row slot_b[bin] (slot_b < 0: row slot_a alone)"""
         a = np.ascontiguousarray(slot_a, dtype=np.int32)

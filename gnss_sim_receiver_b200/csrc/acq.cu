@@ -55,6 +55,12 @@ struct gb200_acq
     gb200_acq_result* h_results{nullptr};
     std::vector<char> code_set;
     std::vector<int> dwells_done;  // per slot: dwells accumulated in the grid
+    // folded input (QuickSync, pcps_quicksync_acquisition_cc.cc:296-318): a block of fold_len samples is wiped off over its whole length and
+    // its first fold_chunks * fft_size samples are added up chunk by chunk into ONE fft_size-point transform input per Doppler bin
+    int fold_chunks{0}, fold_len{0}, fold_bins{0};
+    float2* d_fold_iq{nullptr};   // [fold_len] the block as uploaded
+    float* d_fold_phase{nullptr};  // [n_bins][fold_len] fp32 accumulated wipe-off phases over the whole block
+    float2* d_fold{nullptr};       // [n_bins][N] folded, wiped input of every bin
     // last run (replay)
     std::vector<int> last_slots;
     int last_dwell{0};

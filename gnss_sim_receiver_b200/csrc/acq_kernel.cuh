@@ -189,6 +189,60 @@ __global__ void __launch_bounds__(256) acq_gstage_fwd_kernel(FftPlan pl, const v
         }
 }
 
+// Folded, wiped input of every Doppler bin — pcps_quicksync_acquisition_cc.cc:304-318: the block times the bin's wipe-off
+// (volk_32fc_x2_multiply_32fc: four products, one difference, one sum, each rounded), then chunk i of M samples added to the transform
+// input for i = 0 ... K-1 in that order.  grid = (ceil(M / 256), bins); out[bin][out_stride]; phase: [bins][len] accumulated fp32 phases.
+__global__ void acq_fold_kernel(const float2* __restrict__ iq, const float* __restrict__ phase, int len, int M, int K, float2* __restrict__ out, int out_stride)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= M) return;
+    const float* prow = phase + (size_t)blockIdx.y * len;
+    float2 acc = make_float2(0.0f, 0.0f);
+    for (int i = 0; i < K; i++)
+        {
+            const int n = i * M + k;
+            const float2 x = iq[n];
+            float s, c;
+            sincosf(__ldg(prow + n), &s, &c);
+            acc.x = __fadd_rn(acc.x, __fsub_rn(__fmul_rn(x.x, c), __fmul_rn(x.y, s)));
+            acc.y = __fadd_rn(acc.y, __fadd_rn(__fmul_rn(x.x, s), __fmul_rn(x.y, c)));
+        }
+    out[(size_t)blockIdx.y * out_stride + k] = acc;  // (a padded transform's tail behind M stays zero)
+}
+
+// Candidate correlations that resolve the folding ambiguity (:337-349): acc[i] = sum_{j < n_code} iq[d_i + j] * w_bin[d_i + j] * code[j],
+// d_i = index + i * M.  grid = (n_candidates); the sum is a tree, not the reference's left-to-right loop (only the largest |acc|^2 is used).
+__global__ void acq_fold_candidates_kernel(const float2* __restrict__ iq, const float* __restrict__ prow, int M, int index, const float2* __restrict__ code, int n_code,
+    float2* __restrict__ acc_out)
+{
+    __shared__ float2 s_acc[32];
+    const int d = index + (int)blockIdx.x * M;
+    float2 acc = make_float2(0.0f, 0.0f);
+    for (int j = threadIdx.x; j < n_code; j += blockDim.x)
+        {
+            const float2 x = iq[d + j];
+            float s, c;
+            sincosf(__ldg(prow + d + j), &s, &c);
+            const float2 t = make_float2(__fsub_rn(__fmul_rn(x.x, c), __fmul_rn(x.y, s)), __fadd_rn(__fmul_rn(x.x, s), __fmul_rn(x.y, c)));
+            const float2 cd = code[j];
+            acc.x += __fsub_rn(__fmul_rn(t.x, cd.x), __fmul_rn(t.y, cd.y));
+            acc.y += __fadd_rn(__fmul_rn(t.x, cd.y), __fmul_rn(t.y, cd.x));
+        }
+    for (int o = 16; o > 0; o >>= 1)
+        {
+            acc.x += __shfl_down_sync(0xffffffffu, acc.x, o);
+            acc.y += __shfl_down_sync(0xffffffffu, acc.y, o);
+        }
+    if ((threadIdx.x & 31) == 0) s_acc[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0)
+        {
+            float2 t = make_float2(0.0f, 0.0f);
+            for (int w = 0; w < (int)(blockDim.x + 31) / 32; w++) t.x += s_acc[w].x, t.y += s_acc[w].y;
+            acc_out[blockIdx.x] = t;
+        }
+}
+
 // block-wide reduction of (max value, first index of the maximum, sum); result valid on thread 0
 __device__ __forceinline__ void acq_block_reduce(float& v, int& idx, float& sum)
 {

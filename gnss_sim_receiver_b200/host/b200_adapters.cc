@@ -452,6 +452,98 @@ void GalileoE5aNoncoherentIQAcquisitionCafB200::set_local_code()
     acquisition_cc_->set_local_code(codeI_.data(), codeQ_.data());
 }
 
+// adapters/gps_l1_ca_pcps_quicksync_acquisition.cc:36-135
+GpsL1CaPcpsQuickSyncAcquisitionB200::GpsL1CaPcpsQuickSyncAcquisitionB200(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
+    : configuration_(c),
+      role_(role),
+      item_size_(sizeof(gr_complex)),
+      doppler_max_(static_cast<unsigned int>(c->property(role + ".doppler_max", 5000))),
+      sampled_ms_(static_cast<unsigned int>(c->property(role + ".coherent_integration_time_ms", 4))),
+      bit_transition_flag_(c->property(role + ".bit_transition_flag", false))
+{
+    item_type_ = c->property(role_ + ".item_type", std::string("gr_complex"));
+    const int64_t fs_in_deprecated = c->property("GNSS-SDR.internal_fs_hz", static_cast<int64_t>(2048000));
+    fs_in_ = c->property("GNSS-SDR.internal_fs_sps", fs_in_deprecated);
+    code_length_ = static_cast<unsigned int>(std::round(static_cast<double>(fs_in_) / (1023000.0 / 1023.0)));
+    const auto temp = static_cast<unsigned int>(std::ceil(std::sqrt(std::log2(code_length_))));
+    folding_factor_ = c->property(role_ + ".folding_factor", temp);
+    if (folding_factor_ == 0U) throw std::invalid_argument("QuickSync acquisition: folding_factor must be positive");
+    if (sampled_ms_ % folding_factor_ != 0)
+        {
+            std::cout << "QuickSync Algorithm requires a coherent_integration_time multiple of " << folding_factor_ << "ms, Value entered " << sampled_ms_ << " ms\n";
+            sampled_ms_ = sampled_ms_ < folding_factor_ ? folding_factor_ : (sampled_ms_ / folding_factor_) * folding_factor_;
+            std::cout << " Coherent_integration_time of " << sampled_ms_ << " ms will be used instead.\n";
+        }
+    vector_length_ = code_length_ * sampled_ms_;
+    max_dwells_ = bit_transition_flag_ ? 2U : static_cast<unsigned int>(c->property(role_ + ".max_dwells", 1));
+    const int samples_per_ms = static_cast<int>(code_length_);
+    code_ = std::vector<std::complex<float>>(code_length_);
+    if (item_type_ != "gr_complex") throw std::invalid_argument(item_type_ + " unknown acquisition item type (GPS_L1_CA_PCPS_QuickSync_Acquisition_B200 takes gr_complex)");
+    acquisition_cc_ = std::make_shared<b200_pcps_quicksync_acquisition>(folding_factor_, sampled_ms_, max_dwells_, doppler_max_, fs_in_, samples_per_ms, static_cast<int32_t>(code_length_),
+        bit_transition_flag_, c->property(role + ".device", 0));
+    if (in > 1) std::cerr << "This implementation only supports one input stream\n";
+    if (out > 0) std::cerr << "This implementation does not provide an output stream\n";
+}
+void GpsL1CaPcpsQuickSyncAcquisitionB200::connect(gr::top_block_sptr top_block)
+{
+    if (top_block) { /* the block cuts its own vectors out of the stream: no stream_to_vector to connect (cf. :294-300) */ }
+}
+void GpsL1CaPcpsQuickSyncAcquisitionB200::disconnect(gr::top_block_sptr top_block)
+{
+    if (top_block) { /* nothing to disconnect */ }
+}
+void GpsL1CaPcpsQuickSyncAcquisitionB200::stop_acquisition()
+{
+    acquisition_cc_->set_state(0);
+    acquisition_cc_->set_active(false);
+}
+// :154-176
+void GpsL1CaPcpsQuickSyncAcquisitionB200::set_threshold(float threshold)
+{
+    float pfa = configuration_->property(role_ + std::to_string(channel_) + ".pfa", static_cast<float>(0.0));
+    if (pfa == 0.0) pfa = configuration_->property(role_ + ".pfa", static_cast<float>(0.0));
+    threshold_ = pfa == 0.0 ? threshold : calculate_threshold(pfa);
+    acquisition_cc_->set_threshold(threshold_);
+}
+// :274-291: the (1 - pfa)^(1 / cells) quantile of an exponential distribution of rate code_length / folding_factor, cells counted on the folded grid
+float GpsL1CaPcpsQuickSyncAcquisitionB200::calculate_threshold(float pfa) const
+{
+    unsigned int frequency_bins = 0;
+    for (int doppler = static_cast<int>(-doppler_max_); doppler <= static_cast<int>(doppler_max_); doppler += static_cast<int>(doppler_step_)) frequency_bins++;
+    const unsigned int ncells = (code_length_ / folding_factor_) * frequency_bins;
+    const double exponent = 1.0 / static_cast<double>(ncells);
+    const double val = std::pow(1.0 - pfa, exponent);
+    const double lambda = static_cast<double>(code_length_) / static_cast<double>(folding_factor_);
+    return static_cast<float>(-std::log1p(-val) / lambda);
+}
+void GpsL1CaPcpsQuickSyncAcquisitionB200::set_doppler_max(unsigned int doppler_max)
+{
+    doppler_max_ = doppler_max;
+    acquisition_cc_->set_doppler_max(doppler_max_);
+}
+void GpsL1CaPcpsQuickSyncAcquisitionB200::set_doppler_step(unsigned int doppler_step)
+{
+    doppler_step_ = doppler_step;
+    acquisition_cc_->set_doppler_step(doppler_step_);
+}
+void GpsL1CaPcpsQuickSyncAcquisitionB200::set_gnss_synchro(Gnss_Synchro* gnss_synchro)
+{
+    gnss_synchro_ = gnss_synchro;
+    acquisition_cc_->set_gnss_synchro(gnss_synchro_);
+}
+void GpsL1CaPcpsQuickSyncAcquisitionB200::set_channel(unsigned int channel)
+{
+    channel_ = channel;
+    acquisition_cc_->set_channel(channel_);
+}
+// :228-244.  The reference copies sampled_ms / folding_factor periods into a buffer of ONE period (it overruns it when that quotient
+// exceeds 1); the block reads one period only (pcps_quicksync_acquisition_cc.cc:137), which is what is built here.
+void GpsL1CaPcpsQuickSyncAcquisitionB200::set_local_code()
+{
+    gps_l1_ca_code_gen_complex_sampled(code_.data(), static_cast<int>(code_.size()), gnss_synchro_->PRN, static_cast<int32_t>(fs_in_), 0);
+    acquisition_cc_->set_local_code(code_.data());
+}
+
 std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out)
 {
     const std::string impl = c->property(role + ".implementation", std::string("Pass_Through"));
@@ -460,6 +552,7 @@ std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const ConfigurationInterfa
     if (impl == "GPS_L5i_PCPS_Acquisition_B200") return std::make_unique<GpsL5iPcpsAcquisitionB200>(c, role, in, out);
     if (impl == "Galileo_E5a_Pcps_Acquisition_B200") return std::make_unique<GalileoE5aPcpsAcquisitionB200>(c, role, in, out);
     if (impl == "Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200") return std::make_unique<GalileoE5aNoncoherentIQAcquisitionCafB200>(c, role, in, out);
+    if (impl == "GPS_L1_CA_PCPS_QuickSync_Acquisition_B200") return std::make_unique<GpsL1CaPcpsQuickSyncAcquisitionB200>(c, role, in, out);
     if (impl == "GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200") return std::make_unique<GpsL1CaPcpsAcquisitionFineDopplerB200>(c, role, in, out);
     return nullptr;
 }

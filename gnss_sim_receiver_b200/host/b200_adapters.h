@@ -11,6 +11,7 @@
 #include "b200_pcps_acquisition.h"
 #include "b200_pcps_acquisition_fine_doppler.h"
 #include "b200_e5a_noncoherent_iq_acquisition_caf.h"
+#include "b200_pcps_quicksync_acquisition.h"
 #include "gnss_sdr_compat.h"
 #include <memory>
 #include <string>
@@ -270,6 +271,53 @@ private:
     int Zero_padding, CAF_window_hz_, code_length_{0};
     unsigned int vector_length_{0}, channel_{0}, doppler_max_, doppler_step_{0}, sampled_ms_, max_dwells_;
     bool bit_transition_flag_, both_signal_components{false};
+};
+
+// adapters/gps_l1_ca_pcps_quicksync_acquisition.{h:50-185,cc:36-312}: `GPS_L1_CA_PCPS_QuickSync_Acquisition`; gr_complex items only; keys doppler_max
+// (5000), coherent_integration_time_ms (4; rounded to a multiple of the folding factor), folding_factor (ceil(sqrt(log2(samples per code)))),
+// bit_transition_flag (then max_dwells = 2), max_dwells (1), pfa.  The block's input items are vectors of samples-per-code x folding_factor
+// samples (the adapter's stream_to_vector, :113-114).
+class GpsL1CaPcpsQuickSyncAcquisitionB200 : public AcquisitionInterface
+{
+public:
+    GpsL1CaPcpsQuickSyncAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
+    std::string role() override { return role_; }
+    std::string implementation() override { return "GPS_L1_CA_PCPS_QuickSync_Acquisition_B200"; }
+    size_t item_size() override { return item_size_; }
+    void connect(gr::top_block_sptr top_block) override;
+    void disconnect(gr::top_block_sptr top_block) override;
+    gr::basic_block_sptr get_left_block() override { return acquisition_cc_; }  // (the reference returns its stream_to_vector here; the block takes the stream itself)
+    gr::basic_block_sptr get_right_block() override { return acquisition_cc_; }
+    void set_gnss_synchro(Gnss_Synchro* p_gnss_synchro) override;
+    void set_channel(unsigned int channel) override;
+    void set_channel_fsm(std::weak_ptr<ChannelFsm> channel_fsm) override { channel_fsm_ = std::move(channel_fsm); }
+    void set_threshold(float threshold) override;
+    void set_doppler_max(unsigned int doppler_max) override;
+    void set_doppler_step(unsigned int doppler_step) override;
+    void init() override { acquisition_cc_->init(); }
+    void set_local_code() override;
+    void set_state(int state) override { acquisition_cc_->set_state(state); }
+    signed int mag() override { return static_cast<signed int>(acquisition_cc_->mag()); }
+    void reset() override { acquisition_cc_->set_active(true); }
+    void stop_acquisition() override;
+    void set_resampler_latency(uint32_t latency_samples __attribute__((unused))) override {}
+    std::shared_ptr<b200_pcps_quicksync_acquisition> block() { return acquisition_cc_; }
+    unsigned int folding_factor() const { return folding_factor_; }
+    unsigned int sampled_ms() const { return sampled_ms_; }
+
+private:
+    float calculate_threshold(float pfa) const;
+    const ConfigurationInterface* configuration_;
+    std::shared_ptr<b200_pcps_quicksync_acquisition> acquisition_cc_;
+    std::weak_ptr<ChannelFsm> channel_fsm_;
+    std::vector<std::complex<float>> code_;
+    std::string role_, item_type_;
+    Gnss_Synchro* gnss_synchro_{nullptr};
+    int64_t fs_in_;
+    size_t item_size_;
+    float threshold_{0.0F};
+    unsigned int channel_{0}, doppler_max_, doppler_step_{0}, sampled_ms_, max_dwells_{1}, folding_factor_{2}, code_length_{0}, vector_length_{0};
+    bool bit_transition_flag_;
 };
 
 // The `.implementation` strings this tree serves; nullptr for any other string (the caller falls through to the

@@ -587,6 +587,14 @@ struct gb200h_acqcaf
     int last_event{0};
 };
 
+struct gb200h_acqqs
+{
+    B200Configuration cfg;
+    std::unique_ptr<GpsL1CaPcpsQuickSyncAcquisitionB200> adapter;
+    Gnss_Synchro synchro;
+    int last_event{0};
+};
+
 struct gb200h_acqfd
 {
     B200Configuration cfg;
@@ -702,6 +710,104 @@ int gb200h_acqcaf_caf_vector(gb200h_acqcaf* a, float* dst, int max_bins)
     const int n = std::min<int>(max_bins, static_cast<int>(v.size()));
     if (n > 0 && dst) std::copy(v.begin(), v.begin() + n, dst);
     return static_cast<int>(v.size());
+}
+
+int gb200h_acqqs_create(const char* conf_text, const char* role, unsigned prn, gb200h_acqqs** out)
+{
+    try
+        {
+            auto a = std::make_unique<gb200h_acqqs>();
+            a->cfg.load_string(conf_text);
+            auto blk = GetB200AcqBlock(&a->cfg, role, 1, 0);
+            auto* qs = dynamic_cast<GpsL1CaPcpsQuickSyncAcquisitionB200*>(blk.get());
+            if (!qs) throw std::runtime_error(std::string(role) + ".implementation is not GPS_L1_CA_PCPS_QuickSync_Acquisition_B200");
+            blk.release();
+            a->adapter.reset(qs);
+            a->synchro.System = 'G';
+            std::memset(a->synchro.Signal, 0, 3);
+            a->synchro.Signal[0] = '1';
+            a->synchro.Signal[1] = 'C';
+            a->synchro.PRN = prn;
+            a->adapter->set_gnss_synchro(&a->synchro);
+            a->adapter->set_channel(0);
+            gb200h_acqqs* raw = a.get();
+            a->adapter->block()->set_event_sink([raw](int ev) { raw->last_event = ev; });
+            *out = a.release();
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+void gb200h_acqqs_destroy(gb200h_acqqs* a) { delete a; }
+
+int gb200h_acqqs_arm(gb200h_acqqs* a, unsigned doppler_max, unsigned doppler_step, float threshold)
+{
+    try
+        {
+            auto& ad = *a->adapter;
+            ad.set_doppler_max(doppler_max);
+            ad.set_doppler_step(doppler_step);
+            ad.set_threshold(threshold);
+            ad.init();
+            ad.set_local_code();
+            a->last_event = 0;
+            ad.set_state(1);
+            return 0;
+        }
+    catch (const std::exception& e)
+        {
+            return fail(e);
+        }
+}
+
+int64_t gb200h_acqqs_work(gb200h_acqqs* a, const void* samples, int64_t n_samples, int max_items)
+{
+    try
+        {
+            auto& blk = *a->adapter->block();
+            const auto* in = static_cast<const std::complex<float>*>(samples);
+            const int64_t len = blk.item_length(), n_items = n_samples / len;
+            int64_t pos = 0;
+            while (pos < n_items)
+                {
+                    pos += blk.general_work(in + pos * len, static_cast<int>(std::min<int64_t>(n_items - pos, max_items)));
+                    if (blk.state() == 0 && !blk.active()) break;
+                }
+            return pos;
+        }
+    catch (const std::exception& e)
+        {
+            fail(e);
+            return -1;
+        }
+}
+
+int gb200h_acqqs_get_status(gb200h_acqqs* a, gb200h_acqqs_status* s)
+{
+    const auto& blk = *a->adapter->block();
+    std::memset(s, 0, sizeof(*s));
+    s->acq_delay_samples = a->synchro.Acq_delay_samples;
+    s->acq_doppler_hz = a->synchro.Acq_doppler_hz;
+    s->acq_samplestamp_samples = a->synchro.Acq_samplestamp_samples;
+    s->acq_doppler_step = a->synchro.Acq_doppler_step;
+    s->sample_counter = blk.sample_counter();
+    s->test_statistics = blk.test_statistics();
+    s->threshold = blk.threshold();
+    s->mag = blk.mag_f();
+    s->input_power = blk.input_power();
+    s->state = blk.state();
+    s->active = blk.active() ? 1 : 0;
+    s->last_event = a->last_event;
+    s->num_doppler_bins = static_cast<int32_t>(blk.num_doppler_bins());
+    s->fft_size = static_cast<int32_t>(blk.fft_size());
+    s->well_count = static_cast<int32_t>(blk.well_count());
+    s->item_length = blk.item_length();
+    s->folding_factor = static_cast<int32_t>(a->adapter->folding_factor());
+    s->sampled_ms = static_cast<int32_t>(a->adapter->sampled_ms());
+    return 0;
 }
 
 int gb200h_acqfd_create(const char* conf_text, const char* role, unsigned prn, gb200h_acqfd** out)

@@ -145,6 +145,25 @@ int gb200h_acqcaf_get_status(gb200h_acqcaf* a, gb200h_acqcaf_status* s);
 /* the filtered CAF vector of the last search (num_doppler_bins floats; 0 returned when CAF_window_hz = 0) */
 int gb200h_acqcaf_caf_vector(gb200h_acqcaf* a, float* dst, int max_bins);
 
+/* ---- QuickSync acquisition (GPS_L1_CA_PCPS_QuickSync_Acquisition_B200; b200_pcps_quicksync_acquisition.h) */
+typedef struct gb200h_acqqs gb200h_acqqs;
+typedef struct
+{
+    double acq_delay_samples, acq_doppler_hz;
+    uint64_t acq_samplestamp_samples, sample_counter;
+    float test_statistics, threshold, mag, input_power;
+    int32_t state, active, last_event, num_doppler_bins, fft_size, well_count, item_length, folding_factor, sampled_ms;
+    uint32_t acq_doppler_step;
+} gb200h_acqqs_status;
+int gb200h_acqqs_create(const char* conf_text, const char* role, unsigned prn, gb200h_acqqs** out);
+void gb200h_acqqs_destroy(gb200h_acqqs* a);
+/* set_doppler_max, set_doppler_step, set_threshold (a configured pfa wins), init, set_local_code, set_state(1) */
+int gb200h_acqqs_arm(gb200h_acqqs* a, unsigned doppler_max, unsigned doppler_step, float threshold);
+/* plays stream_to_vector + the scheduler: the stream is cut into vector items of item_length samples and general_work is called with at most
+ * `max_items` of them until the block has raised its event and gone idle or the items are used up; returns the ITEMS consumed, -1 on error */
+int64_t gb200h_acqqs_work(gb200h_acqqs* a, const void* samples, int64_t n_samples, int max_items);
+int gb200h_acqqs_get_status(gb200h_acqqs* a, gb200h_acqqs_status* s);
+
 /* MAT level-5 writer used by the acquisition dump (b200_mat_writer.h): one file with a single matrix and one scalar of each class */
 int gb200h_mat_write_sample(const char* filename, const float* grid, int rows, int cols, int32_t i32, uint32_t u32, uint64_t u64, float f32);
 

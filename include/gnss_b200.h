@@ -388,6 +388,15 @@ int gb200_acq_read_grid(gb200_acq* h, int slot, float* grid_host);
 int gb200_acq_read_cells(gb200_acq* h, int n_slots, float* vmax, int32_t* imax, float* sum);
 /* forward transform of one fft_size block through the engine's FFT (test hook: natural-order output) */
 int gb200_acq_fft(gb200_acq* h, const gb200_cf32* in_host, gb200_cf32* out_host, int inverse);
+/* Folded input — pcps_quicksync_acquisition_cc (pcps_quicksync_acquisition_cc.cc:296-318): every run takes a block of block_len samples,
+ * wipes the WHOLE block off per Doppler bin (phase accumulated over block_len samples) and adds its first `chunks` pieces of fft_size samples,
+ * in order, into the one fft_size-point transform input of that bin; the rest of the run (code product, inverse transform, |.|^2, maxima,
+ * statistics) is unchanged.  gr_complex engines with consumed_samples == fft_size only; chunks = 0 switches it off.  With folding on,
+ * gb200_acq_run / _run_device read block_len samples. */
+int gb200_acq_set_input_folding(gb200_acq* h, int chunks, int block_len);
+/* The correlations that resolve the folding ambiguity (:337-349), on the block of the last folded run:
+ * acc_out[i] = sum_{j < n_code} x[d_i + j] * wipeoff_bin[d_i + j] * code[j],  d_i = index + i * fft_size,  i < n_candidates. */
+int gb200_acq_folded_candidates(gb200_acq* h, int bin, int index, const gb200_cf32* code_host, int n_code, int n_candidates, gb200_cf32* acc_out);
 /* Non-coherent combination of kept grid rows, per Doppler bin — galileo_e5a_noncoherentIQ_acquisition_caf_cc's "d_magnitudeIA[i] += d_magnitudeQA[i]"
  * then volk_gnsssdr_32f_index_max_32u (galileo_e5a_noncoherent_iq_acquisition_caf_cc.cc:464-467,475-478,494-497,505-508,525-531): for every bin
  * of the last run, row slot_a[bin] + row slot_b[bin] of the kept grid (slot_b[bin] < 0: row slot_a[bin] alone), its maximum and the first

@@ -543,6 +543,51 @@ class RefAcqCaf:
         return out
 
 
+class RefAcqQsStatus(C.Structure):
+    """ref_acqqs_status (oracle/ref_acqqs.cc)"""
+    _fields_ = [("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double), ("acq_samplestamp_samples", C.c_uint64), ("sample_counter", C.c_uint64),
+                ("consumed_total", C.c_int64), ("test_statistics", C.c_float), ("threshold", C.c_float), ("mag", C.c_float), ("input_power", C.c_float),
+                ("state", C.c_int32), ("active", C.c_int32), ("num_doppler_bins", C.c_int32), ("fft_size", C.c_int32), ("well_count", C.c_int32), ("item_length", C.c_int32),
+                ("folding_factor", C.c_int32), ("sampled_ms", C.c_int32), ("n_events", C.c_int32), ("events", C.c_int32 * 8), ("acq_doppler_step", C.c_uint32)]
+
+
+class RefAcqQs:
+    """pcps_quicksync_acquisition_cc of the reference (oracle/ref_acqqs.cc: the reference's own block compiled unmodified into oracle/_ref), made
+    and driven like adapters/gps_l1_ca_pcps_quicksync_acquisition.cc does; folding_factor 0 = the adapter's default"""
+
+    def __init__(self, fs_in, folding_factor, sampled_ms, max_dwells, doppler_max, prn, bit_transition=False):
+        r = ref()
+        r.ref_acqqs_new.restype = C.c_void_p
+        r.ref_acqqs_new.argtypes = [C.c_longlong, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_uint]
+        r.ref_acqqs_free.argtypes = [C.c_void_p]
+        r.ref_acqqs_arm.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_float]
+        r.ref_acqqs_work.restype = C.c_longlong
+        r.ref_acqqs_work.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int]
+        r.ref_acqqs_get_status.argtypes = [C.c_void_p, C.POINTER(RefAcqQsStatus)]
+        self._r = r
+        r.ref_acq_fft_precision.argtypes = [C.c_int]
+        r.ref_acq_fft_precision(0)
+        self._h = r.ref_acqqs_new(int(fs_in), int(folding_factor), int(sampled_ms), int(max_dwells), int(doppler_max), int(bit_transition), int(prn))
+
+    def close(self):
+        if self._h:
+            self._r.ref_acqqs_free(self._h)
+            self._h = None
+
+    def arm(self, doppler_max, doppler_step, threshold):
+        self._r.ref_acqqs_arm(self._h, int(doppler_max), int(doppler_step), float(threshold))
+
+    def work(self, samples, max_items):
+        """returns the vector ITEMS consumed"""
+        samples = np.ascontiguousarray(samples, dtype=np.complex64)
+        return int(self._r.ref_acqqs_work(self._h, samples.ctypes.data, samples.size, int(max_items)))
+
+    def status(self):
+        s = RefAcqQsStatus()
+        self._r.ref_acqqs_get_status(self._h, C.byref(s))
+        return s
+
+
 # ---------------------------------------------------------------------------------------------------------------- the reference's own tracking block
 class RefTrkBlock:
     """dll_pll_veml_tracking of the reference (oracle/ref_trkblk.cc: the reference's own dll_pll_veml_tracking.cc + dll_pll_conf.cc compiled
