@@ -118,6 +118,7 @@ SYMBOLS = {
     "gb200h_acqcaf_get_status": (_i, [_vp, C.POINTER(CafStatus)]),
     "gb200h_acqcaf_caf_vector": (_i, [_vp, _vp, _i]),
     "gb200h_acqqs_create": (_i, [C.c_char_p, C.c_char_p, C.c_uint, C.POINTER(_vp)]),
+    "gb200h_acqqs_create2": (_i, [C.c_char_p, C.c_char_p, C.c_uint, C.c_char, C.c_char_p, C.POINTER(_vp)]),
     "gb200h_acqqs_destroy": (None, [_vp]),
     "gb200h_acqqs_arm": (_i, [_vp, C.c_uint, C.c_uint, C.c_float]),
     "gb200h_acqqs_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
@@ -359,12 +360,12 @@ class E5aCafAcquisitionBlock:
 
 
 class QuickSyncAcquisitionBlock:
-    """GPS_L1_CA_PCPS_QuickSync_Acquisition_B200 (host/b200_pcps_quicksync_acquisition.h) driven like a channel drives it"""
+    """GPS_L1_CA_PCPS_QuickSync_Acquisition_B200 / Galileo_E1_PCPS_QuickSync_Ambiguous_Acquisition_B200 (host/b200_pcps_quicksync_acquisition.h) driven like a channel drives it"""
 
-    def __init__(self, conf_text, role, prn):
+    def __init__(self, conf_text, role, prn, system="G", signal="1C"):
         self._lib = lib()
         self._h = _vp()
-        check(self._lib.gb200h_acqqs_create(conf_text.encode(), role.encode(), prn, C.byref(self._h)))
+        check(self._lib.gb200h_acqqs_create2(conf_text.encode(), role.encode(), prn, system.encode(), signal.encode(), C.byref(self._h)))
 
     def close(self):
         if self._h:

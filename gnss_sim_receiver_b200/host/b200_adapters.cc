@@ -484,6 +484,39 @@ GpsL1CaPcpsQuickSyncAcquisitionB200::GpsL1CaPcpsQuickSyncAcquisitionB200(const C
     if (in > 1) std::cerr << "This implementation only supports one input stream\n";
     if (out > 0) std::cerr << "This implementation does not provide an output stream\n";
 }
+// adapters/galileo_e1_pcps_quicksync_ambiguous_acquisition.cc:36-150
+GpsL1CaPcpsQuickSyncAcquisitionB200::GpsL1CaPcpsQuickSyncAcquisitionB200(const ConfigurationInterface* c, const std::string& role, unsigned int in, unsigned int out, GalileoE1Tag)
+    : galileo_(true),
+      configuration_(c),
+      role_(role),
+      item_size_(sizeof(gr_complex)),
+      doppler_max_(static_cast<unsigned int>(c->property(role + ".doppler_max", 5000))),
+      sampled_ms_(static_cast<unsigned int>(c->property(role + ".coherent_integration_time_ms", 8))),
+      bit_transition_flag_(c->property(role + ".bit_transition_flag", false))
+{
+    item_type_ = c->property(role_ + ".item_type", std::string("gr_complex"));
+    const int64_t fs_in_deprecated = c->property("GNSS-SDR.internal_fs_hz", static_cast<int64_t>(4000000));
+    fs_in_ = c->property("GNSS-SDR.internal_fs_sps", fs_in_deprecated);
+    code_length_ = static_cast<unsigned int>(std::round(static_cast<double>(fs_in_) / (1023000.0 / 4092.0)));  // GALILEO_E1_CODE_CHIP_RATE_CPS / GALILEO_E1_B_CODE_LENGTH_CHIPS: 4 ms
+    const auto samples_per_ms = static_cast<int>(std::round(code_length_ / 4.0));
+    folding_factor_ = static_cast<unsigned int>(c->property(role + ".folding_factor", 2));
+    if (folding_factor_ == 0U) throw std::invalid_argument("QuickSync acquisition: folding_factor must be positive");
+    if (sampled_ms_ % (folding_factor_ * 4) != 0)
+        {
+            std::cout << "QuickSync Algorithm requires a coherent_integration_time multiple of " << (folding_factor_ * 4) << "ms, Value entered " << sampled_ms_ << " ms\n";
+            sampled_ms_ = sampled_ms_ < folding_factor_ * 4 ? folding_factor_ * 4 : (sampled_ms_ / (folding_factor_ * 4)) * (folding_factor_ * 4);
+            std::cout << "coherent_integration_time = " << sampled_ms_ << " ms will be used.\n";
+        }
+    vector_length_ = sampled_ms_ * static_cast<unsigned int>(samples_per_ms);
+    max_dwells_ = bit_transition_flag_ ? 2U : static_cast<unsigned int>(c->property(role_ + ".max_dwells", 1));
+    code_ = std::vector<std::complex<float>>(code_length_);
+    if (item_type_ != "gr_complex") throw std::invalid_argument(item_type_ + " unknown acquisition item type (Galileo_E1_PCPS_QuickSync_Ambiguous_Acquisition_B200 takes gr_complex)");
+    acquisition_cc_ = std::make_shared<b200_pcps_quicksync_acquisition>(folding_factor_, sampled_ms_, max_dwells_, doppler_max_, fs_in_, samples_per_ms, static_cast<int32_t>(code_length_),
+        bit_transition_flag_, c->property(role + ".device", 0));
+    acquisition_cc_->set_item_length(static_cast<int>(vector_length_));  // the reference's stream_to_vector (:129-130)
+    if (in > 1) std::cerr << "This implementation only supports one input stream\n";
+    if (out > 0) std::cerr << "This implementation does not provide an output stream\n";
+}
 void GpsL1CaPcpsQuickSyncAcquisitionB200::connect(gr::top_block_sptr top_block)
 {
     if (top_block) { /* the block cuts its own vectors out of the stream: no stream_to_vector to connect (cf. :294-300) */ }
@@ -540,6 +573,15 @@ void GpsL1CaPcpsQuickSyncAcquisitionB200::set_channel(unsigned int channel)
 // exceeds 1); the block reads one period only (pcps_quicksync_acquisition_cc.cc:137), which is what is built here.
 void GpsL1CaPcpsQuickSyncAcquisitionB200::set_local_code()
 {
+    if (galileo_)
+        {
+            // galileo_e1_pcps_quicksync_ambiguous_acquisition.cc:234-258 (one period; the reference's extra copies overrun its one-period buffer)
+            const bool cboc = configuration_->property("Acquisition" + std::to_string(channel_) + ".cboc", false);
+            const char sig[3] = {gnss_synchro_->Signal[0], gnss_synchro_->Signal[1], '\0'};
+            galileo_e1_code_gen_complex_sampled(code_.data(), sig, cboc, gnss_synchro_->PRN, static_cast<int32_t>(fs_in_), 0, false);
+            acquisition_cc_->set_local_code(code_.data());
+            return;
+        }
     gps_l1_ca_code_gen_complex_sampled(code_.data(), static_cast<int>(code_.size()), gnss_synchro_->PRN, static_cast<int32_t>(fs_in_), 0);
     acquisition_cc_->set_local_code(code_.data());
 }
@@ -552,6 +594,7 @@ std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const ConfigurationInterfa
     if (impl == "GPS_L5i_PCPS_Acquisition_B200") return std::make_unique<GpsL5iPcpsAcquisitionB200>(c, role, in, out);
     if (impl == "Galileo_E5a_Pcps_Acquisition_B200") return std::make_unique<GalileoE5aPcpsAcquisitionB200>(c, role, in, out);
     if (impl == "Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200") return std::make_unique<GalileoE5aNoncoherentIQAcquisitionCafB200>(c, role, in, out);
+    if (impl == "Galileo_E1_PCPS_QuickSync_Ambiguous_Acquisition_B200") return std::make_unique<GalileoE1PcpsQuickSyncAmbiguousAcquisitionB200>(c, role, in, out);
     if (impl == "GPS_L1_CA_PCPS_QuickSync_Acquisition_B200") return std::make_unique<GpsL1CaPcpsQuickSyncAcquisitionB200>(c, role, in, out);
     if (impl == "GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200") return std::make_unique<GpsL1CaPcpsAcquisitionFineDopplerB200>(c, role, in, out);
     return nullptr;

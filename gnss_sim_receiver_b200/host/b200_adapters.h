@@ -282,7 +282,7 @@ class GpsL1CaPcpsQuickSyncAcquisitionB200 : public AcquisitionInterface
 public:
     GpsL1CaPcpsQuickSyncAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams);
     std::string role() override { return role_; }
-    std::string implementation() override { return "GPS_L1_CA_PCPS_QuickSync_Acquisition_B200"; }
+    std::string implementation() override { return galileo_ ? "Galileo_E1_PCPS_QuickSync_Ambiguous_Acquisition_B200" : "GPS_L1_CA_PCPS_QuickSync_Acquisition_B200"; }
     size_t item_size() override { return item_size_; }
     void connect(gr::top_block_sptr top_block) override;
     void disconnect(gr::top_block_sptr top_block) override;
@@ -305,6 +305,14 @@ public:
     unsigned int folding_factor() const { return folding_factor_; }
     unsigned int sampled_ms() const { return sampled_ms_; }
 
+protected:
+    struct GalileoE1Tag
+    {
+    };
+    // adapters/galileo_e1_pcps_quicksync_ambiguous_acquisition.cc:36-150
+    GpsL1CaPcpsQuickSyncAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams, GalileoE1Tag);
+    bool galileo_{false};
+
 private:
     float calculate_threshold(float pfa) const;
     const ConfigurationInterface* configuration_;
@@ -318,6 +326,17 @@ private:
     float threshold_{0.0F};
     unsigned int channel_{0}, doppler_max_, doppler_step_{0}, sampled_ms_, max_dwells_{1}, folding_factor_{2}, code_length_{0}, vector_length_{0};
     bool bit_transition_flag_;
+};
+
+// adapters/galileo_e1_pcps_quicksync_ambiguous_acquisition.{h,cc}: `Galileo_E1_PCPS_QuickSync_Ambiguous_Acquisition` — the same block over 4 ms E1 codes:
+// coherent_integration_time_ms (8) a multiple of 4 x folding_factor (2), `Acquisition<channel>.cboc`, vector items of sampled_ms x samples per ms
+class GalileoE1PcpsQuickSyncAmbiguousAcquisitionB200 : public GpsL1CaPcpsQuickSyncAcquisitionB200
+{
+public:
+    GalileoE1PcpsQuickSyncAmbiguousAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams)
+        : GpsL1CaPcpsQuickSyncAcquisitionB200(configuration, role, in_streams, out_streams, GalileoE1Tag{})
+    {
+    }
 };
 
 // The `.implementation` strings this tree serves; nullptr for any other string (the caller falls through to the

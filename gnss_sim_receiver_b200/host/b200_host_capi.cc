@@ -712,7 +712,9 @@ int gb200h_acqcaf_caf_vector(gb200h_acqcaf* a, float* dst, int max_bins)
     return static_cast<int>(v.size());
 }
 
-int gb200h_acqqs_create(const char* conf_text, const char* role, unsigned prn, gb200h_acqqs** out)
+int gb200h_acqqs_create(const char* conf_text, const char* role, unsigned prn, gb200h_acqqs** out) { return gb200h_acqqs_create2(conf_text, role, prn, 'G', "1C", out); }
+
+int gb200h_acqqs_create2(const char* conf_text, const char* role, unsigned prn, char system, const char* signal, gb200h_acqqs** out)
 {
     try
         {
@@ -720,13 +722,13 @@ int gb200h_acqqs_create(const char* conf_text, const char* role, unsigned prn, g
             a->cfg.load_string(conf_text);
             auto blk = GetB200AcqBlock(&a->cfg, role, 1, 0);
             auto* qs = dynamic_cast<GpsL1CaPcpsQuickSyncAcquisitionB200*>(blk.get());
-            if (!qs) throw std::runtime_error(std::string(role) + ".implementation is not GPS_L1_CA_PCPS_QuickSync_Acquisition_B200");
+            if (!qs) throw std::runtime_error(std::string(role) + ".implementation is not a B200 QuickSync acquisition adapter");
             blk.release();
             a->adapter.reset(qs);
-            a->synchro.System = 'G';
+            a->synchro.System = system;
             std::memset(a->synchro.Signal, 0, 3);
-            a->synchro.Signal[0] = '1';
-            a->synchro.Signal[1] = 'C';
+            a->synchro.Signal[0] = signal[0];
+            a->synchro.Signal[1] = signal[0] ? signal[1] : '\0';
             a->synchro.PRN = prn;
             a->adapter->set_gnss_synchro(&a->synchro);
             a->adapter->set_channel(0);

@@ -156,6 +156,8 @@ typedef struct
     uint32_t acq_doppler_step;
 } gb200h_acqqs_status;
 int gb200h_acqqs_create(const char* conf_text, const char* role, unsigned prn, gb200h_acqqs** out);
+/* same for either QuickSync adapter: `system` / `signal` fill the channel's Gnss_Synchro ('G' "1C", 'E' "1B" / "1C") */
+int gb200h_acqqs_create2(const char* conf_text, const char* role, unsigned prn, char system, const char* signal, gb200h_acqqs** out);
 void gb200h_acqqs_destroy(gb200h_acqqs* a);
 /* set_doppler_max, set_doppler_step, set_threshold (a configured pfa wins), init, set_local_code, set_state(1) */
 int gb200h_acqqs_arm(gb200h_acqqs* a, unsigned doppler_max, unsigned doppler_step, float threshold);

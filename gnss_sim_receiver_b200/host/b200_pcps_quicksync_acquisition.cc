@@ -45,6 +45,12 @@ b200_pcps_quicksync_acquisition::b200_pcps_quicksync_acquisition(uint32_t foldin
     d_code.assign(static_cast<size_t>(d_samples_per_code), std::complex<float>(0.0F, 0.0F));
 }
 
+void b200_pcps_quicksync_acquisition::set_item_length(int n)
+{
+    if (n < d_samples_per_code * static_cast<int>(d_folding_factor)) throw std::invalid_argument("QuickSync acquisition: vector items shorter than samples_per_code * folding_factor");
+    item_length_ = n;
+}
+
 b200_pcps_quicksync_acquisition::~b200_pcps_quicksync_acquisition() { gb200_acq_destroy(h_); }
 
 // :133-156: the unfolded replica is kept for the delay resolution; the transform gets the replica folded folding_factor times
@@ -77,7 +83,7 @@ void b200_pcps_quicksync_acquisition::init()
     // :188-189: phase_step_rad = float(TWO_PI) * doppler / float(fs) with an int doppler: the engine forms the same product from the float
     for (uint32_t k = 0; k < d_num_doppler_bins; k++) f[k] = static_cast<float>(-static_cast<int32_t>(d_doppler_max) + static_cast<int32_t>(d_doppler_step * k));
     if (gb200_acq_set_doppler_bins(h_, f.data(), static_cast<int>(d_num_doppler_bins)) != GB200_OK) fail("gb200_acq_set_doppler_bins");
-    if (gb200_acq_set_input_folding(h_, static_cast<int>(d_folding_factor * d_folding_factor), item_length()) != GB200_OK) fail("gb200_acq_set_input_folding");
+    if (gb200_acq_set_input_folding(h_, static_cast<int>(d_folding_factor * d_folding_factor), d_samples_per_code * static_cast<int>(d_folding_factor)) != GB200_OK) fail("gb200_acq_set_input_folding");
 }
 
 // :197-219
@@ -109,7 +115,7 @@ void b200_pcps_quicksync_acquisition::dwell(const std::complex<float>* in)
     d_sample_counter += static_cast<uint64_t>(d_sampled_ms) * d_samples_per_ms;
     d_well_count++;
     // :291-296: mean |x|^2 over the item, summed in sample order like volk_32f_accumulator_s32f
-    const int n = item_length();
+    const int n = d_samples_per_code * static_cast<int>(d_folding_factor);
     for (int i = 0; i < n; i++)
         {
             const float re = in[i].real(), im = in[i].imag();

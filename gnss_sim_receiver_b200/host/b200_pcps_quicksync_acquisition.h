@@ -44,7 +44,11 @@ public:
 
     // general_work (:214-550): `in` holds ninput_items vector items of item_length() samples each; returns the ITEMS consumed
     int general_work(const std::complex<float>* in, int ninput_items);
-    int item_length() const { return d_samples_per_code * static_cast<int>(d_folding_factor); }
+    // samples per vector item: samples_per_code * folding_factor are read of each; the Galileo adapter's stream_to_vector makes items of
+    // sampled_ms * samples_per_ms samples (galileo_e1_pcps_quicksync_ambiguous_acquisition.cc:129-130), which is longer when the coherent time
+    // exceeds folding_factor code periods
+    int item_length() const { return item_length_ ? item_length_ : d_samples_per_code * static_cast<int>(d_folding_factor); }
+    void set_item_length(int n);
 
     int state() const { return d_state; }
     bool active() const { return d_active; }
@@ -69,7 +73,7 @@ private:
     float d_threshold{0.0F}, d_mag{0.0F}, d_input_power{0.0F}, d_test_statistics{0.0F};
     int32_t d_samples_per_ms, d_samples_per_code, d_state{0};
     uint32_t d_channel{0}, d_folding_factor, d_doppler_max, d_doppler_step{0}, d_sampled_ms, d_max_dwells, d_well_count{0}, d_fft_size, d_num_doppler_bins{0};
-    int device_;
+    int device_, item_length_{0};
     bool d_bit_transition_flag, d_active{false};
 };
 }  // namespace gb200h

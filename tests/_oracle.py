@@ -555,8 +555,10 @@ class RefAcqQs:
     """pcps_quicksync_acquisition_cc of the reference (oracle/ref_acqqs.cc: the reference's own block compiled unmodified into oracle/_ref), made
     and driven like adapters/gps_l1_ca_pcps_quicksync_acquisition.cc does; folding_factor 0 = the adapter's default"""
 
-    def __init__(self, fs_in, folding_factor, sampled_ms, max_dwells, doppler_max, prn, bit_transition=False):
+    def __init__(self, fs_in, folding_factor, sampled_ms, max_dwells, doppler_max, prn, bit_transition=False, galileo_signal=None, cboc=False):
         r = ref()
+        r.ref_acqqs_new_e1.restype = C.c_void_p
+        r.ref_acqqs_new_e1.argtypes = [C.c_longlong, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_uint, C.c_char_p, C.c_int]
         r.ref_acqqs_new.restype = C.c_void_p
         r.ref_acqqs_new.argtypes = [C.c_longlong, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_uint]
         r.ref_acqqs_free.argtypes = [C.c_void_p]
@@ -567,7 +569,10 @@ class RefAcqQs:
         self._r = r
         r.ref_acq_fft_precision.argtypes = [C.c_int]
         r.ref_acq_fft_precision(0)
-        self._h = r.ref_acqqs_new(int(fs_in), int(folding_factor), int(sampled_ms), int(max_dwells), int(doppler_max), int(bit_transition), int(prn))
+        if galileo_signal:  # the Galileo E1 adapter over the same block
+            self._h = r.ref_acqqs_new_e1(int(fs_in), int(folding_factor), int(sampled_ms), int(max_dwells), int(doppler_max), int(bit_transition), int(prn), galileo_signal.encode(), int(cboc))
+        else:
+            self._h = r.ref_acqqs_new(int(fs_in), int(folding_factor), int(sampled_ms), int(max_dwells), int(doppler_max), int(bit_transition), int(prn))
 
     def close(self):
         if self._h:

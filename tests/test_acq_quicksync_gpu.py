@@ -77,6 +77,38 @@ def test_dwells_negative_acquisition_bit_transition_and_pfa():
     a.close()
 
 
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("folding,sampled_ms,signal,cboc", [(None, 8, "1B", False), (2, 16, "1B", True), (4, 16, "1C", False)])
+def test_galileo_e1_adapter_equals_the_reference_block(folding, sampled_ms, signal, cboc):
+    """`Galileo_E1_PCPS_QuickSync_Ambiguous_Acquisition_B200`: the same block over 4 ms E1 codes (E1-B or the E1-C pilot, sinBOC or CBOC replica), vector
+    items of sampled_ms x samples per ms — longer than the searched part when the coherent time exceeds folding_factor code periods"""
+    import _signals as S
+    from gnss_sim_receiver_b200 import _hostapi as H
+    prn, doppler, delay_chips, dmax, dstep = 11, 1830.0, 1500.0, 5000, 125
+    comps = [dict(table=S.e1_table(prn, signal), f_chip=2 * 1.023e6, doppler=doppler, delay=2 * delay_chips, cn0=50.0, phase=1.0)]
+    x = S.synth_if(160 * 4000, FS, comps, seed=3)
+    r = "Acquisition_1B"
+    conf = (f"GNSS-SDR.internal_fs_sps={int(FS)}\n{r}.implementation=Galileo_E1_PCPS_QuickSync_Ambiguous_Acquisition_B200\n{r}.item_type=gr_complex\n{r}.doppler_max={dmax}\n"
+            f"{r}.coherent_integration_time_ms={sampled_ms}\nAcquisition0.cboc={'true' if cboc else 'false'}\n" + (f"{r}.folding_factor={folding}\n" if folding else ""))
+    a = H.QuickSyncAcquisitionBlock(conf, r, prn, "E", signal)
+    a.arm(dmax, dstep, 0.001)
+    ca = a.work(x, 2)
+    sa = a.status()
+    a.close()
+    b = O.RefAcqQs(FS, folding or 0, sampled_ms, 1, dmax, prn, galileo_signal=signal, cboc=cboc)
+    b.arm(dmax, dstep, 0.001)
+    cb = b.work(x, 2)
+    sb = b.status()
+    b.close()
+    assert ca == cb == 3 and sa.sample_counter == sb.sample_counter and [sa.last_event] == list(sb.events[:sb.n_events]) == [1]
+    assert (sa.folding_factor, sa.sampled_ms, sa.item_length, sa.fft_size, sa.num_doppler_bins) == (sb.folding_factor, sb.sampled_ms, sb.item_length, sb.fft_size, sb.num_doppler_bins)
+    assert sa.item_length == sampled_ms * 4000 and sa.fft_size == 16000 // (folding or 2)
+    assert sa.input_power == sb.input_power and sa.acq_delay_samples == sb.acq_delay_samples and sa.acq_doppler_hz == sb.acq_doppler_hz
+    assert sa.acq_samplestamp_samples == sb.acq_samplestamp_samples == sampled_ms * 4000 and sa.acq_doppler_step == sb.acq_doppler_step == dstep
+    assert abs(sa.mag - sb.mag) <= 1e-4 * sb.mag and abs(sa.test_statistics - sb.test_statistics) <= 1e-4 * sb.test_statistics
+    assert abs(sa.acq_delay_samples - delay_chips * 16000 / 4092) <= 2.0 and abs(sa.acq_doppler_hz - doppler) <= 62.5
+
+
 def test_errors_are_loud():
     from gnss_sim_receiver_b200 import _hostapi as H
     with pytest.raises(Exception, match="gr_complex"):
