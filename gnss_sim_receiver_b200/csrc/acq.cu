@@ -61,6 +61,10 @@ struct gb200_acq
     float2* d_fold_iq{nullptr};   // [fold_len] the block as uploaded
     float* d_fold_phase{nullptr};  // [n_bins][fold_len] fp32 accumulated wipe-off phases over the whole block
     float2* d_fold{nullptr};       // [n_bins][N] folded, wiped input of every bin
+    int fold_alloc_bins{0};        // bins the two tables above are allocated for (kept across Doppler-grid re-installs of the same size)
+    // scratch of the strategy helpers (spectrum peak, grid pair maximum / probe, folded candidates): grown on demand, never shrunk
+    char* d_aux{nullptr};
+    size_t aux_bytes{0};
     // last run (replay)
     std::vector<int> last_slots;
     int last_dwell{0};

@@ -420,8 +420,9 @@ class RefAcq:
         self._r.ref_acq_get_status(self._h, C.byref(s))
         return s
 
-    def work(self, items, scalars_per_item):
-        """general_work over a stream of items until the block stops (positive / negative acquisition) or the stream ends; returns items consumed"""
+    def work(self, items, scalars_per_item, chunk=None):
+        """general_work over a stream of items until the block stops (positive / negative acquisition) or the stream ends; returns items consumed.
+        chunk: at most that many items are offered per scheduler call (what gb200h_acq_work's `chunk` is on the product side); None = all that is left"""
         items = np.ascontiguousarray(items)
         n_items, isz = len(items) // scalars_per_item, items.itemsize * scalars_per_item
         pos, idle = 0, 0
@@ -431,7 +432,7 @@ class RefAcq:
                 break
             # (the block switches from buffering to searching on the call AFTER the one that filled its buffer, :985-989, so a call with
             # no new items is part of the sequence; two calls in a row without any effect end the loop)
-            c = self._r.ref_acq_work(self._h, items.ctypes.data + pos * isz, n_items - pos)
+            c = self._r.ref_acq_work(self._h, items.ctypes.data + pos * isz, n_items - pos if chunk is None else min(chunk, n_items - pos))
             pos += c
             st2 = self.status()
             idle = idle + 1 if (c == 0 and st2.state == st.state and st2.active == st.active) else 0

@@ -172,7 +172,7 @@ def test_two_step_acquisition_refines_doppler():
         b.init(10000, 250, 0.0)
         b.set_local_code(O.gps_l1_ca_code_sampled(prn, int(FS), 4000))
         b.arm()
-        rc = b.work(x, 1)
+        rc = b.work(x, 1, chunk=1000)  # the same scheduler calls as a.work(x, chunk=1000)
         rs = b.status()
         b.close()
         assert rc == consumed and list(rs.fsm_events[:rs.n_fsm_events]) == [1]
