@@ -117,6 +117,9 @@ SYMBOLS = {
     "gb200h_acqcaf_work": (C.c_int64, [_vp, _vp, C.c_int64, _i]),
     "gb200h_acqcaf_get_status": (_i, [_vp, C.POINTER(CafStatus)]),
     "gb200h_acqcaf_caf_vector": (_i, [_vp, _vp, _i]),
+    "gb200h_acqfd_work_gr": (C.c_int64, [_vp, _vp, C.c_int64, C.POINTER(C.c_int)]),
+    "gb200h_acqcaf_work_gr": (C.c_int64, [_vp, _vp, C.c_int64, C.POINTER(C.c_int)]),
+    "gb200h_acqqs_work_gr": (C.c_int64, [_vp, _vp, C.c_int64, C.POINTER(C.c_int)]),
     "gb200h_acqqs_create": (_i, [C.c_char_p, C.c_char_p, C.c_uint, C.POINTER(_vp)]),
     "gb200h_acqqs_create2": (_i, [C.c_char_p, C.c_char_p, C.c_uint, C.c_char, C.c_char_p, C.POINTER(_vp)]),
     "gb200h_acqqs_destroy": (None, [_vp]),
@@ -314,6 +317,13 @@ class FineDopplerAcquisitionBlock:
         items = np.ascontiguousarray(items, dtype=np.complex64)
         return check(self._lib.gb200h_acqfd_work(self._h, items.ctypes.data, items.size, int(noutput_items)))
 
+    def work_gr(self, items):
+        """the same stream through the block's gr::block face (host/b200_gr_blocks.h); returns (consumed, last event on the "events" port)"""
+        items = np.ascontiguousarray(items, dtype=np.complex64)
+        ev = C.c_int()
+        done = check(self._lib.gb200h_acqfd_work_gr(self._h, items.ctypes.data, items.size, C.byref(ev)))
+        return done, ev.value
+
     def status(self):
         s = FineDopplerStatus()
         check(self._lib.gb200h_acqfd_get_status(self._h, C.byref(s)))
@@ -345,6 +355,13 @@ class E5aCafAcquisitionBlock:
     def work(self, items, chunk):
         items = np.ascontiguousarray(items, dtype=np.complex64)
         return check(self._lib.gb200h_acqcaf_work(self._h, items.ctypes.data, items.size, int(chunk)))
+
+    def work_gr(self, items):
+        """the same stream through the block's gr::block face (host/b200_gr_blocks.h); returns (consumed, last event on the "events" port)"""
+        items = np.ascontiguousarray(items, dtype=np.complex64)
+        ev = C.c_int()
+        done = check(self._lib.gb200h_acqcaf_work_gr(self._h, items.ctypes.data, items.size, C.byref(ev)))
+        return done, ev.value
 
     def status(self):
         s = CafStatus()
@@ -385,6 +402,13 @@ class QuickSyncAcquisitionBlock:
         """returns the vector ITEMS consumed"""
         samples = np.ascontiguousarray(samples, dtype=np.complex64)
         return check(self._lib.gb200h_acqqs_work(self._h, samples.ctypes.data, samples.size, int(max_items)))
+
+    def work_gr(self, items):
+        """the same stream through the block's gr::block face (host/b200_gr_blocks.h); returns (consumed, last event on the "events" port)"""
+        items = np.ascontiguousarray(items, dtype=np.complex64)
+        ev = C.c_int()
+        done = check(self._lib.gb200h_acqqs_work_gr(self._h, items.ctypes.data, items.size, C.byref(ev)))
+        return done, ev.value
 
     def status(self):
         s = QuickSyncStatus()

@@ -69,6 +69,53 @@ int b200_acquisition_gr::general_work(int noutput_items, gr_vector_int& ninput_i
     return 0;
 }
 
+// ------------------------------------------------------------------ the other acquisition strategies
+b200_fine_doppler_acquisition_gr::b200_fine_doppler_acquisition_gr(std::shared_ptr<b200_pcps_acquisition_fine_doppler> impl)
+    : gr::block("b200_pcps_acquisition_fine_doppler", gr::io_signature::make(1, 1, sizeof(gr_complex)), gr::io_signature::make(0, 1, sizeof(Gnss_Synchro))), d_impl(std::move(impl))
+{
+    this->message_port_register_out(pmt::mp("events"));
+    d_impl->set_event_sink([this](int ev) { this->message_port_pub(pmt::mp("events"), pmt::from_long(ev)); });
+}
+void b200_fine_doppler_acquisition_gr::forecast(int noutput_items, gr_vector_int& ninput_items_required)
+{
+    if (noutput_items != 0) ninput_items_required[0] = d_impl->fft_size();  // :171-178
+}
+int b200_fine_doppler_acquisition_gr::general_work(int noutput_items, gr_vector_int& ninput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items)
+{
+    (void)output_items;
+    this->consume_each(d_impl->general_work(noutput_items, reinterpret_cast<const std::complex<float>*>(input_items[0]), ninput_items[0]));
+    return 0;
+}
+
+b200_e5a_caf_acquisition_gr::b200_e5a_caf_acquisition_gr(std::shared_ptr<b200_e5a_noncoherent_iq_acquisition_caf> impl)
+    : gr::block("b200_e5a_noncoherent_iq_acquisition_caf", gr::io_signature::make(1, 1, sizeof(gr_complex)), gr::io_signature::make(0, 1, sizeof(Gnss_Synchro))), d_impl(std::move(impl))
+{
+    this->message_port_register_out(pmt::mp("events"));
+    d_impl->set_event_sink([this](int ev) { this->message_port_pub(pmt::mp("events"), pmt::from_long(ev)); });
+}
+int b200_e5a_caf_acquisition_gr::general_work(int noutput_items, gr_vector_int& ninput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items)
+{
+    (void)noutput_items;
+    (void)output_items;
+    this->consume_each(d_impl->general_work(reinterpret_cast<const std::complex<float>*>(input_items[0]), ninput_items[0]));
+    return 0;
+}
+
+b200_quicksync_acquisition_gr::b200_quicksync_acquisition_gr(std::shared_ptr<b200_pcps_quicksync_acquisition> impl)
+    : gr::block("b200_pcps_quicksync_acquisition", gr::io_signature::make(1, 1, static_cast<int>(sizeof(gr_complex)) * impl->item_length()), gr::io_signature::make(0, 1, sizeof(Gnss_Synchro))),
+      d_impl(std::move(impl))
+{
+    this->message_port_register_out(pmt::mp("events"));
+    d_impl->set_event_sink([this](int ev) { this->message_port_pub(pmt::mp("events"), pmt::from_long(ev)); });
+}
+int b200_quicksync_acquisition_gr::general_work(int noutput_items, gr_vector_int& ninput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items)
+{
+    (void)noutput_items;
+    (void)output_items;
+    this->consume_each(d_impl->general_work(reinterpret_cast<const std::complex<float>*>(input_items[0]), ninput_items[0]));  // vector items
+    return 0;
+}
+
 std::shared_ptr<b200_tracking_gr> make_b200_tracking_gr(std::shared_ptr<b200_dll_pll_veml_tracking> impl, size_t item_size, unsigned vector_length)
 {
     return std::make_shared<b200_tracking_gr>(std::move(impl), item_size, vector_length);

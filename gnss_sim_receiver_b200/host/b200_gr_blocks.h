@@ -10,7 +10,10 @@
 #define GB200_GR_BLOCKS_H
 
 #include "b200_dll_pll_veml_tracking.h"
+#include "b200_e5a_noncoherent_iq_acquisition_caf.h"
 #include "b200_pcps_acquisition.h"
+#include "b200_pcps_acquisition_fine_doppler.h"
+#include "b200_pcps_quicksync_acquisition.h"
 #include <gnuradio/block.h>
 #include <memory>
 
@@ -39,6 +42,42 @@ public:
 
 private:
     std::shared_ptr<b200_pcps_acquisition> d_impl;
+};
+
+// The other acquisition strategies, same pattern: "events" out port (1 positive / 2 negative), consume_each of what the FSM took.
+//   pcps_acquisition_fine_doppler_cc.cc:40-68 (gr_complex in, Gnss_Synchro out), :171-178 (forecast: fft_size items), :450-563
+class b200_fine_doppler_acquisition_gr : public gr::block
+{
+public:
+    explicit b200_fine_doppler_acquisition_gr(std::shared_ptr<b200_pcps_acquisition_fine_doppler> impl);
+    void forecast(int noutput_items, gr_vector_int& ninput_items_required) override;
+    int general_work(int noutput_items, gr_vector_int& ninput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override;
+
+private:
+    std::shared_ptr<b200_pcps_acquisition_fine_doppler> d_impl;
+};
+
+//   galileo_e5a_noncoherent_iq_acquisition_caf_cc.cc:55-75, :295-777
+class b200_e5a_caf_acquisition_gr : public gr::block
+{
+public:
+    explicit b200_e5a_caf_acquisition_gr(std::shared_ptr<b200_e5a_noncoherent_iq_acquisition_caf> impl);
+    int general_work(int noutput_items, gr_vector_int& ninput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override;
+
+private:
+    std::shared_ptr<b200_e5a_noncoherent_iq_acquisition_caf> d_impl;
+};
+
+//   pcps_quicksync_acquisition_cc.cc:54-67 (VECTOR items in), :214-550.  The reference's item is sampled_ms * samples_per_ms gr_complex; here the item is
+//   what its adapters' stream_to_vector makes (b200_pcps_quicksync_acquisition::item_length)
+class b200_quicksync_acquisition_gr : public gr::block
+{
+public:
+    explicit b200_quicksync_acquisition_gr(std::shared_ptr<b200_pcps_quicksync_acquisition> impl);
+    int general_work(int noutput_items, gr_vector_int& ninput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override;
+
+private:
+    std::shared_ptr<b200_pcps_quicksync_acquisition> d_impl;
 };
 
 std::shared_ptr<b200_tracking_gr> make_b200_tracking_gr(std::shared_ptr<b200_dll_pll_veml_tracking> impl, size_t item_size, unsigned vector_length);

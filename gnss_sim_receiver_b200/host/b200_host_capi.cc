@@ -886,6 +886,63 @@ int64_t gb200h_acqfd_work(gb200h_acqfd* a, const void* items, int64_t n_items, i
         }
 }
 
+extern "C++" {
+namespace
+{
+// one strategy block through its gr::block face: feed, read the "events" port, hand the event sink back to the door
+template <class Gr, class Door>
+int64_t work_through_gr(Door* a, const void* items, int64_t n_items, int* last_event_from_port)
+{
+    auto blk = std::make_shared<Gr>(a->adapter->block());  // re-points the block's event sink at the port
+    const int64_t done = blk->stub_feed(items, n_items, nullptr);
+    auto& pub = blk->stub_published("events");
+    if (last_event_from_port) *last_event_from_port = pub.empty() ? 0 : static_cast<int>(pmt::to_long(pub.back()));
+    if (!pub.empty()) a->last_event = static_cast<int>(pmt::to_long(pub.back()));
+    a->adapter->block()->set_event_sink([a](int ev) { a->last_event = ev; });
+    return done;
+}
+}  // namespace
+}  // extern "C++"
+
+int64_t gb200h_acqfd_work_gr(gb200h_acqfd* a, const void* items, int64_t n_items, int* last_event_from_port)
+{
+    try
+        {
+            return work_through_gr<b200_fine_doppler_acquisition_gr>(a, items, n_items, last_event_from_port);
+        }
+    catch (const std::exception& e)
+        {
+            fail(e);
+            return -1;
+        }
+}
+
+int64_t gb200h_acqcaf_work_gr(gb200h_acqcaf* a, const void* items, int64_t n_items, int* last_event_from_port)
+{
+    try
+        {
+            return work_through_gr<b200_e5a_caf_acquisition_gr>(a, items, n_items, last_event_from_port);
+        }
+    catch (const std::exception& e)
+        {
+            fail(e);
+            return -1;
+        }
+}
+
+int64_t gb200h_acqqs_work_gr(gb200h_acqqs* a, const void* samples, int64_t n_samples, int* last_event_from_port)
+{
+    try
+        {
+            return work_through_gr<b200_quicksync_acquisition_gr>(a, samples, n_samples / a->adapter->block()->item_length(), last_event_from_port);
+        }
+    catch (const std::exception& e)
+        {
+            fail(e);
+            return -1;
+        }
+}
+
 int gb200h_acqfd_get_status(gb200h_acqfd* a, gb200h_acqfd_status* s)
 {
     const auto& blk = *a->adapter->block();

@@ -121,6 +121,8 @@ int gb200h_acqfd_arm(gb200h_acqfd* a, unsigned doppler_max, unsigned doppler_ste
  * items are left, until the block has raised its event and gone idle; returns the items consumed, -1 on error */
 int64_t gb200h_acqfd_work(gb200h_acqfd* a, const void* items, int64_t n_items, int noutput_items);
 int gb200h_acqfd_get_status(gb200h_acqfd* a, gb200h_acqfd_status* s);
+/* the same items through the block's gr::block face (b200_fine_doppler_acquisition_gr; GNU Radio stub outside GNSS-SDR: one output item per call): items consumed, event from the "events" port */
+int64_t gb200h_acqfd_work_gr(gb200h_acqfd* a, const void* items, int64_t n_items, int* last_event_from_port);
 
 /* ---- Galileo E5a non-coherent I/Q acquisition with CAF (Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200; b200_e5a_noncoherent_iq_acquisition_caf.h) */
 typedef struct gb200h_acqcaf gb200h_acqcaf;
@@ -142,6 +144,7 @@ int gb200h_acqcaf_arm(gb200h_acqcaf* a, unsigned doppler_max, unsigned doppler_s
  * is used up; returns the items consumed, -1 on error */
 int64_t gb200h_acqcaf_work(gb200h_acqcaf* a, const void* items, int64_t n_items, int chunk);
 int gb200h_acqcaf_get_status(gb200h_acqcaf* a, gb200h_acqcaf_status* s);
+int64_t gb200h_acqcaf_work_gr(gb200h_acqcaf* a, const void* items, int64_t n_items, int* last_event_from_port); /* b200_e5a_caf_acquisition_gr */
 /* the filtered CAF vector of the last search (num_doppler_bins floats; 0 returned when CAF_window_hz = 0) */
 int gb200h_acqcaf_caf_vector(gb200h_acqcaf* a, float* dst, int max_bins);
 
@@ -165,6 +168,7 @@ int gb200h_acqqs_arm(gb200h_acqqs* a, unsigned doppler_max, unsigned doppler_ste
  * `max_items` of them until the block has raised its event and gone idle or the items are used up; returns the ITEMS consumed, -1 on error */
 int64_t gb200h_acqqs_work(gb200h_acqqs* a, const void* samples, int64_t n_samples, int max_items);
 int gb200h_acqqs_get_status(gb200h_acqqs* a, gb200h_acqqs_status* s);
+int64_t gb200h_acqqs_work_gr(gb200h_acqqs* a, const void* samples, int64_t n_samples, int* last_event_from_port); /* b200_quicksync_acquisition_gr: vector ITEMS consumed */
 
 /* MAT level-5 writer used by the acquisition dump (b200_mat_writer.h): one file with a single matrix and one scalar of each class */
 int gb200h_mat_write_sample(const char* filename, const float* grid, int rows, int cols, int32_t i32, uint32_t u32, uint64_t u64, float f32);
