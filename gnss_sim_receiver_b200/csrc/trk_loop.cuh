@@ -87,9 +87,9 @@ struct LoopState
     int error;                 // sticky: command outside what the selected kernel serves
 };
 
-struct LoopCounters
+struct alignas(16) LoopCounters
 {
-    unsigned n_records, n_planned, n_ready_again, n_errors, n_loss_of_lock, pad_[3];
+    unsigned n_records, n_planned, n_ready_again, n_errors, n_loss_of_lock, pad_[3];  // pad_[0]: ticket of the publishing round (trk_loop_kernel)
 };
 
 // ------------------------------------------------------------------------------------------------ scalar pieces
@@ -621,7 +621,8 @@ constexpr int LOOP_STATE_WORDS = (int)(sizeof(LoopState) / 4);
 constexpr int LOOP_STATE_STRIDE = (int)sizeof(LoopState) + 8;
 static_assert(sizeof(LoopState) % 8 == 0, "LoopState is copied as words and holds doubles");
 __global__ void __launch_bounds__(LOOP_CTA) trk_loop_kernel(const LoopConf* __restrict__ conf, LoopState* __restrict__ states, int n_channels, unsigned long long head,
-    const float* __restrict__ outs, TrkDevCmd* __restrict__ cmds, gb200_loop_record* __restrict__ records, unsigned max_records, LoopCounters* __restrict__ cnt)
+    const float* __restrict__ outs, TrkDevCmd* __restrict__ cmds, gb200_loop_record* __restrict__ records, unsigned max_records, LoopCounters* __restrict__ cnt,
+    LoopCounters* __restrict__ publish)
 {
     __shared__ LoopConf k;
     __shared__ __align__(16) unsigned char sm_states[LOOP_CTA * LOOP_STATE_STRIDE];
@@ -731,6 +732,33 @@ __global__ void __launch_bounds__(LOOP_CTA) trk_loop_kernel(const LoopConf* __re
             if (m_planned) atomicAdd(&cnt->n_planned, (unsigned)__popc(m_planned));
             if (m_again) atomicAdd(&cnt->n_ready_again, (unsigned)__popc(m_again));
             if (m_bad) atomicAdd(&cnt->n_errors, (unsigned)__popc(m_bad));
+        }
+    // The last round of a step publishes its totals itself (publish = the step's host-mapped counter block): the CTA that finishes last
+    // moves them over and leaves the device counters zero for the slot's next step — no memset before and no copy after the kernels on the
+    // stream, a period is the correlator kernel and this one.
+    if (publish)
+        {
+            __shared__ unsigned s_last;
+            __syncthreads();
+            if (threadIdx.x == 0)
+                {
+                    __threadfence();
+                    s_last = atomicAdd(&cnt->pad_[0], 1u) == gridDim.x - 1 ? 1u : 0u;
+                }
+            __syncthreads();
+            if (s_last && threadIdx.x == 0)
+                {
+                    // every other CTA's atomics are in L2 (their fence came before their ticket): two vector loads past L1, two vector stores to
+                    // the mapped block, two to clear; the host reads after the kernel's completion event, which orders the stores
+                    __threadfence();
+                    uint4* c = reinterpret_cast<uint4*>(cnt);
+                    const uint4 a = __ldcg(c), b = __ldcg(c + 1);
+                    uint4* o = reinterpret_cast<uint4*>(publish);
+                    o[0] = a;
+                    o[1] = make_uint4(b.x, 0u, 0u, 0u);
+                    __stcg(c, make_uint4(0u, 0u, 0u, 0u));
+                    __stcg(c + 1, make_uint4(0u, 0u, 0u, 0u));
+                }
         }
 }
 }  // namespace gb200
