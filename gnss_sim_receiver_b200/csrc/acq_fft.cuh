@@ -234,8 +234,13 @@ struct FftNoPre
 };
 struct FftNoPost
 {
+    static constexpr bool batched = false;
     static constexpr bool on = false;
     __device__ __forceinline__ void operator()(float2, int) {}
+    template <int R>
+    __device__ __forceinline__ void batch(const float2*, int, int)
+    {
+    }
 };
 
 // One in-place stage over a shared-memory block x[0..m_blk): sub-blocks of n_s points, radix R; T = the stage's table.
@@ -287,13 +292,18 @@ __device__ __forceinline__ void fft_smem_stage(float2* x, int m_blk, int n_s, un
                             if (k + 1 < R) w = cmul(w, w1);
                         }
                 }
-#pragma unroll
-            for (int k = 0; k < R; k++)
+            if (Post::on && Post::batched)
+                post.template batch<R>(v, blk * n_s + j2, ms);  // the butterfly's R outputs: indices first + k * ms, ascending
+            else
                 {
-                    if (Post::on)
-                        post(v[k], blk * n_s + j2 + k * ms);
-                    else
-                        p[k * ms] = v[k];
+#pragma unroll
+                    for (int k = 0; k < R; k++)
+                        {
+                            if (Post::on)
+                                post(v[k], blk * n_s + j2 + k * ms);
+                            else
+                                p[k * ms] = v[k];
+                        }
                 }
         }
     if (!Post::on) __syncthreads();
@@ -402,16 +412,21 @@ __device__ __forceinline__ void fft_smem_stage2(float2* x, int m_blk, int n_s, u
                                 }
                         }
                 }
+            if (Post::on && Post::batched)
+                post.template batch<R1 * R2>(&v[0][0], blk * n_s + j, ms2);  // k * ms1 + k2 * ms2 = (k * R2 + k2) * ms2: ascending in storage order
+            else
+                {
 #pragma unroll
-            for (int k = 0; k < R1; k++)
+                    for (int k = 0; k < R1; k++)
 #pragma unroll
-                for (int k2 = 0; k2 < R2; k2++)
-                    {
-                        if (Post::on)
-                            post(v[k][k2], blk * n_s + j + k * ms1 + k2 * ms2);
-                        else
-                            p[k * ms1 + k2 * ms2] = v[k][k2];
-                    }
+                        for (int k2 = 0; k2 < R2; k2++)
+                            {
+                                if (Post::on)
+                                    post(v[k][k2], blk * n_s + j + k * ms1 + k2 * ms2);
+                                else
+                                    p[k * ms1 + k2 * ms2] = v[k][k2];
+                            }
+                }
         }
     if (!Post::on) __syncthreads();
 }

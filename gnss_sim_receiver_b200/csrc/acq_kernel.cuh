@@ -305,6 +305,8 @@ struct AcqCodeProduct
 struct AcqSink
 {
     static constexpr bool on = true;
+    static constexpr bool batched = true;
+    int fast;  // every output is searched and no grid is kept (the plain one-dwell CFAR sweep): no masking in the per-butterfly form below
     int out_offset, neff, accumulate;
     float* grid_row;
     float best, sum;
@@ -330,6 +332,56 @@ struct AcqSink
         const bool better = gm > best || (gm == best && i < besti);
         best = better ? gm : best;
         besti = better ? i : besti;
+    }
+    // The R outputs of one butterfly, indices first + i * stride (ascending).  The per-sample form above is a serial compare / select chain R deep
+    // (the final pass of the C3 kernel spent most of its stall samples waiting on it: profiles/r02g_acq_inv_stall_segments.txt, segment 10);
+    // here the butterfly's maximum and its lowest index come out of a tournament (depth log2 R; the lower index sits on the left and only a
+    // strictly larger right value replaces it, so ties go to the first index as in volk_gnsssdr_32f_index_max_32u), the sum out of a tree, and the
+    // running (best, besti, sum) are touched once per butterfly.
+    template <int R>
+    __device__ __forceinline__ void batch(const float2* v, int first, int stride)
+    {
+        float mv[R], sv[R];
+        int mi[R];
+#pragma unroll
+        for (int i = 0; i < R; i++)
+            {
+                float g = __fadd_rn(__fmul_rn(v[i].x, v[i].x), __fmul_rn(v[i].y, v[i].y));
+                mi[i] = i;
+                if (fast)  // uniform
+                    {
+                        mv[i] = g;
+                        sv[i] = g;
+                    }
+                else
+                    {
+                        // samples outside [out_offset, out_offset + neff) add nothing and can never win; a kept grid takes the dwell's sum (:657-665)
+                        const int idx = first + i * stride - out_offset;
+                        const bool ok = (unsigned)idx < (unsigned)neff;
+                        if (grid_row && ok)
+                            {
+                                if (accumulate) g = __fadd_rn(grid_row[idx], g);
+                                grid_row[idx] = g;
+                            }
+                        mv[i] = ok ? g : -2.0f;
+                        sv[i] = ok ? g : 0.0f;
+                    }
+            }
+#pragma unroll
+        for (int w = 1; w < R; w <<= 1)
+#pragma unroll
+            for (int i = 0; i + w < R; i += 2 * w)
+                {
+                    const bool t = mv[i + w] > mv[i];
+                    mv[i] = t ? mv[i + w] : mv[i];
+                    mi[i] = t ? mi[i + w] : mi[i];
+                    sv[i] += sv[i + w];
+                }
+        sum += sv[0];
+        const int n = first + mi[0] * stride - out_offset;
+        const bool better = mv[0] > best || (mv[0] == best && n < besti);
+        best = better ? mv[0] : best;
+        besti = better ? n : besti;
     }
 };
 }  // namespace gb200

@@ -69,6 +69,7 @@ __global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_inv_kernel(AcqParams p, c
                     sink.neff = p.neff;
                     sink.accumulate = p.dwell_index > 0;
                     sink.grid_row = p.keep_grid ? grid + ((size_t)slots[si] * p.n_bins + bin) * p.neff : nullptr;
+                    sink.fast = (!p.keep_grid && p.out_offset == 0 && p.neff == pl.n) ? 1 : 0;
                     sink.best = -1.0f;
                     sink.sum = 0.0f;
                     sink.besti = 0x7fffffff;
@@ -97,6 +98,7 @@ __global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_inv_kernel(AcqParams p, c
             for (int k1 = 0; k1 < 8; k1++) xb[k1] = k1 < R ? cluster.map_shared_rank(x, k1) : x;
             AcqSink sink;
             sink.out_offset = p.out_offset;
+            sink.fast = 0;
             sink.neff = p.neff;
             sink.accumulate = p.dwell_index > 0;
             sink.grid_row = p.keep_grid ? grid + ((size_t)slots[si] * p.n_bins + bin) * p.neff : nullptr;
