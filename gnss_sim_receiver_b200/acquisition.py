@@ -84,7 +84,7 @@ class AcquisitionEngine:
             n, sl = len(arr), arr.ctypes.data
         out = (AcqResult * n)()
         check(self._lib.gb200_acq_run(self._h, iq.ctypes.data, dwell_index, sl, n, out))
-        return list(out)
+        return out  # (a ctypes array of AcqResult: indexable and iterable like the list it used to be copied into)
 
     def run_device(self, dev_ptr, slots=None, dwell_index=0, n_slots=None):
         if slots is None:
@@ -95,7 +95,7 @@ class AcquisitionEngine:
             n, sl = len(arr), arr.ctypes.data
         out = (AcqResult * n)()
         check(self._lib.gb200_acq_run_device(self._h, C.c_void_p(dev_ptr), dwell_index, sl, n, out))
-        return list(out)
+        return out
 
     def replay(self, iters):
         ms = C.c_float()

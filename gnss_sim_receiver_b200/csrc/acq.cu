@@ -67,6 +67,7 @@ struct gb200_acq
     size_t aux_bytes{0};
     // last run (replay)
     std::vector<int> last_slots;
+    std::vector<int> dev_slots;  // what d_slots holds
     int last_dwell{0};
     bool have_run{false};
 };
