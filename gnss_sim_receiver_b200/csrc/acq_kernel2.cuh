@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_inv_kernel(AcqParams p, c
             for (int k1 = 0; k1 < 8; k1++) xb[k1] = k1 < R ? cluster.map_shared_rank(x, k1) : x;
             AcqSink sink;
             sink.out_offset = p.out_offset;
-            sink.fast = 0;
+            sink.fast = (!p.keep_grid && p.out_offset == 0 && p.neff == pl.n) ? 1 : 0;
             sink.neff = p.neff;
             sink.accumulate = p.dwell_index > 0;
             sink.grid_row = p.keep_grid ? grid + ((size_t)slots[si] * p.n_bins + bin) * p.neff : nullptr;
@@ -138,9 +138,18 @@ __global__ void __launch_bounds__(ACQ_MAX_THREADS) acq_inv_kernel(AcqParams p, c
                                 for (int j1 = 0; j1 < R; j1++) v[j1] = y[j1];
                             }
                         }
+                    // outputs j1 * m + j2, ascending in j1: the per-butterfly form of the search (AcqSink::batch) for the radices a split uses
+                    switch (R)
+                        {
+                        case 2: sink.template batch<2>(v, j2, pl.m); break;
+                        case 4: sink.template batch<4>(v, j2, pl.m); break;
+                        case 5: sink.template batch<5>(v, j2, pl.m); break;
+                        case 8: sink.template batch<8>(v, j2, pl.m); break;
+                        default:
 #pragma unroll
-                    for (int j1 = 0; j1 < 8; j1++)
-                        if (j1 < R) sink(v[j1], j1 * pl.m + j2);
+                            for (int j1 = 0; j1 < 8; j1++)
+                                if (j1 < R) sink(v[j1], j1 * pl.m + j2);
+                        }
                 }
             acq_block_reduce(sink.best, sink.besti, sink.sum);
             if (threadIdx.x == 0)
