@@ -79,7 +79,7 @@ constexpr double TWO_PI = 6.283185307179586476925286766559;
 // Stage radices in DIF order, even factors first (the late, short-stride stages are the odd ones).  Pairs of equal small
 // factors are fused into one register-resident pass (16 = 4x4, 8 = 4x2, 9 = 3x3, 25 = 5x5; acq_fft.cuh: fft_smem_stage2):
 // 25000 = 8 * 25 * 25 * 5 takes 4 passes over shared memory instead of 7.  GB200_ACQ_PLAIN_RADIX=1 keeps the plain stages.
-bool is_small_radix(int r) { return r == 2 || r == 3 || r == 4 || r == 5 || r == 7 || r == 8 || r == 9 || r == 16 || r == 25; }
+bool is_small_radix(int r) { return r == 2 || r == 3 || r == 4 || r == 5 || r == 7 || r == 8 || r == 9 || r == 10 || r == 16 || r == 20 || r == 25; }
 
 bool factor_235(int n, std::vector<int>& radix, bool fuse)
 {
@@ -99,6 +99,13 @@ bool factor_235(int n, std::vector<int>& radix, bool fuse)
         {
             while (c2 >= 4) { radix.push_back(16); c2 -= 4; }
             if (c2 == 3) { radix.push_back(8); c2 = 0; }
+        }
+    // a stray 4 or 2 next to an ODD number of factors 5: fused with one of them (radix 20 / 10) the pair costs one pass instead of two and the
+    // remaining fives pair up into radix-25 stages (4000 = 16 * 10 * 25, 8000 = 16 * 20 * 25: three passes instead of four)
+    if (fuse && (c5 & 1) && getenv("GB200_ACQ_NO_RADIX10") == nullptr)
+        {
+            if (c2 == 2) { radix.push_back(20); c2 = 0; c5--; }
+            else if (c2 == 1) { radix.push_back(10); c2 = 0; c5--; }
         }
     while (c2 >= 2) { radix.push_back(4); c2 -= 2; }
     if (c2) radix.push_back(2);
@@ -127,6 +134,8 @@ void stage_factors(int r, int* f1, int* f2)
         case 8: *f1 = 4; *f2 = 2; break;
         case 9: *f1 = 3; *f2 = 3; break;
         case 25: *f1 = 5; *f2 = 5; break;
+        case 10: *f1 = 2; *f2 = 5; break;
+        case 20: *f1 = 4; *f2 = 5; break;
         default: *f1 = r; *f2 = 1; break;
         }
 }

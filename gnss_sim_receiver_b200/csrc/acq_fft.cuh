@@ -112,6 +112,31 @@ __device__ __forceinline__ float2 fft_wconst<9>(int k)
         default: return make_float2(1.0f, 0.0f);
         }
 }
+// (2 x 5 and 4 x 5: a stray factor 2 or 4 fused with a factor 5 saves a whole pass for lengths such as 4000 = 16 * 10 * 25 and 8000 = 16 * 20 * 25)
+template <>
+__device__ __forceinline__ float2 fft_wconst<10>(int k)
+{
+    switch (k)
+        {
+        case 1: return make_float2(0.80901699437494745f, -0.58778525229247314f);
+        case 2: return make_float2(0.30901699437494745f, -0.95105651629515353f);
+        case 3: return make_float2(-0.30901699437494734f, -0.95105651629515364f);
+        case 4: return make_float2(-0.80901699437494734f, -0.58778525229247325f);
+        default: return make_float2(1.0f, 0.0f);
+        }
+}
+template <>
+__device__ __forceinline__ float2 fft_wconst<20>(int k)
+{
+    switch (k)
+        {
+        case 1: return make_float2(0.95105651629515353f, -0.3090169943749474f);
+        case 2: return make_float2(0.80901699437494745f, -0.58778525229247314f);
+        case 3: return make_float2(0.58778525229247314f, -0.80901699437494745f);
+        case 4: return make_float2(0.30901699437494745f, -0.95105651629515353f);
+        default: return make_float2(1.0f, 0.0f);
+        }
+}
 template <>
 __device__ __forceinline__ float2 fft_wconst<16>(int k)
 {
@@ -496,6 +521,8 @@ __device__ __forceinline__ void fft_smem_stage_any(const FftPlan& pl, int s, flo
         case 9: fft_smem_stage2<3, 3, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
         case 16: fft_smem_stage2<4, 4, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
         case 25: fft_smem_stage2<5, 5, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
+        case 10: fft_smem_stage2<2, 5, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
+        case 20: fft_smem_stage2<4, 5, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
         case 7: fft_smem_stage<7, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, pre, post); break;
         default: fft_smem_stage_prime<INV>(x, x + pl.m, m_blk, n_s, pl.radix[s], T, nh); break;  // prime radix 11 ... 61 (never with hooks)
         }
