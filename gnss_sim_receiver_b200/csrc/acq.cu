@@ -79,9 +79,9 @@ constexpr double TWO_PI = 6.283185307179586476925286766559;
 // Stage radices in DIF order, even factors first (the late, short-stride stages are the odd ones).  Pairs of equal small
 // factors are fused into one register-resident pass (16 = 4x4, 8 = 4x2, 9 = 3x3, 25 = 5x5; acq_fft.cuh: fft_smem_stage2):
 // 25000 = 8 * 25 * 25 * 5 takes 4 passes over shared memory instead of 7.  GB200_ACQ_PLAIN_RADIX=1 keeps the plain stages.
-bool is_small_radix(int r) { return r == 2 || r == 3 || r == 4 || r == 5 || r == 7 || r == 8 || r == 9 || r == 10 || r == 16 || r == 20 || r == 25; }
+bool is_small_radix(int r) { return r == 2 || r == 3 || r == 4 || r == 5 || r == 7 || r == 8 || r == 9 || r == 10 || r == 16 || r == 20 || r == 25 || r == 32; }
 
-bool factor_235(int n, std::vector<int>& radix, bool fuse)
+bool factor_235_impl(int n, std::vector<int>& radix, bool fuse, bool allow32)
 {
     radix.clear();
     const int n_in = n;
@@ -97,6 +97,13 @@ bool factor_235(int n, std::vector<int>& radix, bool fuse)
     if (n != 1) return false;
     if (fuse)
         {
+            // 2^5 as ONE radix-32 stage (4 x 8 in registers) when it saves a pass: five or seven twos would otherwise cost 16 * 2 or 16 * 8
+            // (64 data registers per thread: no spills in the inverse kernels at the 128-register cap; GB200_ACQ_NO_RADIX32 switches it off)
+            if ((c2 == 5 || c2 == 7) && allow32)
+                {
+                    radix.push_back(32);
+                    c2 -= 5;
+                }
             while (c2 >= 4) { radix.push_back(16); c2 -= 4; }
             if (c2 == 3) { radix.push_back(8); c2 = 0; }
         }
@@ -119,10 +126,23 @@ bool factor_235(int n, std::vector<int>& radix, bool fuse)
     if (!primes.empty())
         {
             // the first and the last stage carry the hooks of the inverse kernel: the prime stages go in between
-            if (radix.size() < 2) return fuse ? factor_235(n_in, radix, false) : false;  // 16 -> 4 * 4 makes room
+            if (radix.size() < 2) return fuse ? factor_235_impl(n_in, radix, false, false) : false;  // 16 -> 4 * 4 makes room
             radix.insert(radix.begin() + 1, primes.begin(), primes.end());
         }
     return (int)radix.size() <= FFT_MAX_STAGES;
+}
+
+// the factorisation with the fewest passes; the radix-32 stage is taken only when it saves one (at equal count 16 * 10 * 25 beats 32 * 25 * 5:
+// C1 sweep 0.096 against 0.102 ms)
+bool factor_235(int n, std::vector<int>& radix, bool fuse)
+{
+    if (!factor_235_impl(n, radix, fuse, false)) return false;
+    if (fuse && getenv("GB200_ACQ_NO_RADIX32") == nullptr)
+        {
+            std::vector<int> with32;
+            if (factor_235_impl(n, with32, fuse, true) && with32.size() < radix.size()) radix = with32;
+        }
+    return true;
 }
 
 // the plain factors of a (possibly fused) stage radix, in the order the stage applies them
@@ -136,6 +156,7 @@ void stage_factors(int r, int* f1, int* f2)
         case 25: *f1 = 5; *f2 = 5; break;
         case 10: *f1 = 2; *f2 = 5; break;
         case 20: *f1 = 4; *f2 = 5; break;
+        case 32: *f1 = 4; *f2 = 8; break;
         default: *f1 = r; *f2 = 1; break;
         }
 }

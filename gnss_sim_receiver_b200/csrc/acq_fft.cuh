@@ -137,6 +137,22 @@ __device__ __forceinline__ float2 fft_wconst<20>(int k)
         default: return make_float2(1.0f, 0.0f);
         }
 }
+// (4 x 8: 16000 = 32 * 20 * 25 and 20000 = 32 * 25 * 25 in three passes)
+template <>
+__device__ __forceinline__ float2 fft_wconst<32>(int k)
+{
+    switch (k)
+        {
+        case 1: return make_float2(0.98078528040323043f, -0.19509032201612825f);
+        case 2: return make_float2(0.92387953251128674f, -0.38268343236508978f);
+        case 3: return make_float2(0.83146961230254524f, -0.55557023301960218f);
+        case 4: return make_float2(0.70710678118654757f, -0.70710678118654746f);
+        case 5: return make_float2(0.55557023301960229f, -0.83146961230254524f);
+        case 6: return make_float2(0.38268343236508984f, -0.92387953251128674f);
+        case 7: return make_float2(0.19509032201612833f, -0.98078528040323043f);
+        default: return make_float2(1.0f, 0.0f);
+        }
+}
 template <>
 __device__ __forceinline__ float2 fft_wconst<16>(int k)
 {
@@ -201,6 +217,35 @@ struct Dft<4, INV>
         v[2] = csub(t0, t2);
         v[1] = cadd(t1, t3);
         v[3] = csub(t1, t3);
+    }
+};
+
+// 8 points: one radix-2 level with the W_8 rotations, then two 4-point butterflies (even outputs from the sums, odd from the differences)
+template <bool INV>
+struct Dft<8, INV>
+{
+    static __device__ __forceinline__ void run(float2* v)
+    {
+        const float h = 0.70710678118654757f;
+        float2 a[4], b[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            {
+                a[k] = cadd(v[k], v[k + 4]);
+                b[k] = csub(v[k], v[k + 4]);
+            }
+        // b1 * W_8, b2 * W_8^2, b3 * W_8^3 (conjugates for the inverse)
+        b[1] = INV ? make_float2(h * (b[1].x - b[1].y), h * (b[1].x + b[1].y)) : make_float2(h * (b[1].x + b[1].y), h * (b[1].y - b[1].x));
+        b[2] = rot90<INV>(b[2]);
+        b[3] = INV ? make_float2(h * (-b[3].x - b[3].y), h * (b[3].x - b[3].y)) : make_float2(h * (b[3].y - b[3].x), h * (-b[3].x - b[3].y));
+        Dft<4, INV>::run(a);
+        Dft<4, INV>::run(b);
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            {
+                v[2 * k] = a[k];
+                v[2 * k + 1] = b[k];
+            }
     }
 };
 
@@ -523,6 +568,7 @@ __device__ __forceinline__ void fft_smem_stage_any(const FftPlan& pl, int s, flo
         case 25: fft_smem_stage2<5, 5, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
         case 10: fft_smem_stage2<2, 5, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
         case 20: fft_smem_stage2<4, 5, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
+        case 32: fft_smem_stage2<4, 8, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, nh, pre, post); break;
         case 7: fft_smem_stage<7, INV>(x, m_blk, n_s, inv_ms, inv_nblk, T, pre, post); break;
         default: fft_smem_stage_prime<INV>(x, x + pl.m, m_blk, n_s, pl.radix[s], T, nh); break;  // prime radix 11 ... 61 (never with hooks)
         }
