@@ -138,4 +138,15 @@ def test_folded_run_against_numpy():
         folded = (x.astype(np.complex128) * w)[:k * m].reshape(k, m).sum(axis=0)
         want = np.abs(np.fft.ifft(np.fft.fft(folded) * fc) * m) ** 2
         assert np.max(np.abs(g[b] - want)) <= 2e-5 * want.max(), (b, float(np.max(np.abs(g[b] - want)) / want.max()))
+    # gb200_acq_folded_candidates on the same block: acc[i] = sum_j x[d_i + j] * wipeoff_bin[d_i + j] * code[j], d_i = index + i * fft_size
+    long_code = (1j * rng.choice(np.array([-1.0, 1.0]), 4000)).astype(np.complex64)
+    b, index, ncand = 3, 137, 4
+    got = eng.folded_candidates(b, index, long_code, ncand)
+    w = O.acq_wipeoff(length, float(freqs[b]), 4e6).astype(np.complex128)
+    for i in range(ncand):
+        d = index + i * m
+        want_i = np.sum(x[d:d + 4000].astype(np.complex128) * w[d:d + 4000] * long_code.astype(np.complex128))
+        assert abs(got[i] - want_i) <= 2e-5 * np.sqrt(4000.0) * 2, (i, got[i], want_i)
+    with pytest.raises(Exception, match="outside the block"):
+        eng.folded_candidates(b, index, long_code, 14)  # 137 + 13 * 1000 + 4000 > 16024
     eng.close()
