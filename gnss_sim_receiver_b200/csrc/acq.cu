@@ -279,6 +279,10 @@ int make_plan(gb200_acq* h, int max_smem)
                     if (whole <= (size_t)max_smem && 2 * (whole + 1024) > (size_t)228 * 1024 && 2 * (whole / 2 + 4096) <= (size_t)228 * 1024) r_first = 2;
                 }
         }
+    // (the loop below runs once, or twice when its first answer is a split by 2 or 3 of a length that also splits by 4: see after it)
+    const int r_first0 = r_first;
+    for (int pass = 0; pass < 3; pass++)
+    {
     for (int r = r_first; r <= 8 && !g; r++)
         {
             if (N % r) continue;
@@ -300,6 +304,23 @@ int make_plan(gb200_acq* h, int max_smem)
                     h->smem = bytes;
                 }
         }
+    // Split transforms below 65536 points: four blocks joined through distributed shared memory beat two (measured on the final tree, 32 PRN x
+    // 80 bins, ms per sweep — 32000: 0.935 split 2 through global memory, 0.890 split 2 cluster, 0.835 split 4 cluster; 40000: 1.154 / 1.073 /
+    // 0.995; 50000: 1.474 / 1.337 / 1.222; 64000: 2.204 / 1.945 / 1.946; split 5 wins at 32000 and 64000 but loses at 40000 and 50000, split 8 is
+    // twice as slow): two or three CTAs per SM instead of one, and three-pass blocks.
+    if (pass == 0 && g > 1 && g < 4 && N % 4 == 0 && N < 65536 && getenv("GB200_ACQ_SPLIT") == nullptr && getenv("GB200_ACQ_NO_SPLIT4") == nullptr)
+        {
+            g = 0;
+            r_first = 4;
+            continue;
+        }
+    if (pass == 1 && !g)  // (no split by 4 ... 8 fits after all: back to the first answer)
+        {
+            r_first = r_first0;
+            continue;
+        }
+    break;
+    }
     if (!g) return set_error(GB200_EINVAL, "fft_size %d: no split into <= 8 shared-memory blocks", N);
     pl.g_radix = g;
     pl.m = N / g;
