@@ -250,6 +250,14 @@ def test_gpu_entry_points_fail_loudly_without_a_device():
         H.TrackingBank(CONF_C1, "Tracking_1C", 2)
     with pytest.raises(H.HostError, match="no CUDA device|CPU fallback"):
         H.AcquisitionBlock(CONF_C1, "Acquisition_1C", 1)
+    # the SURVEY 8f-4 strategy blocks likewise: no host path stands in for the engines
+    base = "GNSS-SDR.internal_fs_sps=4000000\n"
+    with pytest.raises(H.HostError, match="no CUDA device|CPU fallback"):
+        H.FineDopplerAcquisitionBlock(base + "Acquisition_1C.implementation=GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200\n", "Acquisition_1C", 1)
+    with pytest.raises(H.HostError, match="no CUDA device|CPU fallback"):
+        H.QuickSyncAcquisitionBlock(base + "Acquisition_1C.implementation=GPS_L1_CA_PCPS_QuickSync_Acquisition_B200\n", "Acquisition_1C", 1)
+    with pytest.raises(H.HostError, match="no CUDA device|CPU fallback"):
+        H.E5aCafAcquisitionBlock("GNSS-SDR.internal_fs_sps=12000000\nAcquisition_5X.implementation=Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200\n", "Acquisition_5X", 1)
 
 
 def test_mat_writer_is_readable_by_scipy(tmp_path):
