@@ -662,6 +662,12 @@ def run_ours(args):
     if closed is not None and closed.get("parity_vs_host_loop", {}).get("ok"):
         e2e_obj = dict(closed["e2e"], what="closed loop through gb200_loop_step with a host IQ block per code period (see closed_loop)")
         e2e_obj.pop("ms_per_period", None)
+        # the same channels as two banks on the GPU (one bank's loop kernel under the other's correlator): the headline when its records
+        # are identical to the one-bank run's and it is the faster form; the one-bank figure stays in closed_loop.e2e
+        two = closed.get("e2e_two_banks")
+        if two and two["records_identical_to_one_bank"] and two["value"] > e2e_obj["value"]:
+            e2e_obj = {k: two[k] for k in ("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step", "form")}
+            e2e_obj["what"] = "closed loop, the GPU's channels as two banks, a host IQ block per code period into each (see closed_loop.e2e_two_banks; one bank: closed_loop.e2e)"
     else:
         e2e_obj = e2e_open
     if acq is not None:

@@ -56,6 +56,78 @@ def _stream(local, codes, seed):
     return out, dict(doppler=dopp, delay=delay, cn0=cn0)
 
 
+def run_two_banks(lib, codes, sat, acq, cfg, block, local, rank, dist, periods_lock, K, sub, one_bank_recs, n_banks=2):
+    """The same channels as `n_banks` independent banks on the GPU (an engine with its own stream and ring + a device loop each, channels / n_banks
+    channels per bank), submitted back to back: one bank's loop kernel (a dependent chain on two warps per SM) runs under the other bank's
+    correlator instead of on the critical path.  Every bank is pushed the period's IQ block itself (n_banks x the H2D bytes).  The records of
+    the sampled channels over the lock-in must be IDENTICAL to the one-bank run's: same kernels, same hand-over, same stream."""
+    import torch
+    import bench
+    from gnss_sim_receiver_b200.tracking import TrackingEngine, TrackingLoop
+    nch = len(sat)
+    per = nch // n_banks
+    engs, loops = [], []
+    for b in range(n_banks):
+        e = TrackingEngine(device=local, max_channels=per, max_code_len=1023, ring_samples=16 * N_BLK, max_block=N_BLK + 8, max_cmds=per)
+        for c in range(per):
+            e.set_code(c, codes[sat[b * per + c]])
+        lp = TrackingLoop(e, cfg, per)
+        for c in range(per):
+            g = b * per + c
+            lp.start(c, int(sat[g]) + 1, acq[g][0], acq[g][1], 0, 0)
+        engs.append(e)
+        loops.append(lp)
+    local_sub = [[c - b * per for c in sub if b * per <= c < (b + 1) * per] for b in range(n_banks)]
+    kept = []
+
+    def pipelined(p0, k, keep):
+        cmds = recs = 0
+        for lp in loops:
+            lp.submit(block(p0))
+        for p in range(p0 + 1, p0 + k + 1):
+            if p < p0 + k:
+                for lp in loops:
+                    lp.submit(block(p))
+            for b, lp in enumerate(loops):
+                r = lp.collect(copy=False)
+                recs += len(r)
+                cmds += lp.last_step["commands"]
+                if keep and len(r):
+                    m = r[np.isin(r["channel"], local_sub[b])].copy()
+                    m["channel"] += b * per
+                    kept.append(m)
+        return cmds, recs
+
+    pipelined(0, periods_lock, rank == 0)
+    torch.cuda.synchronize()
+    bench.barrier(dist)
+    l0 = lib.gb200_launch_count()
+    t0 = time.perf_counter()
+    cmds, recs = pipelined(periods_lock, K, False)
+    torch.cuda.synchronize()
+    wall = bench.reduce_max(dist, local, time.perf_counter() - t0)
+    launches = lib.gb200_launch_count() - l0
+    locked = sum(1 for lp in loops for c in range(0, per, 64) if lp.channel(c)["state"] == 4)
+    for lp in loops:
+        lp.close()
+    for e in engs:
+        e.close()
+    if rank != 0:
+        return None
+    one = np.concatenate(one_bank_recs) if one_bank_recs else np.zeros(0)
+    got = np.concatenate(kept) if kept else np.zeros(0)
+    same = len(one) == len(got) and len(one) > 0
+    if same:
+        for c in sub:
+            a, b_ = one[one["channel"] == c], got[got["channel"] == c]
+            same = same and len(a) == len(b_) and all(a[f].tobytes() == b_[f].tobytes() for f in a.dtype.names)
+    return {"value": float(cmds) * N_BLK / 1e6 / wall, "unit": "channel-Msps/s", "ms_per_period": wall / K * 1e3, "banks": n_banks, "channels_per_bank": per,
+            "h2d_bytes_per_step": n_banks * N_BLK * 8, "d2h_bytes_per_step": int(72 * recs / K) + 32 * n_banks, "gpu_launches": int(launches), "records": int(recs),
+            "channels_in_narrow_tracking_of_sampled": f"{locked}/{n_banks * len(range(0, per, 64))}",
+            "records_identical_to_one_bank": bool(same), "records_compared": int(len(got)),
+            "form": f"{n_banks} banks of {per} channels on the GPU, gb200_loop_submit / gb200_loop_collect per bank, two steps in flight per bank"}
+
+
 def run_closed_loop(args, rank, world, local, dist, flush):
     import torch
     import bench
@@ -178,6 +250,7 @@ def run_closed_loop(args, rank, world, local, dist, flush):
     kernel = loop.kernel
     loop.close()
     eng.close()
+    two = run_two_banks(lib, codes, sat, acq, cfg, block, local, rank, dist, periods_lock, K, sub, dev_recs)
     if rank != 0:
         return None
     ch_samples = float(cmds) * N_BLK * world
@@ -192,4 +265,5 @@ def run_closed_loop(args, rank, world, local, dist, flush):
         "real_time_margin": (N_BLK / FS) / (wall / K),
         "gpu_launches": int(launches), "records": int(n_rec), "channels_in_narrow_tracking_of_sampled": f"{locked}/{len(range(0, nch, 64))}",
         "parity_vs_host_loop": parity,
+        "e2e_two_banks": None if two is None else dict(two, value=two["value"] * world),
     }
