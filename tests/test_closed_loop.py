@@ -444,6 +444,47 @@ def test_device_loop_pipelined_form_gives_the_same_records():
 
 
 @pytest.mark.gpu
+def test_banked_loop_gives_the_records_of_one_bank():
+    """BankedTrackingLoop (the GPU's channels as two banks, one bank's loop kernel under the other's correlator) against ONE TrackingLoop over the same
+    channels and stream: identical records per channel, channel numbers global; uneven split (5 channels = 3 + 2)."""
+    from gnss_sim_receiver_b200.tracking import BankedTrackingLoop, loop_config
+    nsat = 5
+    sc = scenario(nsat, seed=17)
+    x = np.concatenate([c for _, c in stream_chunks(sc, 3.0)])
+    e1, l1 = _device_loop(nsat, sc)
+    cfg = loop_config("1C", FS, pll_bw_hz=35.0, dll_bw_hz=2.0, early_late_space_chips=0.5, pull_in_time_s=1, cn0_samples=20, cn0_min=25, max_code_lock_fail=50,
+                      max_carrier_lock_fail=5000, carrier_lock_th=0.5)
+    bl = BankedTrackingLoop(cfg, nsat, n_banks=2, max_code_len=1023, ring_samples=4 * CHUNK, max_block=2 * 4000)
+    assert [lp.n for lp in bl.loops] == [3, 2]
+    for k in range(nsat):
+        bl.set_code(k, sc["codes"][k])
+        bl.start(k, int(sc["prn"][k]), float(sc["acq_delay"][k]), float(sc["doppler"][k] + sc["acq_err"][k]), 0, 0)
+    per = 4000
+    blocks = [np.ascontiguousarray(x[i:i + per]) for i in range(0, len(x), per)]
+    a, b = [], []
+    for blk in blocks:
+        a.append(l1.step(blk))
+    bl.submit(blocks[0])
+    for blk in blocks[1:]:
+        bl.submit(blk)
+        b.append(bl.collect())
+    b.append(bl.collect())
+    assert bl.last_step["commands"] == l1.last_step["commands"] == nsat
+    a, b = np.concatenate(a), np.concatenate(b)
+    assert len(a) > 50 and len(a) == len(b) and set(b["channel"]) == set(range(nsat))
+    for k in range(nsat):
+        assert a[a["channel"] == k].tobytes() == b[b["channel"] == k].tobytes()
+        assert bl.channel(k)["state"] == l1.channel(k)["state"] >= 2
+    with pytest.raises(IndexError):
+        bl.start(nsat, 1, 0.0, 0.0)
+    with pytest.raises(ValueError):
+        BankedTrackingLoop(cfg, 1, n_banks=2)
+    bl.close()
+    l1.close()
+    e1.close()
+
+
+@pytest.mark.gpu
 def test_device_loop_many_channels_run_kernel():
     """2048 channels at 25 MS/s (the run-based correlator kernel drives the loop): every channel reaches narrow tracking on its own
     satellite of a 32-satellite stream and reports Doppler / CN0 near the truth; one correlate launch + one loop kernel per code period."""
