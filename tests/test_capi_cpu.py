@@ -57,6 +57,13 @@ def test_no_device_is_a_loud_error_not_a_fallback(capi):
     with pytest.raises(capi.GB200Error):
         from gnss_sim_receiver_b200.tracking import TrackingEngine
         TrackingEngine()
+    # the banked loop checks its arguments first and then fails like the engine it is made of (nothing is left half-built)
+    from gnss_sim_receiver_b200.tracking import BankedTrackingLoop, loop_config
+    cfg = loop_config("1C", 4e6)
+    with pytest.raises(ValueError):
+        BankedTrackingLoop(cfg, 1, n_banks=2)
+    with pytest.raises(capi.GB200Error, match="no CPU fallback"):
+        BankedTrackingLoop(cfg, 8, n_banks=2)
 
 
 def test_product_never_references_the_oracle():
