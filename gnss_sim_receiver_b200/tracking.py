@@ -320,6 +320,7 @@ class BankedTrackingLoop:
         per = -(-n_channels // n_banks)
         self.n, self.cfg, self.per = n_channels, config, per
         self.engines, self.loops = [], []
+        self._last = dict(device_ms=0.0, commands=0, rounds=0)
         slots = 2 if config.track_pilot else 1  # code slots and commands per channel (tracking + data component)
         try:
             for b in range(n_banks):
