@@ -7,7 +7,7 @@ Same workload as bench_closed_loop.py (GPS L1 C/A, 25 MS/s cf32, 11 taps, 10240 
 (gb200_loop_submit / gb200_loop_collect, two steps in flight per bank), host buffers in, records out; every bank is pushed the period's
 IQ block itself (B x the H2D bytes).  One JSON line per B:
 
-    python tools/prof_two_banks.py [--banks 1,2,4] [--periods 1000] [--lock 400]
+    python tools/prof_two_banks.py [--banks 1,2,4] [--periods 1000] [--lock 400] [--channels 1024,4096]
 """
 import argparse
 import json
@@ -21,14 +21,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def run(n_banks, periods, lock, stream):
+def run(n_banks, periods, lock, stream, nch=None):
     import torch
     import bench
     import bench_closed_loop as C
     from gnss_sim_receiver_b200 import _capi
     from gnss_sim_receiver_b200.tracking import TrackingEngine, TrackingLoop, loop_config
     lib = _capi.lib()
-    nch = bench.CHANNELS_PER_GPU
+    nch = nch or bench.CHANNELS_PER_GPU
     per = nch // n_banks
     codes = bench.gps_codes()
     pinned, sc = stream
@@ -92,12 +92,14 @@ def main():
     ap.add_argument("--banks", default="1,2,4")
     ap.add_argument("--periods", type=int, default=1000)
     ap.add_argument("--lock", type=int, default=400)
+    ap.add_argument("--channels", default="", help="comma-separated channel counts on the GPU (default: the bench's 10240)")
     a = ap.parse_args()
     import bench
     import bench_closed_loop as C
     stream = C._stream(0, bench.gps_codes(), 100)
-    for b in [int(x) for x in a.banks.split(",")]:
-        print(json.dumps(run(b, a.periods, a.lock, stream)), flush=True)
+    for nch in [int(x) for x in a.channels.split(",")] if a.channels else [None]:
+        for b in [int(x) for x in a.banks.split(",")]:
+            print(json.dumps(dict(run(b, a.periods, a.lock, stream, nch), channels=nch or bench.CHANNELS_PER_GPU)), flush=True)
 
 
 if __name__ == "__main__":
