@@ -312,7 +312,8 @@ class BankedTrackingLoop:
     Why: a bank's period is correlate -> loop closure -> correlate ... on the engine's one stream, so the loop-closure kernel (a short dependent chain
     on two warps per SM) sits between two correlator launches.  With two banks — two streams — it runs under the other bank's correlator: 0.302 instead
     of 0.331 ms per period for 10 240 channels at 25 MS/s, identical records (bench_closed_loop.py::run_two_banks).  Every bank keeps its own copy of the
-    IQ ring, so a block is uploaded n_banks times.  More than two banks add nothing."""
+    IQ ring, so a block is uploaded n_banks times.  More than two banks add nothing; below about 2 000 channels a period is bound by the host calls and
+    ONE bank (TrackingLoop) is the faster form (profiles/r02p_two_banks_channel_counts.jsonl)."""
 
     def __init__(self, config, n_channels, n_banks=2, device=0, max_code_len=10230, iq_dtype=IQ_CF32, ring_samples=1 << 20, max_block=1 << 17):
         if n_banks < 1 or n_channels < n_banks:
